@@ -1,0 +1,317 @@
+// gsr_api.cu -- the extern "C" boundary (include/gsr.h) and the host-side stage sequence.
+//
+// Mirrors CudaRasterizer::Rasterizer::{forward,backward,markVisible}
+// (diff-gaussian-rasterization-npu/cuda_rasterizer/rasterizer_impl.cu:141-153, :198-341, :345-450).
+// No global mutable state: scratch lives in the three caller-owned buffers, errors and stage
+// timings are thread-local.
+#include "../../include/gsr.h"
+#include "gsr_common.cuh"
+#include <cstdio>
+#include <cstring>
+#include <cstdarg>
+
+static thread_local char tl_error[512] = "";
+static thread_local int tl_profiling = 0;
+static thread_local float tl_stage_ms[10] = { -1, -1, -1, -1, -1, -1, -1, -1, -1, -1 };
+
+static int fail(int code, const char* fmt, ...) {
+    va_list ap; va_start(ap, fmt);
+    vsnprintf(tl_error, sizeof(tl_error), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                         \
+    do { cudaError_t e_ = (expr);                                                              \
+         if (e_ != cudaSuccess) return fail(GSR_ERR_CUDA, "[CUDA ERROR] in %s\nLine %d: %s", __FILE__, __LINE__, cudaGetErrorString(e_)); } while (0)
+
+// reference CHECK_CUDA (auxiliary.h:178-185): with debug, synchronise after the stage and report
+#define STAGE_CHECK(debug, stream, what)                                                       \
+    do { cudaError_t e_ = cudaGetLastError();                                                  \
+         if (e_ == cudaSuccess && (debug)) e_ = cudaStreamSynchronize(stream);                 \
+         if (e_ != cudaSuccess) return fail(GSR_ERR_CUDA, "[CUDA ERROR] in %s: %s", what, cudaGetErrorString(e_)); } while (0)
+
+static inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+extern "C" const char* gsr_last_error(void) { return tl_error; }
+extern "C" const char* gsr_version(void) { return "gsr_b200 0.1 (sm_100a)"; }
+extern "C" void gsr_set_profiling(int enabled) { tl_profiling = enabled; }
+extern "C" float gsr_last_stage_ms(int stage) { return (stage >= 0 && stage < 10) ? tl_stage_ms[stage] : -1.0f; }
+
+// ---- scratch layouts ------------------------------------------------------------------------------
+extern "C" void gsr_get_geometry_layout(int P, gsr_geometry_layout* o) {
+    size_t off = 0; const size_t p = (size_t)(P > 0 ? P : 0);
+    o->depths = off;        off = up256(off + p * 4);
+    o->records = off;       off = up256(off + p * GSR_REC_FLOATS * 4);
+    o->cov3D = off;         off = up256(off + p * 6 * 4);
+    o->clamped = off;       off = up256(off + p);
+    o->tiles_touched = off; off = up256(off + p * 4);
+    o->point_offsets = off; off = up256(off + p * 4);
+    /* scan state */        off = up256(off + gsr_scan_state_words(p) * 4);
+    o->total = off + 256;
+}
+static size_t geom_scan_state_offset(int P) {
+    gsr_geometry_layout l; gsr_get_geometry_layout(P, &l);
+    return up256(l.point_offsets + (size_t)(P > 0 ? P : 0) * 4);
+}
+extern "C" void gsr_get_image_layout(int width, int height, gsr_image_layout* o) {
+    const size_t hw = (size_t)width * height;
+    const size_t tiles = (size_t)((width + GSR_TILE - 1) / GSR_TILE) * ((height + GSR_TILE - 1) / GSR_TILE);
+    size_t off = 0;
+    o->final_T = off;   off = up256(off + hw * 4);
+    o->n_contrib = off; off = up256(off + hw * 4);
+    o->ranges = off;    off = up256(off + tiles * 8);
+    o->total = off + 256;
+}
+extern "C" void gsr_get_binning_layout(size_t n, int width, int height, gsr_binning_layout* o) {
+    (void)width; (void)height;
+    size_t off = 0;
+    o->keys_unsorted = off;   off = up256(off + n * 8);
+    o->values_unsorted = off; off = up256(off + n * 4);
+    o->keys = off;            off = up256(off + n * 8);
+    o->point_list = off;      off = up256(off + n * 4);
+    o->sort_temp = off;       off = up256(off + sort_temp_bytes(n));
+    o->total = off + 256;
+}
+extern "C" size_t gsr_geometry_bytes(int P) { gsr_geometry_layout l; gsr_get_geometry_layout(P, &l); return l.total; }
+extern "C" size_t gsr_image_bytes(int w, int h) { gsr_image_layout l; gsr_get_image_layout(w, h, &l); return l.total; }
+extern "C" size_t gsr_binning_bytes(size_t n, int w, int h) { gsr_binning_layout l; gsr_get_binning_layout(n, w, h, &l); return l.total; }
+
+static inline char* align_base(char* p) { return (char*)(((uintptr_t)p + 255) & ~(uintptr_t)255); }
+
+static GeomView geom_view(char* base, int P) {
+    base = align_base(base);
+    gsr_geometry_layout l; gsr_get_geometry_layout(P, &l);
+    GeomView g;
+    g.depths = (float*)(base + l.depths);
+    g.records = (float4*)(base + l.records);
+    g.cov3D = (float*)(base + l.cov3D);
+    g.clamped = (unsigned char*)(base + l.clamped);
+    g.tiles_touched = (uint32_t*)(base + l.tiles_touched);
+    g.point_offsets = (uint32_t*)(base + l.point_offsets);
+    g.scan_state = (uint32_t*)(base + geom_scan_state_offset(P));
+    return g;
+}
+static ImageView image_view(char* base, int w, int h) {
+    base = align_base(base);
+    gsr_image_layout l; gsr_get_image_layout(w, h, &l);
+    ImageView v;
+    v.final_T = (float*)(base + l.final_T);
+    v.n_contrib = (uint32_t*)(base + l.n_contrib);
+    v.ranges = (uint2*)(base + l.ranges);
+    return v;
+}
+static BinningView binning_view(char* base, size_t n, int w, int h) {
+    base = align_base(base);
+    gsr_binning_layout l; gsr_get_binning_layout(n, w, h, &l);
+    BinningView b;
+    b.keys_unsorted = (uint64_t*)(base + l.keys_unsorted);
+    b.values_unsorted = (uint32_t*)(base + l.values_unsorted);
+    b.keys = (uint64_t*)(base + l.keys);
+    b.point_list = (uint32_t*)(base + l.point_list);
+    b.sort_temp = base + l.sort_temp;
+    return b;
+}
+
+// rasterizer_impl.cu:35-50
+static uint32_t higher_msb(uint32_t n) {
+    uint32_t msb = sizeof(n) * 4, step = msb;
+    while (step > 1) { step /= 2; if (n >> msb) msb += step; else msb -= step; }
+    if (n >> msb) msb++;
+    return msb;
+}
+
+void launch_sort_pairs_pingpong(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, size_t n,
+                                int end_bit, char* temp, cudaStream_t s, int* result_in_b);
+
+// ---- stage timers (profiling only) -----------------------------------------------------------------
+struct StageTimer {
+    cudaEvent_t ev[10]; int n = 0; bool on; cudaStream_t s;
+    StageTimer(bool enabled, cudaStream_t st) : on(enabled), s(st) { if (on) for (auto& e : ev) cudaEventCreate(&e); }
+    void mark() { if (on && n < 10) cudaEventRecord(ev[n++], s); }
+    void finish(const int* stage_ids) {
+        if (!on) return;
+        cudaStreamSynchronize(s);
+        for (int k = 0; k + 1 < n; k++) { float ms = -1; cudaEventElapsedTime(&ms, ev[k], ev[k + 1]); tl_stage_ms[stage_ids[k]] = ms; }
+        for (auto& e : ev) cudaEventDestroy(e);
+        on = false;
+    }
+    ~StageTimer() { if (on) for (auto& e : ev) cudaEventDestroy(e); }
+};
+
+static int check_aligned16(const void* p, const char* name) {
+    if (p && ((uintptr_t)p & 15)) return fail(GSR_ERR_INVALID, "%s must be 16-byte aligned", name);
+    return GSR_OK;
+}
+
+extern "C" int gsr_forward(const gsr_forward_args* a, gsr_alloc_fn geom_alloc, void* geom_user,
+                           gsr_alloc_fn binning_alloc, void* binning_user, gsr_alloc_fn image_alloc,
+                           void* image_user, void* stream_, int* num_rendered) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!a || !num_rendered || !geom_alloc || !binning_alloc || !image_alloc) return fail(GSR_ERR_INVALID, "null argument");
+    *num_rendered = 0;
+    const int P = a->P, W = a->width, H = a->height;
+    if (P < 0 || W <= 0 || H <= 0) return fail(GSR_ERR_INVALID, "bad sizes P=%d W=%d H=%d", P, W, H);
+    if (!a->out_color) return fail(GSR_ERR_INVALID, "out_color is null");
+    if (P == 0) return GSR_OK;     // reference: kernels skipped, outputs stay as allocated (rasterize_points.cu:88)
+    if (!a->means3D || !a->opacities || !a->viewmatrix || !a->projmatrix || !a->cam_pos || !a->background || !a->radii)
+        return fail(GSR_ERR_INVALID, "missing required input pointer");
+    if (!a->shs && !a->colors_precomp)   // reference: NUM_CHANNELS != 3 && colors_precomp == nullptr (rasterizer_impl.cu:244-247)
+        return fail(GSR_ERR_INVALID, "For non-RGB, provide precomputed Gaussian colors!");
+    if (a->shs && a->M <= 0) return fail(GSR_ERR_INVALID, "shs given but M=%d", a->M);
+    if (a->shs && (a->D < 0 || (a->D + 1) * (a->D + 1) > a->M || a->D > 3)) return fail(GSR_ERR_INVALID, "SH degree %d does not fit M=%d", a->D, a->M);
+    if (!a->cov3D_precomp && (!a->scales || !a->rotations)) return fail(GSR_ERR_INVALID, "need scales+rotations or cov3D_precomp");
+    if (check_aligned16(a->rotations, "rotations") || (a->M == 16 && check_aligned16(a->shs, "shs"))) return GSR_ERR_INVALID;
+
+    const int gx = (W + GSR_TILE - 1) / GSR_TILE, gy = (H + GSR_TILE - 1) / GSR_TILE;
+
+    char* geom_raw = geom_alloc(gsr_geometry_bytes(P), geom_user);
+    if (!geom_raw) return fail(GSR_ERR_ALLOC, "geometry allocator returned null");
+    char* img_raw = image_alloc(gsr_image_bytes(W, H), image_user);
+    if (!img_raw) return fail(GSR_ERR_ALLOC, "image allocator returned null");
+    GeomView g = geom_view(geom_raw, P);
+    ImageView im = image_view(img_raw, W, H);
+
+    FwdParams p;
+    p.P = P; p.D = a->D; p.M = a->shs ? a->M : 0; p.W = W; p.H = H; p.gx = gx; p.gy = gy;
+    p.background = a->background; p.means3D = a->means3D; p.shs = a->shs; p.colors_precomp = a->colors_precomp;
+    p.opacities = a->opacities; p.scales = a->scales; p.rotations = a->rotations; p.cov3D_precomp = a->cov3D_precomp;
+    p.viewmatrix = a->viewmatrix; p.projmatrix = a->projmatrix; p.cam_pos = a->cam_pos;
+    p.scale_modifier = a->scale_modifier; p.tan_fovx = a->tan_fovx; p.tan_fovy = a->tan_fovy;
+    p.focal_y = H / (2.0f * a->tan_fovy);          // rasterizer_impl.cu:224-225
+    p.focal_x = W / (2.0f * a->tan_fovx);
+    p.prefiltered = a->prefiltered; p.antialiasing = a->antialiasing;
+
+    StageTimer tm(tl_profiling != 0, stream);
+    tm.mark();
+    CUDA_TRY(cudaMemsetAsync(g.scan_state, 0, gsr_scan_state_words((size_t)P) * 4, stream));
+    launch_preprocess_fwd(p, g, a->radii, stream);
+    STAGE_CHECK(a->debug, stream, "preprocess");
+    tm.mark();
+    launch_scan(P, g, stream);
+    STAGE_CHECK(a->debug, stream, "scan");
+
+    // total instance count -> host (the reference's blocking cudaMemcpy, rasterizer_impl.cu:283-284)
+    static thread_local uint32_t* pinned = nullptr;
+    if (!pinned) CUDA_TRY(cudaHostAlloc((void**)&pinned, 64, cudaHostAllocDefault));
+    CUDA_TRY(cudaMemcpyAsync(pinned, g.scan_state + 1, 8, cudaMemcpyDeviceToHost, stream));
+    tm.mark();
+    CUDA_TRY(cudaStreamSynchronize(stream));
+    const uint32_t trapped = pinned[0];
+    const size_t N = pinned[1];
+    if (trapped) return fail(GSR_ERR_PREFILTERED, "Point is filtered although prefiltered is set. This shouldn't happen!");
+    if (N >= (1u << 30)) return fail(GSR_ERR_INVALID, "num_rendered=%zu exceeds the supported 2^30", N);
+    *num_rendered = (int)N;
+    tm.mark();      // host round trip ends here (stage 8 = sync gap)
+
+    char* bin_raw = binning_alloc(gsr_binning_bytes(N, W, H), binning_user);
+    if (!bin_raw) return fail(GSR_ERR_ALLOC, "binning allocator returned null");
+    BinningView b = binning_view(bin_raw, N, W, H);
+
+    const int end_bit = 32 + (int)higher_msb((uint32_t)(gx * gy));
+    const int passes = (end_bit + 7) / 8;
+    // ping-pong: start in whichever buffer pair makes the sorted result land in (keys, point_list)
+    uint64_t* k_start = (passes & 1) ? b.keys_unsorted : b.keys;
+    uint32_t* v_start = (passes & 1) ? b.values_unsorted : b.point_list;
+    uint64_t* k_other = (passes & 1) ? b.keys : b.keys_unsorted;
+    uint32_t* v_other = (passes & 1) ? b.point_list : b.values_unsorted;
+    if (N > 0) {
+        launch_duplicate_keys(P, gx, gy, g, a->radii, k_start, v_start, stream);
+        STAGE_CHECK(a->debug, stream, "duplicateWithKeys");
+        tm.mark();
+        int in_b = 0;
+        launch_sort_pairs_pingpong(k_start, v_start, k_other, v_other, N, end_bit, b.sort_temp, stream, &in_b);
+        STAGE_CHECK(a->debug, stream, "radix sort");
+        tm.mark();
+    } else { tm.mark(); tm.mark(); }
+    launch_tile_ranges(N, b.keys, im.ranges, gx * gy, stream);
+    STAGE_CHECK(a->debug, stream, "identifyTileRanges");
+    tm.mark();
+    launch_render_fwd(W, H, gx, gy, im.ranges, b.point_list, g.records, a->background, im.final_T, im.n_contrib,
+                      a->out_color, a->out_invdepth, stream);
+    STAGE_CHECK(a->debug, stream, "render");
+    tm.mark();
+    // marks: start | preprocess | scan+copy | host sync | duplicate | sort | ranges | render
+    static const int ids[] = { 0, 1, 8, 2, 3, 4, 5 };
+    tm.finish(ids);
+    return GSR_OK;
+}
+
+extern "C" int gsr_backward(const gsr_backward_args* a, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!a) return fail(GSR_ERR_INVALID, "null argument");
+    const int P = a->P, W = a->width, H = a->height;
+    if (P < 0 || W <= 0 || H <= 0 || a->R < 0) return fail(GSR_ERR_INVALID, "bad sizes");
+    if (P == 0) return GSR_OK;
+    if (!a->geom_buffer || !a->binning_buffer || !a->image_buffer || !a->dL_dpix || !a->radii)
+        return fail(GSR_ERR_INVALID, "missing buffer");
+    if (!a->dL_dmean2D || !a->dL_dconic || !a->dL_dopacity || !a->dL_dcolor || !a->dL_dmean3D || !a->dL_dcov3D)
+        return fail(GSR_ERR_INVALID, "missing gradient output");
+    if (a->dL_dinvdepth_pix && !a->dL_dinvdepth) return fail(GSR_ERR_INVALID, "dL_dinvdepth output required");
+    if (a->shs && a->M > 0 && !a->dL_dsh) return fail(GSR_ERR_INVALID, "dL_dsh output required");
+    if (a->scales && (!a->dL_dscale || !a->dL_drot || !a->rotations)) return fail(GSR_ERR_INVALID, "dL_dscale/dL_drot outputs required");
+    if (check_aligned16(a->rotations, "rotations") || check_aligned16(a->dL_drot, "dL_drot") ||
+        check_aligned16(a->dL_dconic, "dL_dconic") || (a->M == 16 && (check_aligned16(a->shs, "shs") || check_aligned16(a->dL_dsh, "dL_dsh"))))
+        return GSR_ERR_INVALID;
+    const int gx = (W + GSR_TILE - 1) / GSR_TILE, gy = (H + GSR_TILE - 1) / GSR_TILE;
+    GeomView g = geom_view(a->geom_buffer, P);
+    ImageView im = image_view(a->image_buffer, W, H);
+    BinningView b = binning_view(a->binning_buffer, (size_t)a->R, W, H);
+
+    BwdParams p;
+    p.P = P; p.D = a->D; p.M = a->shs ? a->M : 0; p.W = W; p.H = H; p.gx = gx; p.gy = gy;
+    p.background = a->background; p.means3D = a->means3D; p.shs = a->shs; p.colors_precomp = a->colors_precomp;
+    p.opacities = a->opacities; p.scales = a->scales; p.rotations = a->rotations; p.cov3D_precomp = a->cov3D_precomp;
+    p.viewmatrix = a->viewmatrix; p.projmatrix = a->projmatrix; p.cam_pos = a->cam_pos;
+    p.scale_modifier = a->scale_modifier; p.tan_fovx = a->tan_fovx; p.tan_fovy = a->tan_fovy;
+    p.focal_y = H / (2.0f * a->tan_fovy); p.focal_x = W / (2.0f * a->tan_fovx);
+    p.antialiasing = a->antialiasing; p.radii = a->radii;
+    p.dL_dpix = a->dL_dpix; p.dL_dinvdepth_pix = a->dL_dinvdepth_pix;
+    p.dL_dmean2D = a->dL_dmean2D; p.dL_dconic = a->dL_dconic; p.dL_dopacity = a->dL_dopacity; p.dL_dcolor = a->dL_dcolor;
+    p.dL_dinvdepth = a->dL_dinvdepth_pix ? a->dL_dinvdepth : nullptr;
+    p.dL_dmean3D = a->dL_dmean3D; p.dL_dcov3D = a->dL_dcov3D; p.dL_dsh = a->dL_dsh; p.dL_dscale = a->dL_dscale; p.dL_drot = a->dL_drot;
+
+    StageTimer tm(tl_profiling != 0, stream);
+    tm.mark();
+    // the five atomically accumulated outputs start from zero; everything else is fully written below
+    const size_t sp = (size_t)P;
+    CUDA_TRY(cudaMemsetAsync(a->dL_dmean2D, 0, sp * 3 * 4, stream));
+    CUDA_TRY(cudaMemsetAsync(a->dL_dconic, 0, sp * 4 * 4, stream));
+    CUDA_TRY(cudaMemsetAsync(a->dL_dopacity, 0, sp * 4, stream));
+    CUDA_TRY(cudaMemsetAsync(a->dL_dcolor, 0, sp * 3 * 4, stream));
+    if (p.dL_dinvdepth) CUDA_TRY(cudaMemsetAsync(p.dL_dinvdepth, 0, sp * 4, stream));
+    if (a->R > 0) {
+        launch_render_bwd(p, im.ranges, b.point_list, g.records, im.final_T, im.n_contrib, stream);
+        STAGE_CHECK(a->debug, stream, "render backward");
+    }
+    tm.mark();
+    launch_preprocess_bwd(p, g, stream);
+    STAGE_CHECK(a->debug, stream, "preprocess backward");
+    tm.mark();
+    static const int ids[] = { 6, 7 };
+    tm.finish(ids);
+    return GSR_OK;
+}
+
+extern "C" int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                                unsigned char* present, void* stream_) {
+    (void)projmatrix;   // the reference's projected-bounds test is commented out (auxiliary.h:166)
+    if (P < 0) return fail(GSR_ERR_INVALID, "bad P");
+    if (P == 0) return GSR_OK;
+    if (!means3D || !viewmatrix || !present) return fail(GSR_ERR_INVALID, "null argument");
+    launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream_);
+    STAGE_CHECK(0, (cudaStream_t)stream_, "markVisible");
+    return GSR_OK;
+}
+
+extern "C" size_t gsr_sort_temp_bytes(size_t n) { return sort_temp_bytes(n) + 256; }
+
+extern "C" int gsr_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, size_t n,
+                              int end_bit, char* temp, void* stream_) {
+    if (end_bit < 0 || end_bit > 64) return fail(GSR_ERR_INVALID, "end_bit out of range");
+    if (n >= ((size_t)1 << 30)) return fail(GSR_ERR_INVALID, "n exceeds 2^30");
+    if (n && (!keys_in || !vals_in || !keys_out || !vals_out || !temp)) return fail(GSR_ERR_INVALID, "null argument");
+    launch_sort_pairs(keys_in, vals_in, keys_out, vals_out, n, end_bit, align_base(temp), (cudaStream_t)stream_);
+    STAGE_CHECK(0, (cudaStream_t)stream_, "sort");
+    return GSR_OK;
+}

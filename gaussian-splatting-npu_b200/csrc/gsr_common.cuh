@@ -1,0 +1,133 @@
+// gsr_common.cuh -- shared definitions of the sm_100a rasterizer kernels (internal, not the ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+
+#define GSR_TILE 16
+#define GSR_TILE_PIX 256
+#define GSR_REC_FLOATS 12          // packed per-Gaussian render record, 48 bytes = 3 x float4
+
+// ---- exactly-rounded arithmetic helpers ------------------------------------------------------
+// The chain that decides depth keys, radii, tile rects and n_contrib must round exactly like the
+// reference's sm_100a build (see DESIGN.md "floating-point contract").  These intrinsics are never
+// contracted or re-associated by nvcc/ptxas, so the FFMA placement below is the one we wrote.
+__device__ __forceinline__ float fmul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float fsub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float ffma(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+__device__ __forceinline__ float fdiv(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ float frcp(float a) { return __frcp_rn(a); }
+__device__ __forceinline__ float fsqrt(float a) { return __fsqrt_rn(a); }
+
+// m[r] * x + m[4+r] * y + m[8+r] * z + m[12+r]  (reference auxiliary.h:70-89; its SASS is
+// FMUL(y,m4) ; FFMA(x,m0,.) ; FFMA(z,m8,.) ; FADD(.,m12))
+__device__ __forceinline__ float xform_row(const float* m, int r, float x, float y, float z) {
+    return fadd(ffma(z, m[8 + r], ffma(x, m[r], fmul(y, m[4 + r]))), m[12 + r]);
+}
+
+// reference auxiliary.h:40-43, evaluated in double: DADD ; DFMA(.,S,-1) ; DMUL 0.5 ; F2F
+__device__ __forceinline__ float ndc2pix(float v, int S) {
+    return __double2float_rn(__dmul_rn(__fma_rn(__dadd_rn((double)v, 1.0), (double)S, -1.0), 0.5));
+}
+
+// reference auxiliary.h:45-55.  __float2int_rz saturates / maps NaN to 0 like cvt.rzi.s32.f32.
+__device__ __forceinline__ void get_rect(float px, float py, int radius, int gx, int gy,
+                                         int& x0, int& y0, int& x1, int& y1) {
+    const float rf = (float)radius;
+    x0 = min(gx, max(0, __float2int_rz(fmul(fsub(px, rf), 0.0625f))));
+    y0 = min(gy, max(0, __float2int_rz(fmul(fsub(py, rf), 0.0625f))));
+    x1 = min(gx, max(0, __float2int_rz(fmul(fsub(fadd(fadd(px, rf), 16.0f), 1.0f), 0.0625f))));
+    y1 = min(gy, max(0, __float2int_rz(fmul(fsub(fadd(fadd(py, rf), 16.0f), 1.0f), 0.0625f))));
+}
+
+// power = -0.5 (A dx^2 + C dy^2) - B dx dy with the reference's rounding (forward.cu:355; SASS:
+// FMUL(dy,C) ; FMUL(dx,A) ; FMUL(dy,.) ; FFMA(dx,.,.) ; FMUL(dx,B) ; FMUL(dy,.) ; FFMA(.,-0.5,-.))
+__device__ __forceinline__ float blend_power(float dx, float dy, float A, float B, float C) {
+    const float t1 = fmul(dy, fmul(dy, C));
+    const float a = ffma(dx, fmul(dx, A), t1);
+    const float t4 = fmul(dy, fmul(dx, B));
+    return ffma(a, -0.5f, -t4);
+}
+
+// ---- streaming load/store helpers --------------------------------------------------------------
+__device__ __forceinline__ float4 ldg_stream_f4(const float4* p) {
+    float4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void stg_stream_f4(float4* p, float4 v) {
+    asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// ---- scratch buffer views ----------------------------------------------------------------------
+struct GeomView {
+    float* depths;            // [P]
+    float4* records;          // [P*3]
+    float* cov3D;             // [P*6]
+    unsigned char* clamped;   // [P]
+    uint32_t* tiles_touched;  // [P]
+    uint32_t* point_offsets;  // [P]
+    uint32_t* scan_state;     // scan tile counter + per-tile status words + error counter
+};
+struct ImageView {
+    float* final_T;           // [H*W]
+    uint32_t* n_contrib;      // [H*W]
+    uint2* ranges;            // [T]
+};
+struct BinningView {
+    uint64_t* keys_unsorted;
+    uint32_t* values_unsorted;
+    uint64_t* keys;
+    uint32_t* point_list;
+    char* sort_temp;
+};
+
+// ---- kernel launchers (one per stage), all asynchronous on `stream` ----------------------------
+struct FwdParams {
+    int P, D, M, W, H, gx, gy;
+    const float *background, *means3D, *shs, *colors_precomp, *opacities, *scales, *rotations,
+        *cov3D_precomp, *viewmatrix, *projmatrix, *cam_pos;
+    float scale_modifier, tan_fovx, tan_fovy, focal_x, focal_y;
+    int prefiltered, antialiasing;
+};
+
+#define GSR_SCAN_ITEMS 4096   // tiles_touched values handled per scan tile
+__host__ __device__ inline size_t gsr_scan_tiles(size_t P) { return (P + GSR_SCAN_ITEMS - 1) / GSR_SCAN_ITEMS; }
+// scan_state words: [0] dynamic tile counter, [1] prefiltered-error counter, [2] total (num_rendered),
+// [3] reserved, [4..4+2*tiles) 64-bit status words
+__host__ __device__ inline size_t gsr_scan_state_words(size_t P) { return 4 + 2 * gsr_scan_tiles(P) + 2; }
+
+void launch_preprocess_fwd(const FwdParams& p, const GeomView& g, int* radii, cudaStream_t s);
+void launch_scan(int P, const GeomView& g, cudaStream_t s);
+void launch_duplicate_keys(int P, int gx, int gy, const GeomView& g, const int* radii,
+                           uint64_t* keys, uint32_t* values, cudaStream_t s);
+void launch_tile_ranges(size_t N, const uint64_t* keys, uint2* ranges, int num_tiles, cudaStream_t s);
+void launch_render_fwd(int W, int H, int gx, int gy, const uint2* ranges, const uint32_t* point_list,
+                       const float4* records, const float* background, float* final_T,
+                       uint32_t* n_contrib, float* out_color, float* out_invdepth, cudaStream_t s);
+void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, unsigned char* present,
+                         cudaStream_t s);
+
+size_t sort_temp_bytes(size_t n);
+// Sorts on bits [0,end_bit). Result lands in keys_out/vals_out; keys_in/vals_in are scratch afterwards.
+void launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                       size_t n, int end_bit, char* temp, cudaStream_t s);
+
+struct BwdParams {
+    int P, D, M, W, H, gx, gy;
+    const float *background, *means3D, *shs, *colors_precomp, *opacities, *scales, *rotations,
+        *cov3D_precomp, *viewmatrix, *projmatrix, *cam_pos;
+    float scale_modifier, tan_fovx, tan_fovy, focal_x, focal_y;
+    int antialiasing;
+    const int* radii;
+    const float *dL_dpix, *dL_dinvdepth_pix;
+    float *dL_dmean2D, *dL_dconic, *dL_dopacity, *dL_dcolor, *dL_dinvdepth, *dL_dmean3D, *dL_dcov3D,
+        *dL_dsh, *dL_dscale, *dL_drot;
+};
+void launch_render_bwd(const BwdParams& p, const uint2* ranges, const uint32_t* point_list,
+                       const float4* records, const float* final_T, const uint32_t* n_contrib,
+                       cudaStream_t s);
+void launch_preprocess_bwd(const BwdParams& p, const GeomView& g, cudaStream_t s);

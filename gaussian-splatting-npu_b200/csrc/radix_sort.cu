@@ -1,0 +1,258 @@
+// radix_sort.cu -- hand-written onesweep LSD radix sort of (u64 key, u32 value) pairs.
+//
+// Replaces cub::DeviceRadixSort::SortPairs on the tile|depth keys
+// (diff-gaussian-rasterization-npu/cuda_rasterizer/rasterizer_impl.cu:188-191, :306-311): a STABLE
+// ascending sort on key bits [0, end_bit).
+//
+// Structure (HBM-bound; algorithmic traffic 8n + passes * 24n bytes):
+//   1. sort_hist_kernel: ONE read of the keys builds the digit histograms of every pass
+//      (run-length aggregated shared-memory atomics, then one global atomic per non-empty bin).
+//   2. onesweep_kernel, once per 8-bit digit: each CTA takes a 4096-pair tile by atomic ticket,
+//      ranks its keys with warp-level match_any multisplit (stable), publishes its per-digit counts
+//      in a status array and resolves its global offsets by decoupled look-back over the
+//      predecessor tiles -- so every pass reads and writes each pair exactly once -- then reorders
+//      the tile through shared memory so that the global scatter is written in sorted runs.
+#include "gsr_common.cuh"
+
+#define SORT_THREADS 256
+#define SORT_WARPS (SORT_THREADS / 32)
+#define SORT_IPT 16
+#define SORT_TILE (SORT_THREADS * SORT_IPT)        // 4096 pairs per CTA
+#define RADIX_BITS 8
+#define RADIX 256
+#define SORT_MAX_PASSES 8
+
+#define STATUS_LOCAL 0x40000000u
+#define STATUS_INCL 0x80000000u
+#define STATUS_VMASK 0x3fffffffu
+
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+static inline size_t sort_tiles(size_t n) { return (n + SORT_TILE - 1) / SORT_TILE; }
+
+// temp layout: [ghist: 8*256 u32][counters: 8 u32 (+pad)][status: passes * tiles * 256 u32]
+size_t sort_temp_bytes(size_t n) {
+    return align_up(SORT_MAX_PASSES * RADIX * 4 + 64, 256) + SORT_MAX_PASSES * sort_tiles(n) * RADIX * 4 + 256;
+}
+
+// ---- histogram of all digits in one read ------------------------------------------------------
+#define HIST_THREADS 256
+#define HIST_KPT 8
+
+__global__ void __launch_bounds__(HIST_THREADS)
+sort_hist_kernel(const uint64_t* __restrict__ keys, size_t n, int num_passes, int end_bit, uint32_t* __restrict__ ghist) {
+    __shared__ uint32_t sh[SORT_MAX_PASSES * RADIX];
+    for (int k = threadIdx.x; k < num_passes * RADIX; k += HIST_THREADS) sh[k] = 0;
+    __syncthreads();
+    const size_t chunk = (size_t)HIST_THREADS * HIST_KPT;
+    for (size_t c = blockIdx.x; c * chunk < n; c += gridDim.x) {
+        const size_t base = c * chunk + (size_t)threadIdx.x * HIST_KPT;
+        uint64_t k[HIST_KPT];
+        int cnt = 0;
+        if (base + HIST_KPT <= n) {
+            const ulonglong2* src = reinterpret_cast<const ulonglong2*>(keys + base);
+#pragma unroll
+            for (int j = 0; j < HIST_KPT / 2; j++) { const ulonglong2 q = src[j]; k[2 * j] = q.x; k[2 * j + 1] = q.y; }
+            cnt = HIST_KPT;
+        } else {
+#pragma unroll
+            for (int j = 0; j < HIST_KPT; j++) if (base + j < n) { k[j] = keys[base + j]; cnt = j + 1; }
+        }
+        if (cnt == 0) continue;
+        for (int p = 0; p < num_passes; p++) {
+            const int shift = p * RADIX_BITS;
+            const uint32_t mask = (end_bit - shift >= RADIX_BITS) ? (RADIX - 1) : ((1u << (end_bit - shift)) - 1);
+            uint32_t* h = sh + p * RADIX;
+            uint32_t prev = (uint32_t)(k[0] >> shift) & mask, run = 1;
+#pragma unroll
+            for (int j = 1; j < HIST_KPT; j++) {
+                if (j < cnt) {
+                    const uint32_t d = (uint32_t)(k[j] >> shift) & mask;
+                    if (d == prev) run++;
+                    else { atomicAdd(&h[prev], run); prev = d; run = 1; }
+                }
+            }
+            atomicAdd(&h[prev], run);
+        }
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < num_passes * RADIX; k += HIST_THREADS) {
+        const uint32_t v = sh[k];
+        if (v) atomicAdd(&ghist[k], v);
+    }
+}
+
+// ---- one onesweep pass ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void st_volatile_u32(uint32_t* p, uint32_t v) {
+    asm volatile("st.volatile.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+
+struct OnesweepSmem {
+    uint64_t keys[SORT_TILE];                 // 32 KB
+    uint32_t vals[SORT_TILE];                 // 16 KB
+    uint32_t warp_hist[SORT_WARPS][RADIX];    //  8 KB : per-warp digit counts -> exclusive warp offsets
+    uint32_t bin_base[RADIX];                 // exclusive offset of each digit inside the tile
+    uint32_t gofs[RADIX];                     // global offset of the digit's first key minus bin_base
+    uint32_t scan_tmp[2 * SORT_WARPS];
+    uint32_t tile;
+};
+
+__global__ void __launch_bounds__(SORT_THREADS)
+onesweep_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, uint64_t* __restrict__ kout,
+                uint32_t* __restrict__ vout, size_t n, int shift, uint32_t mask, const uint32_t* __restrict__ ghist,
+                uint32_t* counter, uint32_t* status) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    OnesweepSmem& sm = *reinterpret_cast<OnesweepSmem*>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t lt_mask = (1u << lane) - 1;
+
+    if (tid == 0) sm.tile = atomicAdd(counter, 1u);
+#pragma unroll
+    for (int w = 0; w < SORT_WARPS; w++) sm.warp_hist[w][tid] = 0;
+    __syncthreads();
+    const uint32_t tile = sm.tile;
+    const size_t tile_base = (size_t)tile * SORT_TILE;
+    const uint32_t tile_n = (uint32_t)min((size_t)SORT_TILE, n - tile_base);
+    const size_t my_base = tile_base + (size_t)warp * (32 * SORT_IPT) + lane;
+
+    // 1. load keys, warp-striped: item i of this warp covers 32 consecutive keys
+    uint64_t key[SORT_IPT];
+    const bool full = tile_n == SORT_TILE;
+    if (full) {
+#pragma unroll
+        for (int i = 0; i < SORT_IPT; i++) key[i] = kin[my_base + i * 32];
+    } else {
+#pragma unroll
+        for (int i = 0; i < SORT_IPT; i++) {
+            const size_t idx = my_base + i * 32;
+            key[i] = (idx < n) ? kin[idx] : ~0ull;
+        }
+    }
+
+    // 2. stable in-warp ranking: match_any groups equal digits, the group's first lane bumps the
+    //    warp's counter for that digit, every lane gets (old count + #equal lanes before it)
+    uint16_t rank[SORT_IPT];
+    uint32_t* wh = sm.warp_hist[warp];
+#pragma unroll
+    for (int i = 0; i < SORT_IPT; i++) {
+        const bool valid = full || (my_base + i * 32 < n);
+        const uint32_t d = valid ? ((uint32_t)(key[i] >> shift) & mask) : 0xffffffffu;
+        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        const int leader = __ffs(peers) - 1;
+        uint32_t old = 0;
+        if (lane == leader && valid) { old = wh[d]; wh[d] = old + __popc(peers); }
+        old = __shfl_sync(0xffffffffu, old, leader);
+        rank[i] = (uint16_t)(old + __popc(peers & lt_mask));
+        __syncwarp();
+    }
+    __syncthreads();
+
+    // 3. thread b owns digit b: exclusive scan over the warps, publish the tile's count early
+    uint32_t count = 0;
+#pragma unroll
+    for (int w = 0; w < SORT_WARPS; w++) { const uint32_t t = sm.warp_hist[w][tid]; sm.warp_hist[w][tid] = count; count += t; }
+    uint32_t* my_status = status + (size_t)tile * RADIX + tid;
+    if (tile == 0) st_volatile_u32(my_status, STATUS_INCL | count);
+    else st_volatile_u32(my_status, STATUS_LOCAL | count);
+
+    // 4. block-wide exclusive scans of (tile counts, global histogram) over the 256 digits
+    const uint32_t gh = ghist[tid];
+    uint32_t a = count, b = gh;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t ta = __shfl_up_sync(0xffffffffu, a, d), tb = __shfl_up_sync(0xffffffffu, b, d);
+        if (lane >= d) { a += ta; b += tb; }
+    }
+    if (lane == 31) { sm.scan_tmp[warp] = a; sm.scan_tmp[SORT_WARPS + warp] = b; }
+    __syncthreads();
+    uint32_t offa = 0, offb = 0;
+#pragma unroll
+    for (int w = 0; w < SORT_WARPS; w++) if (w < warp) { offa += sm.scan_tmp[w]; offb += sm.scan_tmp[SORT_WARPS + w]; }
+    const uint32_t bin_base = offa + a - count;       // exclusive, inside the tile
+    const uint32_t g_excl = offb + b - gh;            // exclusive, whole array
+
+    // 5. decoupled look-back: sum of this digit's counts over all predecessor tiles
+    uint32_t prefix = 0;
+    if (tile > 0) {
+        int t = (int)tile - 1;
+        while (true) {
+            const uint32_t w = ld_volatile_u32(status + (size_t)t * RADIX + tid);
+            if ((w & (STATUS_LOCAL | STATUS_INCL)) == 0) continue;
+            prefix += w & STATUS_VMASK;
+            if (w & STATUS_INCL) break;
+            t--;
+        }
+        st_volatile_u32(my_status, STATUS_INCL | (prefix + count));
+    }
+    sm.bin_base[tid] = bin_base;
+    sm.gofs[tid] = g_excl + prefix - bin_base;
+    __syncthreads();
+
+    // 6. reorder the tile in shared memory (values are loaded only now to keep registers low)
+#pragma unroll
+    for (int i = 0; i < SORT_IPT; i++) {
+        const size_t idx = my_base + i * 32;
+        if (full || idx < n) {
+            const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
+            const uint32_t pos = sm.bin_base[d] + wh[d] + rank[i];
+            sm.keys[pos] = key[i];
+            sm.vals[pos] = vin[idx];
+        }
+    }
+    __syncthreads();
+
+    // 7. scatter in sorted runs
+    for (uint32_t j = tid; j < tile_n; j += SORT_THREADS) {
+        const uint64_t k = sm.keys[j];
+        const uint32_t d = (uint32_t)(k >> shift) & mask;
+        const size_t pos = (size_t)(uint32_t)(sm.gofs[d] + j);
+        kout[pos] = k;
+        vout[pos] = sm.vals[j];
+    }
+}
+
+// Returns through *result_in_b whether the sorted data ended in (keys_b, vals_b).
+void launch_sort_pairs_pingpong(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, size_t n,
+                                int end_bit, char* temp, cudaStream_t s, int* result_in_b) {
+    const int passes = (end_bit + RADIX_BITS - 1) / RADIX_BITS;
+    *result_in_b = passes & 1;
+    if (n == 0 || passes == 0) { *result_in_b = 0; return; }
+    const size_t tiles = sort_tiles(n);
+    uint32_t* ghist = reinterpret_cast<uint32_t*>(temp);
+    uint32_t* counters = ghist + SORT_MAX_PASSES * RADIX;
+    const size_t head = align_up(SORT_MAX_PASSES * RADIX * 4 + 64, 256);
+    uint32_t* status = reinterpret_cast<uint32_t*>(temp + head);
+    cudaMemsetAsync(temp, 0, head + (size_t)passes * tiles * RADIX * 4, s);
+
+    int hist_blocks = (int)min((size_t)148 * 8, (n + (size_t)HIST_THREADS * HIST_KPT - 1) / ((size_t)HIST_THREADS * HIST_KPT));
+    sort_hist_kernel<<<hist_blocks, HIST_THREADS, 0, s>>>(keys_a, n, passes, end_bit, ghist);
+
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(OnesweepSmem));
+        attr_set = true;
+    }
+    uint64_t* kin = keys_a; uint32_t* vin = vals_a; uint64_t* kout = keys_b; uint32_t* vout = vals_b;
+    for (int p = 0; p < passes; p++) {
+        const int shift = p * RADIX_BITS;
+        const uint32_t mask = (end_bit - shift >= RADIX_BITS) ? (RADIX - 1) : ((1u << (end_bit - shift)) - 1);
+        onesweep_kernel<<<(unsigned)tiles, SORT_THREADS, sizeof(OnesweepSmem), s>>>(
+            kin, vin, kout, vout, n, shift, mask, ghist + p * RADIX, counters + p, status + (size_t)p * tiles * RADIX);
+        uint64_t* tk = kin; kin = kout; kout = tk;
+        uint32_t* tv = vin; vin = vout; vout = tv;
+    }
+}
+
+void launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, size_t n,
+                       int end_bit, char* temp, cudaStream_t s) {
+    int in_b = 0;
+    launch_sort_pairs_pingpong(keys_in, vals_in, keys_out, vals_out, n, end_bit, temp, s, &in_b);
+    if (!in_b && n) {   // even number of passes: result is back in the input buffers
+        cudaMemcpyAsync(keys_out, keys_in, n * sizeof(uint64_t), cudaMemcpyDeviceToDevice, s);
+        cudaMemcpyAsync(vals_out, vals_in, n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s);
+    }
+}

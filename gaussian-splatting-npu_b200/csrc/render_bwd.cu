@@ -1,0 +1,178 @@
+// render_bwd.cu -- back-to-front backward pass of the tile blend.
+//
+// Replaces BACKWARD::render / renderCUDA<3> (diff-gaussian-rasterization-npu/cuda_rasterizer/
+// backward.cu:452-638).  The reference issues 9-10 global fp32 atomicAdd per contributing
+// (pixel, Gaussian) pair.  Here all 256 pixels of a tile look at the same Gaussian in the same
+// iteration, so the per-Gaussian sums are pre-reduced on chip:
+//   warp shuffle tree over the 32 pixels of a warp (skipped entirely when no lane contributes)
+//   -> shared-memory accumulators per staged Gaussian (one ATOMS per warp and value)
+//   -> ONE global atomic per value per (tile, Gaussian) when the batch retires.
+// That is 256x fewer global atomics than the reference.  Batches start at the tile's deepest
+// contributing position (block max of n_contrib) instead of the end of the list.  The per-pixel
+// recurrences are the reference's; power/alpha use the same exactly-rounded chain as the forward
+// so that every pair takes the same skip decisions it took there.
+#include "gsr_common.cuh"
+
+#define RB_THREADS 256
+#define RB_NV 10     // dcolor r,g,b | dinvdepth | dmean2D x,y | dconic xx,xy,yy | dopacity
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+template <bool HAS_DEPTH>
+__global__ void __launch_bounds__(RB_THREADS)
+render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                  const float4* __restrict__ records, int W, int H, int gx, const float* __restrict__ background,
+                  const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
+                  const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvdepth_pix,
+                  float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity,
+                  float* __restrict__ dL_dcolor, float* __restrict__ dL_dinvdepth) {
+    __shared__ float4 sA[RB_THREADS];          // x, y, conic.a, conic.b
+    __shared__ float4 sB[RB_THREADS];          // conic.c, opacity, r, g
+    __shared__ float2 sC[RB_THREADS];          // b, 1/depth
+    __shared__ uint32_t sId[RB_THREADS];
+    __shared__ float sAcc[RB_THREADS * RB_NV];
+    __shared__ uint32_t sMax[RB_THREADS / 32];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = blockIdx.x;
+    const int tx = tile % gx, ty = tile / gx;
+    const int px = tx * GSR_TILE + (warp & 1) * 8 + (lane & 7);
+    const int py = ty * GSR_TILE + (warp >> 1) * 4 + (lane >> 3);
+    const bool inside = px < W && py < H;
+    const float pxf = (float)px, pyf = (float)py;
+    const size_t pix = (size_t)py * W + px, HW = (size_t)H * W;
+
+    const uint2 range = ranges[tile];
+    const uint32_t last = inside ? n_contrib[pix] : 0u;
+    const float T_final = inside ? final_T[pix] : 0.0f;
+    float dpx0 = 0, dpx1 = 0, dpx2 = 0, dpd = 0;
+    if (inside) {
+        dpx0 = dL_dpix[pix]; dpx1 = dL_dpix[HW + pix]; dpx2 = dL_dpix[2 * HW + pix];
+        if (HAS_DEPTH) dpd = dL_dinvdepth_pix[pix];
+    }
+    const float bg_dot = background[0] * dpx0 + background[1] * dpx1 + background[2] * dpx2;
+    const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+
+    // deepest list position any pixel of this tile blended
+    uint32_t m = __reduce_max_sync(0xffffffffu, last);
+    if (lane == 0) sMax[warp] = m;
+    for (int k = tid; k < RB_THREADS * RB_NV; k += RB_THREADS) sAcc[k] = 0.0f;
+    __syncthreads();
+    uint32_t remaining = 0;
+#pragma unroll
+    for (int w = 0; w < RB_THREADS / 32; w++) remaining = max(remaining, sMax[w]);
+
+    float T = T_final;
+    float acc_r = 0, acc_g = 0, acc_b = 0, acc_d = 0;          // accum_rec / accum_invdepth_rec
+    float last_alpha = 0, last_r = 0, last_g = 0, last_b = 0, last_d = 0;
+
+    while (remaining > 0) {
+        const int n = (int)min((uint32_t)RB_THREADS, remaining);
+        // stage positions [remaining-n, remaining), backmost first
+        if (tid < n) {
+            const uint32_t id = point_list[range.x + remaining - 1 - tid];
+            const float4* rec = records + 3 * (size_t)id;
+            sId[tid] = id;
+            sA[tid] = rec[0];
+            sB[tid] = rec[1];
+            const float4 r2 = rec[2];
+            sC[tid] = make_float2(r2.x, r2.y);
+        }
+        __syncthreads();
+        for (int j = 0; j < n; j++) {
+            const uint32_t pos = remaining - 1 - j;             // 0-based position in the tile's list
+            float v[RB_NV];
+            bool contrib = false;
+            if (pos < last) {
+                const float4 a = sA[j];
+                const float4 b = sB[j];
+                const float dx = fsub(a.x, pxf), dy = fsub(a.y, pyf);
+                const float power = blend_power(dx, dy, a.z, a.w, b.x);
+                if (power <= 0.0f) {
+                    const float G = expf(power);
+                    const float alpha = fminf(0.99f, fmul(b.y, G));
+                    if (alpha >= 1.0f / 255.0f) {
+                        contrib = true;
+                        const float2 c = sC[j];
+                        T = T / (1.0f - alpha);
+                        const float dch = alpha * T;
+                        float dL_dalpha;
+                        acc_r = last_alpha * last_r + (1.0f - last_alpha) * acc_r; last_r = b.z;
+                        dL_dalpha = (b.z - acc_r) * dpx0;
+                        acc_g = last_alpha * last_g + (1.0f - last_alpha) * acc_g; last_g = b.w;
+                        dL_dalpha += (b.w - acc_g) * dpx1;
+                        acc_b = last_alpha * last_b + (1.0f - last_alpha) * acc_b; last_b = c.x;
+                        dL_dalpha += (c.x - acc_b) * dpx2;
+                        v[0] = dch * dpx0; v[1] = dch * dpx1; v[2] = dch * dpx2;
+                        if (HAS_DEPTH) {
+                            acc_d = last_alpha * last_d + (1.0f - last_alpha) * acc_d; last_d = c.y;
+                            dL_dalpha += (c.y - acc_d) * dpd;
+                            v[3] = dch * dpd;
+                        } else v[3] = 0.0f;
+                        dL_dalpha *= T;
+                        last_alpha = alpha;
+                        dL_dalpha += (-T_final / (1.0f - alpha)) * bg_dot;
+                        const float dL_dG = b.y * dL_dalpha;
+                        const float gdx = G * dx, gdy = G * dy;
+                        const float dG_ddelx = -gdx * a.z - gdy * a.w;
+                        const float dG_ddely = -gdy * b.x - gdx * a.w;
+                        v[4] = dL_dG * dG_ddelx * ddelx_dx;
+                        v[5] = dL_dG * dG_ddely * ddely_dy;
+                        v[6] = -0.5f * gdx * dx * dL_dG;
+                        v[7] = -0.5f * gdx * dy * dL_dG;
+                        v[8] = -0.5f * gdy * dy * dL_dG;
+                        v[9] = G * dL_dalpha;
+                    }
+                }
+            }
+            if (__any_sync(0xffffffffu, contrib)) {
+                if (!contrib) {
+#pragma unroll
+                    for (int k = 0; k < RB_NV; k++) v[k] = 0.0f;
+                }
+#pragma unroll
+                for (int k = 0; k < RB_NV; k++) {
+                    if (!HAS_DEPTH && k == 3) continue;
+                    const float s = warp_sum(v[k]);
+                    if (lane == 0) atomicAdd(&sAcc[j * RB_NV + k], s);
+                }
+            }
+        }
+        __syncthreads();
+        // retire the batch: one global atomic per value and Gaussian
+        if (tid < n) {
+            const uint32_t id = sId[tid];
+            float* a = &sAcc[tid * RB_NV];
+            if (a[0] != 0.0f) atomicAdd(&dL_dcolor[3 * (size_t)id], a[0]);
+            if (a[1] != 0.0f) atomicAdd(&dL_dcolor[3 * (size_t)id + 1], a[1]);
+            if (a[2] != 0.0f) atomicAdd(&dL_dcolor[3 * (size_t)id + 2], a[2]);
+            if (HAS_DEPTH && a[3] != 0.0f) atomicAdd(&dL_dinvdepth[id], a[3]);
+            if (a[4] != 0.0f) atomicAdd(&dL_dmean2D[3 * (size_t)id], a[4]);
+            if (a[5] != 0.0f) atomicAdd(&dL_dmean2D[3 * (size_t)id + 1], a[5]);
+            if (a[6] != 0.0f) atomicAdd(&dL_dconic[4 * (size_t)id], a[6]);
+            if (a[7] != 0.0f) atomicAdd(&dL_dconic[4 * (size_t)id + 1], a[7]);
+            if (a[8] != 0.0f) atomicAdd(&dL_dconic[4 * (size_t)id + 3], a[8]);
+            if (a[9] != 0.0f) atomicAdd(&dL_dopacity[id], a[9]);
+#pragma unroll
+            for (int k = 0; k < RB_NV; k++) a[k] = 0.0f;
+        }
+        __syncthreads();
+        remaining -= n;
+    }
+}
+
+void launch_render_bwd(const BwdParams& p, const uint2* ranges, const uint32_t* point_list, const float4* records,
+                       const float* final_T, const uint32_t* n_contrib, cudaStream_t s) {
+    const int tiles = p.gx * p.gy;
+    if (p.dL_dinvdepth_pix)
+        render_bwd_kernel<true><<<tiles, RB_THREADS, 0, s>>>(ranges, point_list, records, p.W, p.H, p.gx, p.background,
+            final_T, n_contrib, p.dL_dpix, p.dL_dinvdepth_pix, p.dL_dmean2D, p.dL_dconic, p.dL_dopacity, p.dL_dcolor,
+            p.dL_dinvdepth);
+    else
+        render_bwd_kernel<false><<<tiles, RB_THREADS, 0, s>>>(ranges, point_list, records, p.W, p.H, p.gx, p.background,
+            final_T, n_contrib, p.dL_dpix, nullptr, p.dL_dmean2D, p.dL_dconic, p.dL_dopacity, p.dL_dcolor, nullptr);
+}

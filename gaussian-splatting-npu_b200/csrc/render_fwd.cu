@@ -1,0 +1,89 @@
+// render_fwd.cu -- 16x16-tile front-to-back alpha blending.
+//
+// Replaces FORWARD::render / renderCUDA<3> (diff-gaussian-rasterization-npu/cuda_rasterizer/
+// forward.cu:277-400).  One CTA per tile, one thread per pixel; FP32-pipe / shared-memory bound.
+// Differences from the reference:
+//   * a Gaussian's whole blend record (xy, conic, opacity, rgb, 1/depth) is staged in shared
+//     memory by the cooperative fetch, so the inner loop never touches global memory (the
+//     reference fetches colour and depth from global for every contributing pair);
+//   * a warp covers an 8x4 pixel block (not a 32x1 strip... the reference's 16x2) so that a warp's
+//     pixels saturate together and whole warps fall out of the inner loop early;
+//   * the per-pair arithmetic that decides n_contrib (power, alpha, T) is written with exactly
+//     rounded intrinsics in the reference build's FFMA placement; expf is CUDA's, as there.
+#include "gsr_common.cuh"
+
+#define RF_THREADS 256
+
+__global__ void __launch_bounds__(RF_THREADS)
+render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                  const float4* __restrict__ records, int W, int H, int gx,
+                  const float* __restrict__ background, float* __restrict__ final_T,
+                  uint32_t* __restrict__ n_contrib, float* __restrict__ out_color, float* __restrict__ out_invdepth) {
+    __shared__ float4 sA[RF_THREADS];   // x, y, conic.a, conic.b
+    __shared__ float4 sB[RF_THREADS];   // conic.c, opacity, r, g
+    __shared__ float2 sC[RF_THREADS];   // b, 1/depth
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = blockIdx.x;
+    const int tx = tile % gx, ty = tile / gx;
+    const int px = tx * GSR_TILE + (warp & 1) * 8 + (lane & 7);
+    const int py = ty * GSR_TILE + (warp >> 1) * 4 + (lane >> 3);
+    const bool inside = px < W && py < H;
+    const float pxf = (float)px, pyf = (float)py;
+
+    const uint2 range = ranges[tile];
+    const int todo = (int)(range.y - range.x);
+
+    bool done = !inside;
+    float T = 1.0f, C0 = 0.0f, C1 = 0.0f, C2 = 0.0f, Dacc = 0.0f;
+    uint32_t last = 0;
+
+    for (int base = 0; base < todo; base += RF_THREADS) {
+        if (__syncthreads_count(done) == RF_THREADS) break;
+        const int n = min(RF_THREADS, todo - base);
+        if (tid < n) {
+            const uint32_t id = point_list[range.x + base + tid];
+            const float4* rec = records + 3 * (size_t)id;
+            sA[tid] = rec[0];
+            sB[tid] = rec[1];
+            const float4 r2 = rec[2];
+            sC[tid] = make_float2(r2.x, r2.y);
+        }
+        __syncthreads();
+        for (int j = 0; !done && j < n; j++) {
+            const float4 a = sA[j];
+            const float4 b = sB[j];
+            const float dx = fsub(a.x, pxf), dy = fsub(a.y, pyf);
+            const float power = blend_power(dx, dy, a.z, a.w, b.x);
+            if (power > 0.0f) continue;
+            const float alpha = fminf(0.99f, fmul(b.y, expf(power)));
+            if (alpha < 1.0f / 255.0f) continue;
+            const float test_T = fmul(T, fsub(1.0f, alpha));
+            if (test_T < 0.0001f) { done = true; continue; }
+            const float2 c = sC[j];
+            C0 = ffma(fmul(b.z, alpha), T, C0);
+            C1 = ffma(fmul(b.w, alpha), T, C1);
+            C2 = ffma(fmul(c.x, alpha), T, C2);
+            Dacc = ffma(fmul(c.y, alpha), T, Dacc);
+            T = test_T;
+            last = (uint32_t)(base + j + 1);
+        }
+    }
+
+    if (inside) {
+        const size_t pix = (size_t)py * W + px, HW = (size_t)H * W;
+        final_T[pix] = T;
+        n_contrib[pix] = last;
+        out_color[pix] = ffma(T, background[0], C0);
+        out_color[HW + pix] = ffma(T, background[1], C1);
+        out_color[2 * HW + pix] = ffma(T, background[2], C2);
+        if (out_invdepth) out_invdepth[pix] = Dacc;
+    }
+}
+
+void launch_render_fwd(int W, int H, int gx, int gy, const uint2* ranges, const uint32_t* point_list,
+                       const float4* records, const float* background, float* final_T, uint32_t* n_contrib,
+                       float* out_color, float* out_invdepth, cudaStream_t s) {
+    render_fwd_kernel<<<gx * gy, RF_THREADS, 0, s>>>(ranges, point_list, records, W, H, gx, background, final_T,
+                                                       n_contrib, out_color, out_invdepth);
+}

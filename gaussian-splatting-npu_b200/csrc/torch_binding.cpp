@@ -1,0 +1,196 @@
+// torch_binding.cpp -- the thin torch-extension layer over the C ABI (include/gsr.h).
+//
+// Keeps the reference's pybind surface so diff_gaussian_rasterization/__init__.py (and therefore
+// gaussian_renderer/__init__.py and train.py) run unchanged:
+//   rasterize_gaussians           <- RasterizeGaussiansCUDA          (DGR/rasterize_points.cu:35-124,  ext.cpp:16)
+//   rasterize_gaussians_backward  <- RasterizeGaussiansBackwardCUDA  (DGR/rasterize_points.cu:126-223, ext.cpp:17)
+//   mark_visible                  <- markVisible                     (DGR/rasterize_points.cu:225-244, ext.cpp:18)
+// (DGR = /root/reference/diff-gaussian-rasterization-npu; the fork renamed the first two to ...NPU
+// and commented the last two bindings out -- both spellings are exported here.)
+// Same argument order, same return tuples, same error text.  Differences: work is issued on the
+// current CUDA stream of means3D's device (the reference uses the legacy default stream and the
+// *current* device), and outputs the kernels fully write are torch::empty instead of zero-filled.
+#include <torch/extension.h>
+#include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <stdexcept>
+#include <tuple>
+#include "gsr.h"
+
+namespace {
+
+char* resize_cb(size_t bytes, void* user) {
+    auto* t = static_cast<torch::Tensor*>(user);
+    t->resize_({(long long)bytes});
+    return reinterpret_cast<char*>(t->data_ptr());
+}
+
+// contiguous fp32 data pointer, nullptr for an empty tensor; `keep` owns any temporary copy
+const float* fptr(const torch::Tensor& t, std::vector<torch::Tensor>& keep, bool align16 = false) {
+    if (t.numel() == 0) return nullptr;
+    torch::Tensor c = t.contiguous();
+    if (c.scalar_type() != torch::kFloat32) c = c.to(torch::kFloat32);
+    if (align16 && (reinterpret_cast<uintptr_t>(c.data_ptr()) & 15)) c = c.clone();
+    keep.push_back(c);
+    return c.data_ptr<float>();
+}
+
+void check(int status) {
+    if (status != GSR_OK) throw std::runtime_error(gsr_last_error());
+}
+
+}  // namespace
+
+std::tuple<int, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+RasterizeGaussiansCUDA(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& colors,
+                       const torch::Tensor& opacity, const torch::Tensor& scales, const torch::Tensor& rotations,
+                       const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+                       const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy,
+                       const int image_height, const int image_width, const torch::Tensor& sh, const int degree,
+                       const torch::Tensor& campos, const bool prefiltered, const bool antialiasing, const bool debug) {
+    if (means3D.ndimension() != 2 || means3D.size(1) != 3) {
+        AT_ERROR("means3D must have dimensions (num_points, 3)");
+    }
+    TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (there is no CPU fallback)");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+
+    const int P = means3D.size(0);
+    const int H = image_height, W = image_width;
+    auto float_opts = means3D.options().dtype(torch::kFloat32);
+    auto int_opts = means3D.options().dtype(torch::kInt32);
+    auto byte_opts = means3D.options().dtype(torch::kByte);
+
+    torch::Tensor out_color = P ? torch::empty({3, H, W}, float_opts) : torch::zeros({3, H, W}, float_opts);
+    torch::Tensor out_invdepth = P ? torch::empty({1, H, W}, float_opts) : torch::zeros({1, H, W}, float_opts);
+    torch::Tensor radii = P ? torch::empty({P}, int_opts) : torch::zeros({P}, int_opts);
+    torch::Tensor geomBuffer = torch::empty({0}, byte_opts);
+    torch::Tensor binningBuffer = torch::empty({0}, byte_opts);
+    torch::Tensor imgBuffer = torch::empty({0}, byte_opts);
+
+    int rendered = 0;
+    if (P != 0) {
+        std::vector<torch::Tensor> keep;
+        gsr_forward_args a;
+        a.P = P; a.D = degree; a.M = sh.size(0) != 0 ? (int)sh.size(1) : 0;
+        a.width = W; a.height = H;
+        a.background = fptr(background, keep);
+        a.means3D = fptr(means3D, keep);
+        a.shs = fptr(sh, keep, true);
+        a.colors_precomp = fptr(colors, keep);
+        a.opacities = fptr(opacity, keep);
+        a.scales = fptr(scales, keep);
+        a.scale_modifier = scale_modifier;
+        a.rotations = fptr(rotations, keep, true);
+        a.cov3D_precomp = fptr(cov3D_precomp, keep);
+        a.viewmatrix = fptr(viewmatrix, keep);
+        a.projmatrix = fptr(projmatrix, keep);
+        a.cam_pos = fptr(campos, keep);
+        a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy;
+        a.prefiltered = prefiltered; a.antialiasing = antialiasing; a.debug = debug;
+        a.out_color = out_color.data_ptr<float>();
+        a.out_invdepth = out_invdepth.data_ptr<float>();
+        a.radii = radii.data_ptr<int>();
+        check(gsr_forward(&a, resize_cb, &geomBuffer, resize_cb, &binningBuffer, resize_cb, &imgBuffer, stream, &rendered));
+    }
+    return std::make_tuple(rendered, out_color, radii, geomBuffer, binningBuffer, imgBuffer, out_invdepth);
+}
+
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+                               const torch::Tensor& colors, const torch::Tensor& opacities, const torch::Tensor& scales,
+                               const torch::Tensor& rotations, const float scale_modifier, const torch::Tensor& cov3D_precomp,
+                               const torch::Tensor& viewmatrix, const torch::Tensor& projmatrix, const float tan_fovx,
+                               const float tan_fovy, const torch::Tensor& dL_dout_color, const torch::Tensor& dL_dout_invdepth,
+                               const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
+                               const torch::Tensor& geomBuffer, const int R, const torch::Tensor& binningBuffer,
+                               const torch::Tensor& imageBuffer, const bool antialiasing, const bool debug) {
+    TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (there is no CPU fallback)");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+
+    const int P = means3D.size(0);
+    const int H = dL_dout_color.size(1), W = dL_dout_color.size(2);
+    const int M = sh.size(0) != 0 ? (int)sh.size(1) : 0;
+    auto opts = means3D.options().dtype(torch::kFloat32);
+    const bool has_depth = dL_dout_invdepth.size(0) != 0;
+    const bool has_scales = scales.numel() != 0;
+    const bool live = P != 0;
+
+    auto mk = [&](std::initializer_list<int64_t> shape, bool written) {
+        return (live && written) ? torch::empty(shape, opts) : torch::zeros(shape, opts);
+    };
+    torch::Tensor dL_dmeans3D = mk({P, 3}, true);
+    torch::Tensor dL_dmeans2D = mk({P, 3}, true);
+    torch::Tensor dL_dcolors = mk({P, 3}, true);
+    torch::Tensor dL_dconic = mk({P, 2, 2}, true);
+    torch::Tensor dL_dopacity = mk({P, 1}, true);
+    torch::Tensor dL_dcov3D = mk({P, 6}, true);
+    torch::Tensor dL_dsh = mk({P, M, 3}, M > 0);
+    torch::Tensor dL_dscales = mk({P, 3}, has_scales);
+    torch::Tensor dL_drotations = mk({P, 4}, has_scales);
+    torch::Tensor dL_dinvdepths = has_depth ? mk({P, 1}, true) : torch::zeros({0, 1}, opts);
+
+    if (live) {
+        std::vector<torch::Tensor> keep;
+        gsr_backward_args a;
+        a.P = P; a.D = degree; a.M = M; a.R = R; a.width = W; a.height = H;
+        a.background = fptr(background, keep);
+        a.means3D = fptr(means3D, keep);
+        a.shs = fptr(sh, keep, true);
+        a.colors_precomp = fptr(colors, keep);
+        a.opacities = fptr(opacities, keep);
+        a.scales = fptr(scales, keep);
+        a.scale_modifier = scale_modifier;
+        a.rotations = fptr(rotations, keep, true);
+        a.cov3D_precomp = fptr(cov3D_precomp, keep);
+        a.viewmatrix = fptr(viewmatrix, keep);
+        a.projmatrix = fptr(projmatrix, keep);
+        a.cam_pos = fptr(campos, keep);
+        a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy;
+        torch::Tensor radii_c = radii.contiguous();
+        a.radii = radii_c.data_ptr<int>();
+        torch::Tensor gb = geomBuffer.contiguous(), bb = binningBuffer.contiguous(), ib = imageBuffer.contiguous();
+        a.geom_buffer = reinterpret_cast<char*>(gb.data_ptr());
+        a.binning_buffer = reinterpret_cast<char*>(bb.data_ptr());
+        a.image_buffer = reinterpret_cast<char*>(ib.data_ptr());
+        a.dL_dpix = fptr(dL_dout_color, keep);
+        a.dL_dinvdepth_pix = has_depth ? fptr(dL_dout_invdepth, keep) : nullptr;
+        a.dL_dmean2D = dL_dmeans2D.data_ptr<float>();
+        a.dL_dconic = dL_dconic.data_ptr<float>();
+        a.dL_dopacity = dL_dopacity.data_ptr<float>();
+        a.dL_dcolor = dL_dcolors.data_ptr<float>();
+        a.dL_dinvdepth = has_depth ? dL_dinvdepths.data_ptr<float>() : nullptr;
+        a.dL_dmean3D = dL_dmeans3D.data_ptr<float>();
+        a.dL_dcov3D = dL_dcov3D.data_ptr<float>();
+        a.dL_dsh = M > 0 ? dL_dsh.data_ptr<float>() : nullptr;
+        a.dL_dscale = has_scales ? dL_dscales.data_ptr<float>() : nullptr;
+        a.dL_drot = has_scales ? dL_drotations.data_ptr<float>() : nullptr;
+        a.antialiasing = antialiasing; a.debug = debug;
+        check(gsr_backward(&a, stream));
+    }
+    return std::make_tuple(dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations);
+}
+
+torch::Tensor markVisible(torch::Tensor& means3D, torch::Tensor& viewmatrix, torch::Tensor& projmatrix) {
+    TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (there is no CPU fallback)");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    const int P = means3D.size(0);
+    torch::Tensor present = torch::full({P}, false, means3D.options().dtype(at::kBool));
+    if (P != 0) {
+        std::vector<torch::Tensor> keep;
+        check(gsr_mark_visible(P, fptr(means3D, keep), fptr(viewmatrix, keep), fptr(projmatrix, keep),
+                               reinterpret_cast<unsigned char*>(present.data_ptr<bool>()), at::cuda::getCurrentCUDAStream()));
+    }
+    return present;
+}
+
+PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+    m.def("rasterize_gaussians", &RasterizeGaussiansCUDA);
+    m.def("rasterize_gaussians_backward", &RasterizeGaussiansBackwardCUDA);
+    m.def("mark_visible", &markVisible);
+    // the fork's spellings (DGR/ext.cpp:16, rasterize_points.h:18,41)
+    m.def("rasterize_gaussians_npu", &RasterizeGaussiansCUDA);
+    m.def("rasterize_gaussians_backward_npu", &RasterizeGaussiansBackwardCUDA);
+    m.attr("backend") = "gsr_b200 sm_100a";
+}

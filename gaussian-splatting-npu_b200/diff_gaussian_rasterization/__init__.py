@@ -1,0 +1,120 @@
+"""Drop-in `diff_gaussian_rasterization` package backed by the B200-native rasterizer.
+
+Public surface (names, argument order, return tuples, error text) is the reference's
+/root/reference/diff-gaussian-rasterization-npu/diff_gaussian_rasterization/__init__.py:
+  GaussianRasterizationSettings (:143-156), GaussianRasterizer (:158-207),
+  rasterize_gaussians (:21-42), _RasterizeGaussians (:44-141)
+so `gaussian_renderer/__init__.py` and `train.py` of the reference run on it unchanged.
+`SparseGaussianAdam` is deliberately NOT exported (train.py:37-41 then keeps separate_sh off).
+
+The compute path is the in-tree torch extension `_C` (csrc/torch_binding.cpp) over the C ABI of
+libgsr_b200.so (include/gsr.h).  There is no CPU or PyTorch fallback: if the extension is missing
+the import fails loudly.
+"""
+from typing import NamedTuple
+
+import torch
+import torch.nn as nn
+
+try:
+    from . import _C
+except ImportError as exc:  # pragma: no cover - exercised only on a broken build
+    raise ImportError(
+        "diff_gaussian_rasterization._C (the sm_100a CUDA extension) is not built or cannot be "
+        "loaded; run `python gaussian-splatting-npu_b200/build.py`. There is no fallback path."
+    ) from exc
+
+__all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians"]
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    """Per-call camera / image configuration.  Field order is part of the API (reference :143-156)."""
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+    antialiasing: bool
+
+
+def _camera_args(rs):
+    return (rs.scale_modifier,), (rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy)
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    """autograd bridge: 9 inputs -> (color[3,H,W], radii[P] int32, invdepth[1,H,W])  (reference :44-141)."""
+
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                cov3Ds_precomp, raster_settings):
+        rs = raster_settings
+        (mod,), cam = _camera_args(rs)
+        # argument order of RasterizeGaussiansCUDA (rasterize_points.h:18-39)
+        out = _C.rasterize_gaussians(
+            rs.bg, means3D, colors_precomp, opacities, scales, rotations, mod, cov3Ds_precomp,
+            *cam, rs.image_height, rs.image_width, sh, rs.sh_degree, rs.campos,
+            rs.prefiltered, rs.antialiasing, rs.debug)
+        num_rendered, color, radii, geom_buf, binning_buf, img_buf, invdepths = out
+        ctx.raster_settings = rs
+        ctx.num_rendered = num_rendered
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh,
+                              opacities, geom_buf, binning_buf, img_buf)
+        return color, radii, invdepths
+
+    @staticmethod
+    def backward(ctx, grad_out_color, _grad_radii, grad_out_depth):
+        rs = ctx.raster_settings
+        (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities,
+         geom_buf, binning_buf, img_buf) = ctx.saved_tensors
+        (mod,), cam = _camera_args(rs)
+        # argument order of RasterizeGaussiansBackwardCUDA (rasterize_points.cu:126-151)
+        (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp,
+         grad_sh, grad_scales, grad_rotations) = _C.rasterize_gaussians_backward(
+            rs.bg, means3D, radii, colors_precomp, opacities, scales, rotations, mod, cov3Ds_precomp,
+            *cam, grad_out_color, grad_out_depth, sh, rs.sh_degree, rs.campos, geom_buf,
+            ctx.num_rendered, binning_buf, img_buf, rs.antialiasing, rs.debug)
+        # one gradient per forward input, in input order; raster_settings gets None
+        return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities,
+                grad_scales, grad_rotations, grad_cov3Ds_precomp, None)
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                        cov3Ds_precomp, raster_settings):
+    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales,
+                                     rotations, cov3Ds_precomp, raster_settings)
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        """bool[P]: which points pass the near-plane frustum test of this camera (reference :163-172)."""
+        rs = self.raster_settings
+        with torch.no_grad():
+            return _C.mark_visible(positions, rs.viewmatrix, rs.projmatrix)
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None,
+                rotations=None, cov3D_precomp=None):
+        have_sh, have_col = shs is not None, colors_precomp is not None
+        if have_sh == have_col:
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        have_sr = scales is not None or rotations is not None
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+                (have_sr and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+
+        def or_empty(t):
+            return torch.Tensor([]) if t is None else t
+
+        return rasterize_gaussians(means3D, means2D, or_empty(shs), or_empty(colors_precomp),
+                                   opacities, or_empty(scales), or_empty(rotations),
+                                   or_empty(cov3D_precomp), self.raster_settings)

@@ -1,0 +1,257 @@
+"""ctypes binding of the C ABI (include/gsr.h, libgsr_b200.so) on torch CUDA tensors.
+
+This is the path the `-m gpu` parity tests and bench.py's device-timed leg call: Python only owns
+device memory (torch tensors) and streams; every kernel is in libgsr_b200.so.  It also decodes the
+opaque scratch buffers with gsr_get_*_layout so that tests can compare every intermediate
+(depths, records, tiles_touched, offsets, sorted keys, point list, ranges, final_T, n_contrib).
+No fallback: a missing library raises.
+"""
+import ctypes
+import os
+from ctypes import (CFUNCTYPE, POINTER, Structure, c_char_p, c_float, c_int, c_size_t, c_ubyte,
+                    c_uint32, c_uint64, c_void_p)
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgsr_b200.so")
+
+ALLOC_FN = CFUNCTYPE(c_void_p, c_size_t, c_void_p)
+
+
+class ForwardArgs(Structure):
+    _fields_ = [("P", c_int), ("D", c_int), ("M", c_int), ("width", c_int), ("height", c_int),
+                ("background", c_void_p), ("means3D", c_void_p), ("shs", c_void_p),
+                ("colors_precomp", c_void_p), ("opacities", c_void_p), ("scales", c_void_p),
+                ("scale_modifier", c_float), ("rotations", c_void_p), ("cov3D_precomp", c_void_p),
+                ("viewmatrix", c_void_p), ("projmatrix", c_void_p), ("cam_pos", c_void_p),
+                ("tan_fovx", c_float), ("tan_fovy", c_float), ("prefiltered", c_int),
+                ("antialiasing", c_int), ("debug", c_int), ("out_color", c_void_p),
+                ("out_invdepth", c_void_p), ("radii", c_void_p)]
+
+
+class BackwardArgs(Structure):
+    _fields_ = [("P", c_int), ("D", c_int), ("M", c_int), ("R", c_int), ("width", c_int), ("height", c_int),
+                ("background", c_void_p), ("means3D", c_void_p), ("shs", c_void_p),
+                ("colors_precomp", c_void_p), ("opacities", c_void_p), ("scales", c_void_p),
+                ("scale_modifier", c_float), ("rotations", c_void_p), ("cov3D_precomp", c_void_p),
+                ("viewmatrix", c_void_p), ("projmatrix", c_void_p), ("cam_pos", c_void_p),
+                ("tan_fovx", c_float), ("tan_fovy", c_float), ("radii", c_void_p),
+                ("geom_buffer", c_void_p), ("binning_buffer", c_void_p), ("image_buffer", c_void_p),
+                ("dL_dpix", c_void_p), ("dL_dinvdepth_pix", c_void_p), ("dL_dmean2D", c_void_p),
+                ("dL_dconic", c_void_p), ("dL_dopacity", c_void_p), ("dL_dcolor", c_void_p),
+                ("dL_dinvdepth", c_void_p), ("dL_dmean3D", c_void_p), ("dL_dcov3D", c_void_p),
+                ("dL_dsh", c_void_p), ("dL_dscale", c_void_p), ("dL_drot", c_void_p),
+                ("antialiasing", c_int), ("debug", c_int)]
+
+
+class GeometryLayout(Structure):
+    _fields_ = [(n, c_size_t) for n in ("depths", "records", "cov3D", "clamped", "tiles_touched",
+                                        "point_offsets", "total")]
+
+
+class BinningLayout(Structure):
+    _fields_ = [(n, c_size_t) for n in ("keys_unsorted", "values_unsorted", "keys", "point_list",
+                                        "sort_temp", "total")]
+
+
+class ImageLayout(Structure):
+    _fields_ = [(n, c_size_t) for n in ("final_T", "n_contrib", "ranges", "total")]
+
+
+EXPORTS = ["gsr_forward", "gsr_backward", "gsr_mark_visible", "gsr_geometry_bytes", "gsr_image_bytes",
+           "gsr_binning_bytes", "gsr_sort_temp_bytes", "gsr_sort_pairs", "gsr_get_geometry_layout",
+           "gsr_get_binning_layout", "gsr_get_image_layout", "gsr_set_profiling", "gsr_last_stage_ms",
+           "gsr_last_error", "gsr_version"]
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("libgsr_b200.so is not built (python gaussian-splatting-npu_b200/build.py); "
+                               "there is no fallback path")
+        L = ctypes.CDLL(LIB_PATH)
+        L.gsr_forward.restype = c_int
+        L.gsr_forward.argtypes = [POINTER(ForwardArgs), ALLOC_FN, c_void_p, ALLOC_FN, c_void_p, ALLOC_FN,
+                                  c_void_p, c_void_p, POINTER(c_int)]
+        L.gsr_backward.restype = c_int
+        L.gsr_backward.argtypes = [POINTER(BackwardArgs), c_void_p]
+        L.gsr_mark_visible.restype = c_int
+        L.gsr_mark_visible.argtypes = [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]
+        for n in ("gsr_geometry_bytes",):
+            getattr(L, n).restype = c_size_t
+            getattr(L, n).argtypes = [c_int]
+        L.gsr_image_bytes.restype = c_size_t
+        L.gsr_image_bytes.argtypes = [c_int, c_int]
+        L.gsr_binning_bytes.restype = c_size_t
+        L.gsr_binning_bytes.argtypes = [c_size_t, c_int, c_int]
+        L.gsr_sort_temp_bytes.restype = c_size_t
+        L.gsr_sort_temp_bytes.argtypes = [c_size_t]
+        L.gsr_sort_pairs.restype = c_int
+        L.gsr_sort_pairs.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_void_p, c_void_p]
+        L.gsr_get_geometry_layout.argtypes = [c_int, POINTER(GeometryLayout)]
+        L.gsr_get_binning_layout.argtypes = [c_size_t, c_int, c_int, POINTER(BinningLayout)]
+        L.gsr_get_image_layout.argtypes = [c_int, c_int, POINTER(ImageLayout)]
+        L.gsr_set_profiling.argtypes = [c_int]
+        L.gsr_last_stage_ms.restype = c_float
+        L.gsr_last_stage_ms.argtypes = [c_int]
+        L.gsr_last_error.restype = c_char_p
+        L.gsr_version.restype = c_char_p
+        _lib = L
+    return _lib
+
+
+def last_error():
+    return lib().gsr_last_error().decode()
+
+
+def _check(status):
+    if status != 0:
+        raise RuntimeError("gsr error %d: %s" % (status, last_error()))
+
+
+def _ptr(t):
+    if t is None or t.numel() == 0:
+        return None
+    assert t.is_cuda and t.is_contiguous()
+    return c_void_p(t.data_ptr())
+
+
+def _stream():
+    return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class _Buf:
+    """One growable scratch tensor + the C callback that (re)allocates it."""
+
+    def __init__(self, device):
+        self.t = torch.empty(0, dtype=torch.uint8, device=device)
+        self.device = device
+
+        def cb(nbytes, _user):
+            self.t = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+            return self.t.data_ptr()
+        self.cb = ALLOC_FN(cb)
+
+
+STAGES = ["preprocess", "scan", "duplicate", "sort", "ranges", "render_fwd", "render_bwd",
+          "preprocess_bwd", "host_sync"]
+
+
+def stage_times_ms():
+    L = lib()
+    return {n: float(L.gsr_last_stage_ms(i)) for i, n in enumerate(STAGES)}
+
+
+def set_profiling(on):
+    lib().gsr_set_profiling(1 if on else 0)
+
+
+def forward(*, means3D, opacities, viewmatrix, projmatrix, cam_pos, background, width, height,
+            tan_fovx, tan_fovy, shs=None, colors_precomp=None, scales=None, rotations=None,
+            cov3D_precomp=None, sh_degree=3, scale_modifier=1.0, prefiltered=False,
+            antialiasing=False, debug=False, want_invdepth=True):
+    """gsr_forward on torch CUDA tensors.  Returns a state dict holding outputs + scratch buffers."""
+    L = lib()
+    dev = means3D.device
+    P = means3D.shape[0]
+    out_color = torch.empty(3, height, width, dtype=torch.float32, device=dev)
+    out_invdepth = torch.empty(1, height, width, dtype=torch.float32, device=dev) if want_invdepth else None
+    radii = torch.empty(P, dtype=torch.int32, device=dev)
+    M = 0 if shs is None else shs.shape[1]
+    a = ForwardArgs(P, sh_degree, M, width, height, _ptr(background), _ptr(means3D), _ptr(shs),
+                    _ptr(colors_precomp), _ptr(opacities), _ptr(scales), scale_modifier, _ptr(rotations),
+                    _ptr(cov3D_precomp), _ptr(viewmatrix), _ptr(projmatrix), _ptr(cam_pos), tan_fovx, tan_fovy,
+                    int(prefiltered), int(antialiasing), int(debug), _ptr(out_color), _ptr(out_invdepth), _ptr(radii))
+    geom, binning, img = _Buf(dev), _Buf(dev), _Buf(dev)
+    n = c_int(0)
+    with torch.cuda.device(dev):
+        _check(L.gsr_forward(ctypes.byref(a), geom.cb, None, binning.cb, None, img.cb, None, _stream(), ctypes.byref(n)))
+    return dict(num_rendered=n.value, out_color=out_color, out_invdepth=out_invdepth, radii=radii,
+                geom=geom.t, binning=binning.t, img=img.t, P=P, W=width, H=height, M=M)
+
+
+def backward(state, *, dL_dcolor, dL_dinvdepth=None, means3D, opacities, viewmatrix, projmatrix, cam_pos,
+             background, tan_fovx, tan_fovy, shs=None, colors_precomp=None, scales=None, rotations=None,
+             cov3D_precomp=None, sh_degree=3, scale_modifier=1.0, antialiasing=False, debug=False):
+    L = lib()
+    dev = means3D.device
+    P, W, H, M = state["P"], state["W"], state["H"], state["M"]
+    e = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)
+    g = dict(dL_dmeans2D=e(P, 3), dL_dconic=e(P, 2, 2), dL_dopacity=e(P, 1), dL_dcolors=e(P, 3),
+             dL_dinvdepths=e(P, 1) if dL_dinvdepth is not None else None, dL_dmeans3D=e(P, 3), dL_dcov3D=e(P, 6),
+             dL_dsh=e(P, M, 3) if M else None, dL_dscales=e(P, 3) if scales is not None else None,
+             dL_drotations=e(P, 4) if scales is not None else None)
+    a = BackwardArgs(P, sh_degree, M, state["num_rendered"], W, H, _ptr(background), _ptr(means3D), _ptr(shs),
+                     _ptr(colors_precomp), _ptr(opacities), _ptr(scales), scale_modifier, _ptr(rotations),
+                     _ptr(cov3D_precomp), _ptr(viewmatrix), _ptr(projmatrix), _ptr(cam_pos), tan_fovx, tan_fovy,
+                     _ptr(state["radii"]), _ptr(state["geom"]), _ptr(state["binning"]), _ptr(state["img"]),
+                     _ptr(dL_dcolor), _ptr(dL_dinvdepth), _ptr(g["dL_dmeans2D"]), _ptr(g["dL_dconic"]),
+                     _ptr(g["dL_dopacity"]), _ptr(g["dL_dcolors"]), _ptr(g["dL_dinvdepths"]), _ptr(g["dL_dmeans3D"]),
+                     _ptr(g["dL_dcov3D"]), _ptr(g["dL_dsh"]), _ptr(g["dL_dscales"]), _ptr(g["dL_drotations"]),
+                     int(antialiasing), int(debug))
+    with torch.cuda.device(dev):
+        _check(L.gsr_backward(ctypes.byref(a), _stream()))
+    return g
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    P = means3D.shape[0]
+    out = torch.zeros(P, dtype=torch.bool, device=means3D.device)
+    _check(lib().gsr_mark_visible(P, _ptr(means3D), _ptr(viewmatrix), _ptr(projmatrix), c_void_p(out.data_ptr()), _stream()))
+    return out
+
+
+def _aligned(t):
+    off = (-t.data_ptr()) % 256
+    return t[off:]
+
+
+def _view(buf, offset, count, dtype):
+    esize = torch.empty(0, dtype=dtype).element_size()
+    return _aligned(buf)[offset:offset + count * esize].view(dtype)
+
+
+def introspect(state):
+    """Decode the scratch buffers of a forward `state` into named torch views."""
+    L = lib()
+    P, W, H, N = state["P"], state["W"], state["H"], state["num_rendered"]
+    gl, bl, il = GeometryLayout(), BinningLayout(), ImageLayout()
+    L.gsr_get_geometry_layout(P, ctypes.byref(gl))
+    L.gsr_get_binning_layout(N, W, H, ctypes.byref(bl))
+    L.gsr_get_image_layout(W, H, ctypes.byref(il))
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    rec = _view(state["geom"], gl.records, P * 12, torch.float32).view(P, 12)
+    clamp = _view(state["geom"], gl.clamped, P, torch.uint8)
+    o = dict(
+        depths=_view(state["geom"], gl.depths, P, torch.float32),
+        means2D=rec[:, 0:2], conic_opacity=rec[:, 2:6], rgb=rec[:, 6:9], invdepth_g=rec[:, 9],
+        cov3D=_view(state["geom"], gl.cov3D, P * 6, torch.float32).view(P, 6),
+        clamped=torch.stack([(clamp >> c) & 1 for c in range(3)], dim=1),
+        tiles_touched=_view(state["geom"], gl.tiles_touched, P, torch.int32),
+        point_offsets=_view(state["geom"], gl.point_offsets, P, torch.int32),
+        final_T=_view(state["img"], il.final_T, H * W, torch.float32).view(H, W),
+        n_contrib=_view(state["img"], il.n_contrib, H * W, torch.int32).view(H, W),
+        ranges=_view(state["img"], il.ranges, T * 2, torch.int32).view(T, 2),
+    )
+    if N:
+        o["keys"] = _view(state["binning"], bl.keys, N, torch.int64)
+        o["point_list"] = _view(state["binning"], bl.point_list, N, torch.int32)
+    else:
+        o["keys"] = torch.empty(0, dtype=torch.int64, device=state["geom"].device)
+        o["point_list"] = torch.empty(0, dtype=torch.int32, device=state["geom"].device)
+    return o
+
+
+def sort_pairs(keys, values, end_bit):
+    """gsr_sort_pairs on int64 keys / int32 values (bit patterns of u64 / u32). Inputs are clobbered."""
+    L = lib()
+    n = keys.numel()
+    ko, vo = torch.empty_like(keys), torch.empty_like(values)
+    temp = torch.empty(int(L.gsr_sort_temp_bytes(n)), dtype=torch.uint8, device=keys.device)
+    _check(L.gsr_sort_pairs(_ptr(keys) if n else None, _ptr(values) if n else None, c_void_p(ko.data_ptr()) if n else None,
+                            c_void_p(vo.data_ptr()) if n else None, n, end_bit, c_void_p(temp.data_ptr()), _stream()))
+    return ko, vo

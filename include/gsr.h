@@ -1,0 +1,195 @@
+/*
+ * gsr.h -- C ABI of the B200-native differentiable Gaussian-splatting rasterizer (libgsr_b200.so).
+ *
+ * This is the drop-in boundary.  Every entry point replaces one static method of the reference's
+ * torch-free core class CudaRasterizer::Rasterizer
+ * (/root/reference/diff-gaussian-rasterization-npu/cuda_rasterizer/rasterizer.h:24-90), with the
+ * same argument meaning, so the reference's binding layer (rasterize_points.cu) can call it
+ * unchanged in spirit: plain pointers and sizes, no torch types, no C++ types, no exceptions.
+ *
+ * Conventions
+ *   - all pointers are DEVICE pointers on the current CUDA device unless the name says host;
+ *   - all floats are IEEE fp32, all arrays contiguous, layouts as in the reference
+ *     (means3D[P,3], scales[P,3], rotations[P,4] (w,x,y,z), opacities[P], shs[P,M,3],
+ *      viewmatrix/projmatrix[16] with memory index m[4*col+row], out_color[3,H,W] planar);
+ *   - a NULL pointer selects the same code path an empty tensor selects in the reference
+ *     (shs==NULL <-> colors_precomp path, scales==NULL <-> cov3D_precomp path,
+ *      dL_dout_invdepth==NULL <-> no inverse-depth gradient);
+ *   - every function returns GSR_OK (0) or a negative error code and never throws;
+ *     gsr_last_error() returns the calling thread's last message;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream, which is what the
+ *     reference launches on).  Entry points are re-entrant and keep no global mutable state.
+ */
+#ifndef GSR_H_INCLUDED
+#define GSR_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSR_OK 0
+#define GSR_ERR_INVALID (-1)   /* bad argument (reference: AT_ERROR / std::runtime_error) */
+#define GSR_ERR_CUDA (-2)      /* a CUDA call failed (reference: CHECK_CUDA, auxiliary.h:178-185) */
+#define GSR_ERR_PREFILTERED (-3) /* a Gaussian was culled although prefiltered=1 (reference: __trap, auxiliary.h:168-172) */
+#define GSR_ERR_ALLOC (-4)     /* an allocator callback returned NULL */
+
+/*
+ * Scratch allocator callback: must return a device buffer of at least `bytes` bytes that stays
+ * valid until the matching gsr_backward has run.  Replaces std::function<char*(size_t)>
+ * (rasterizer.h:36-38; the reference's binding resizes a torch byte tensor, rasterize_points.cu:27-33).
+ */
+typedef char* (*gsr_alloc_fn)(size_t bytes, void* user);
+
+/* Arguments of Rasterizer::forward, rasterizer.h:35-61. */
+typedef struct gsr_forward_args {
+    int P;                       /* number of Gaussians */
+    int D;                       /* active SH degree (0..3) */
+    int M;                       /* SH coefficients per Gaussian in `shs` (0 if shs==NULL) */
+    int width, height;
+    const float* background;     /* [3] */
+    const float* means3D;        /* [P,3] */
+    const float* shs;            /* [P,M,3] or NULL */
+    const float* colors_precomp; /* [P,3] or NULL */
+    const float* opacities;      /* [P] */
+    const float* scales;         /* [P,3] or NULL */
+    float scale_modifier;
+    const float* rotations;      /* [P,4] or NULL */
+    const float* cov3D_precomp;  /* [P,6] or NULL */
+    const float* viewmatrix;     /* [16] */
+    const float* projmatrix;     /* [16] */
+    const float* cam_pos;        /* [3] */
+    float tan_fovx, tan_fovy;
+    int prefiltered;
+    int antialiasing;
+    int debug;                   /* 1: synchronise + check after every stage (CHECK_CUDA) */
+    float* out_color;            /* [3,H,W], fully written */
+    float* out_invdepth;         /* [1,H,W] or NULL, fully written */
+    int* radii;                  /* [P], fully written */
+} gsr_forward_args;
+
+/* Arguments of Rasterizer::backward, rasterizer.h:63-89. */
+typedef struct gsr_backward_args {
+    int P, D, M;
+    int R;                       /* num_rendered returned by the matching forward */
+    int width, height;
+    const float* background;
+    const float* means3D;
+    const float* shs;
+    const float* colors_precomp;
+    const float* opacities;
+    const float* scales;
+    float scale_modifier;
+    const float* rotations;
+    const float* cov3D_precomp;
+    const float* viewmatrix;
+    const float* projmatrix;
+    const float* cam_pos;
+    float tan_fovx, tan_fovy;
+    const int* radii;            /* [P] from forward */
+    char* geom_buffer;           /* the three scratch buffers the forward filled */
+    char* binning_buffer;
+    char* image_buffer;
+    const float* dL_dpix;        /* [3,H,W] */
+    const float* dL_dinvdepth_pix; /* [1,H,W] or NULL */
+    /* Outputs.  All are FULLY written by gsr_backward (rows of invisible Gaussians get zeros), so
+     * the caller may pass uninitialised memory; the reference needed ten torch::zeros
+     * (rasterize_points.cu:163-172). */
+    float* dL_dmean2D;           /* [P,3]  (.x,.y written, .z = 0) */
+    float* dL_dconic;            /* [P,4]  (.x,.y,.w written, .z = 0) */
+    float* dL_dopacity;          /* [P] */
+    float* dL_dcolor;            /* [P,3] */
+    float* dL_dinvdepth;         /* [P] or NULL (required iff dL_dinvdepth_pix != NULL) */
+    float* dL_dmean3D;           /* [P,3] */
+    float* dL_dcov3D;            /* [P,6] */
+    float* dL_dsh;               /* [P,M,3] or NULL when M==0 */
+    float* dL_dscale;            /* [P,3] or NULL when scales==NULL */
+    float* dL_drot;              /* [P,4] or NULL when rotations==NULL */
+    int antialiasing;
+    int debug;
+} gsr_backward_args;
+
+/*
+ * Rasterizer::forward (rasterizer.h:35, rasterizer_impl.cu:198-341).  Calls the three allocators
+ * (geometry, binning, image -- in that order, binning after the instance count is known), runs
+ * preprocess -> scan -> duplicateWithKeys -> radix sort -> tile ranges -> blend on `stream`, and
+ * stores the number of rendered (Gaussian,tile) instances in *num_rendered (host int).  It
+ * synchronises `stream` once (the reference's blocking cudaMemcpy, rasterizer_impl.cu:284).
+ */
+int gsr_forward(const gsr_forward_args* args,
+                gsr_alloc_fn geom_alloc, void* geom_user,
+                gsr_alloc_fn binning_alloc, void* binning_user,
+                gsr_alloc_fn image_alloc, void* image_user,
+                void* stream, int* num_rendered);
+
+/* Rasterizer::backward (rasterizer.h:63, rasterizer_impl.cu:345-450).  Asynchronous on `stream`. */
+int gsr_backward(const gsr_backward_args* args, void* stream);
+
+/* Rasterizer::markVisible (rasterizer.h:28-33, rasterizer_impl.cu:141-153). present is bool[P] (1 byte each). */
+int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     unsigned char* present, void* stream);
+
+/* Scratch sizes (reference: required<GeometryState>(P) etc., rasterizer_impl.h:66-72). */
+size_t gsr_geometry_bytes(int P);
+size_t gsr_image_bytes(int width, int height);
+size_t gsr_binning_bytes(size_t num_rendered, int width, int height);
+
+/*
+ * Stable LSD radix sort of n (u64 key, u32 value) pairs on key bits [0, end_bit): the hand-written
+ * onesweep that replaces cub::DeviceRadixSort::SortPairs (rasterizer_impl.cu:306-311).  `temp` must
+ * hold gsr_sort_temp_bytes(n) bytes.  keys_in/vals_in are clobbered (ping-pong); the result is in
+ * keys_out/vals_out.  Exposed so the sort can be tested and timed alone.
+ */
+size_t gsr_sort_temp_bytes(size_t n);
+int gsr_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                   size_t n, int end_bit, char* temp, void* stream);
+
+/*
+ * Introspection of the opaque scratch buffers for the parity tests (the reference's tests would
+ * use GeometryState/BinningState/ImageState::fromChunk, rasterizer_impl.h:29-65).  Fills byte
+ * offsets of each sub-array relative to the buffer base.
+ */
+typedef struct gsr_geometry_layout {
+    size_t depths;        /* f32[P] */
+    size_t records;       /* f32[P,12]: x,y,conic.a,conic.b | conic.c,opacity,r,g | b,1/depth,0,0 */
+    size_t cov3D;         /* f32[P,6] */
+    size_t clamped;       /* u8[P]: bit c set <=> colour channel c was clamped */
+    size_t tiles_touched; /* u32[P] */
+    size_t point_offsets; /* u32[P] inclusive scan */
+    size_t total;
+} gsr_geometry_layout;
+typedef struct gsr_binning_layout {
+    size_t keys_unsorted; /* u64[N] ping-pong partner of `keys`   (scratch after the sort) */
+    size_t values_unsorted; /* u32[N] ping-pong partner of `point_list` (scratch after the sort) */
+    size_t keys;          /* u64[N] sorted */
+    size_t point_list;    /* u32[N] sorted values */
+    size_t sort_temp;
+    size_t total;
+} gsr_binning_layout;
+typedef struct gsr_image_layout {
+    size_t final_T;       /* f32[H*W] */
+    size_t n_contrib;     /* u32[H*W] */
+    size_t ranges;        /* u32[T,2] */
+    size_t total;
+} gsr_image_layout;
+void gsr_get_geometry_layout(int P, gsr_geometry_layout* out);
+void gsr_get_binning_layout(size_t num_rendered, int width, int height, gsr_binning_layout* out);
+void gsr_get_image_layout(int width, int height, gsr_image_layout* out);
+
+/* Per-stage device times of the calling thread's last gsr_forward/gsr_backward when profiling is
+ * enabled with gsr_set_profiling(1) (adds event records + one extra sync; off by default).
+ * Stage ids: 0 preprocess, 1 scan, 2 duplicate, 3 sort, 4 ranges, 5 render_fwd,
+ *            6 render_bwd, 7 preprocess_bwd, 8 host round trip for num_rendered.
+ * Returns milliseconds or -1. */
+void gsr_set_profiling(int enabled);
+float gsr_last_stage_ms(int stage);
+
+const char* gsr_last_error(void);
+const char* gsr_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSR_H_INCLUDED */
