@@ -1,0 +1,392 @@
+#!/usr/bin/env python
+"""bench.py -- fwd+bwd renders/s of the differentiable Gaussian-splatting rasterizer.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c2|c1|c3|c4]
+
+Workload at N=1 is BASELINE.json configs[1] ("c2"): 3M SH-3 Gaussians, one 1920x1080 view, forward
++ backward.  One "step" = one view's forward + backward (+ the NCCL gradient all-reduce when N>1:
+every rank renders its own camera of the same replicated scene, weak scaling, views/s aggregate).
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for what each key means.
+
+  value        device-timed (CUDA events around the K steps) through the C ABI, inputs resident in HBM
+  e2e          the same step through the public Python API (diff_gaussian_rasterization autograd
+               Function) with the per-step inputs (camera + target image) copied from pinned host
+               memory and the loss read back to the host inside the timed region
+  roofline     the dominant kernel (backward blend, FP32-pipe bound) + roofline_stages for every stage
+  cpu_baseline the CPU oracle (a port of the reference algorithm) on the same workload, host threads
+  --impl reference : the reference algorithm's CPU implementation (the oracle port) timed alone.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "gaussian-splatting-npu_b200")
+for _p in (ROOT, PKG, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+from gsr_b200 import synth  # noqa: E402
+
+WORKLOADS = {
+    # name: (P, W, H, seed, s0, antialiasing, n_cams)
+    "c1": dict(P=100_000, W=800, H=800, seed=1001, kind="random_init", aa=False,
+               desc="nerf_synthetic lego camera 800x800, 100K random-init SH3 Gaussians"),
+    "c2": dict(P=3_000_000, W=1920, H=1080, seed=2002, s0=0.004, kind="trained", aa=False,
+               desc="Mip-NeRF360-shape: 3M SH3 Gaussians, single view 1920x1080"),
+    "c3": dict(P=1_800_000, W=979, H=546, seed=3003, s0=0.006, kind="trained", aa=False, extent=1.5,
+               desc="T&T-shape: 1.8M SH3 Gaussians, 979x546"),
+    "c4": dict(P=6_000_000, W=3840, H=2160, seed=4004, s0=0.004, kind="trained", aa=True,
+               desc="6M SH3 Gaussians at 3840x2160, antialiasing + inverse depth"),
+}
+
+FP32_LANES = 148 * 128 * 2     # FMA lanes x 2 flop
+
+
+def make_workload(name, cam_index=0):
+    w = WORKLOADS[name]
+    if w["kind"] == "random_init":
+        scene = synth.random_init_scene(w["P"], w["seed"])
+        import cases
+        cam = cases._lego_cam(1, w["W"], w["H"])
+    else:
+        scene = synth.trained_like_scene(w["P"], w["seed"], s0=w["s0"], extent=w.get("extent", 1.0))
+        cam = synth.orbit_cameras(8, w["W"], w["H"], w["seed"])[cam_index % 8]
+    return w, scene, cam
+
+
+def oracle_step(scene, cam, w, grads):
+    """One fwd+bwd of the CPU oracle; returns (seconds, forward dict)."""
+    from oracle import gs_oracle as go
+    S = go.Scene(W=cam.image_width, H=cam.image_height, means3D=scene["means3D"], opacities=scene["opacities"],
+                 viewmatrix=cam.world_view_transform, projmatrix=cam.full_proj_transform, cam_pos=cam.camera_center,
+                 tan_fovx=cam.tanfovx, tan_fovy=cam.tanfovy, background=np.zeros(3, np.float32), shs=scene["shs"],
+                 scales=scene["scales"], rotations=scene["rotations"], sh_degree=scene["sh_degree"],
+                 antialiasing=w["aa"])
+    t0 = time.perf_counter()
+    f = go.forward(S, borderline=False)
+    go.backward(S, f, grads[0], grads[1])
+    return time.perf_counter() - t0, f
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            for k, nme in enumerate(names):
+                if len(r) > 4 + k and r[4 + k].lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def run_reference(args):
+    """--impl reference: the reference algorithm's CPU implementation (oracle port), all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import gs_oracle as go
+    w, scene, cam = make_workload(args.workload)
+    grads = synth.upstream_grads(w["H"], w["W"], 5)
+    for _ in range(args.warmup):
+        oracle_step(scene, cam, w, grads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        oracle_step(scene, cam, w, grads)
+    dt = time.perf_counter() - t0
+    val = args.steps / dt
+    cores = go.num_threads()
+    sample = "full workload: one %dx%d view of %d Gaussians, fwd+bwd per step" % (w["W"], w["H"], w["P"])
+    print(json.dumps({
+        "impl": "reference", "metric": "fwd+bwd renders/s", "value": val, "unit": "renders/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000 * dt / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload + ": " + w["desc"]},
+        "cpu_baseline": {"value": val, "unit": "renders/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "renders/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--workload", default="c2")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-ref-cuda", action="store_true")
+    ap.add_argument("--views-per-rank", type=int, default=1)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    from gsr_b200 import capi
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    w, scene, cam = make_workload(args.workload, cam_index=rank)
+    W, H, P = w["W"], w["H"], w["P"]
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    # replicated Gaussians, resident in HBM; parameters live in one flat [P,59] gradient-bucket layout
+    from gsr_b200.dist import FlatGaussians
+    G = FlatGaussians.from_numpy(scene, dev)
+    bg = torch.zeros(3, device=dev)
+    view, proj, campos = t(cam.world_view_transform), t(cam.full_proj_transform), t(cam.camera_center)
+    dcol_np, ddep_np = synth.upstream_grads(H, W, 5)
+    dcol, ddep = t(dcol_np), t(ddep_np)
+    common = dict(means3D=G.xyz, opacities=G.opacity, viewmatrix=view, projmatrix=proj, cam_pos=campos, background=bg,
+                  tan_fovx=cam.tanfovx, tan_fovy=cam.tanfovy, shs=G.shs, scales=G.scales, rotations=G.rotations,
+                  sh_degree=3, antialiasing=w["aa"])
+
+    grad_views = G.grad_views()     # the backward kernels write straight into the all-reduce bucket
+
+    def abi_step():
+        st = capi.forward(width=W, height=H, **common)
+        g = capi.backward(st, dL_dcolor=dcol, dL_dinvdepth=ddep, out=grad_views, **common)
+        return st, g
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---------------- device-timed leg (C ABI, inputs resident) ----------------
+    sampler = ClockSampler(local_rank)
+    sampler.start()          # nvidia-smi's own start-up must be over before the timed region begins
+    time.sleep(1.0)
+    for _ in range(max(args.warmup, 3)):
+        st, g = abi_step()
+        if world > 1:
+            G.allreduce_from(g)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        st, g = abi_step()
+        if world > 1:
+            G.allreduce_from(g)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    if world > 1:
+        tms = torch.tensor([ms], device=dev)
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        ms = float(tms.item())
+    value = world * args.steps / (ms / 1000.0)
+    N = st["num_rendered"]
+
+    # ---------------- per-stage device times (profiling mode, separate pass) ----------------
+    capi.set_profiling(True)
+    stage = {}
+    for _ in range(3):
+        st, g = abi_step()
+        for k, v in capi.stage_times_ms().items():
+            stage.setdefault(k, []).append(v)
+    capi.set_profiling(False)
+    stage_ms = {k: float(np.median(v)) for k, v in stage.items()}
+    it = capi.introspect(st)
+    pairs_bwd_eval = int(it["n_contrib"].to(torch.int64).sum().item())
+    P_vis = int((st["radii"] > 0).sum().item())
+
+    # ---------------- e2e leg: public Python API, host inputs, loss read back ----------------
+    rs_kw = dict(image_height=H, image_width=W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=bg, scale_modifier=1.0,
+                 sh_degree=3, prefiltered=False, debug=False, antialiasing=w["aa"])
+    target_host = torch.from_numpy(np.random.default_rng(9).random((3, H, W), dtype=np.float32)).pin_memory()
+    cam_host = torch.from_numpy(np.concatenate([cam.world_view_transform.ravel(), cam.full_proj_transform.ravel(),
+                                                cam.camera_center.ravel()]).astype(np.float32)).pin_memory()
+    target_dev = torch.empty(3, H, W, device=dev)
+    cam_dev = torch.empty(35, device=dev)
+    params = G.as_leaf_params()
+    loss_host = torch.empty(1).pin_memory()
+
+    def api_step():
+        cam_dev.copy_(cam_host, non_blocking=True)
+        target_dev.copy_(target_host, non_blocking=True)
+        rs = GaussianRasterizationSettings(viewmatrix=cam_dev[0:16].view(4, 4), projmatrix=cam_dev[16:32].view(4, 4),
+                                           campos=cam_dev[32:35], **rs_kw)
+        means2D = torch.zeros_like(params["xyz"], requires_grad=True)
+        color, radii, invd = GaussianRasterizer(rs)(means3D=params["xyz"], means2D=means2D, opacities=params["opacity"],
+                                                    shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
+        loss = (color - target_dev).abs().mean()
+        loss.backward()
+        if world > 1:
+            G.allreduce_param_grads(params)
+        loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        for p_ in params.values():
+            p_.grad = None
+        return float(loss_host[0])
+
+    for _ in range(3):
+        api_step()
+    barrier()
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(args.steps):
+        api_step()
+    e1.record()
+    barrier()
+    wall = time.perf_counter() - t0
+    e2e_ms = max(e0.elapsed_time(e1), wall * 1000.0)
+    if world > 1:
+        tms = torch.tensor([e2e_ms], device=dev)
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        e2e_ms = float(tms.item())
+    e2e_val = world * args.steps / (e2e_ms / 1000.0)
+    h2d = target_host.numel() * 4 + cam_host.numel() * 4
+    d2h = 4 + 4    # loss + num_rendered
+
+    out = None
+    if rank == 0:
+        peaks = {}
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                peaks = json.load(f)
+        except OSError:
+            pass
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        peak_src = "measured (MEASURED_PEAKS.json)" if peaks else "fallback 6650 GB/s"
+        sm_mhz = clocks.get("sm_mhz") or 1965.0
+        fp32_peak_max = FP32_LANES * 1.965e9 / 1e12
+        fp32_peak_clk = FP32_LANES * sm_mhz * 1e6 / 1e12
+
+        # ---------------- CPU baseline (oracle port), bounded sample = one full view ----------------
+        cpu = None
+        pairs_eval = pairs_blend = None
+        if not args.no_cpu_baseline and world == 1:
+            from oracle import gs_oracle as go
+            sec, f = oracle_step(scene, cam, w, (dcol_np, ddep_np))
+            pairs_eval, pairs_blend = f["pairs_evaluated"], f["pairs_blended"]
+            cpu = {"value": 1.0 / sec, "unit": "renders/s", "cores": go.num_threads(), "kind": "port",
+                   "sample": "one full %dx%d view of %d Gaussians, fwd+bwd, %.1f s" % (W, H, P, sec)}
+
+        passes = (32 + int(np.ceil(np.log2(max(((W + 15) // 16) * ((H + 15) // 16), 2)))) + 7) // 8
+        def hbm(bytes_, ms_):
+            a = bytes_ / (ms_ / 1e3) / 1e9 if ms_ and ms_ > 0 else None
+            return {"bound": "hbm", "algorithmic_bytes": int(bytes_), "ms": ms_, "achieved": a, "peak": hbm_peak,
+                    "unit": "GB/s", "frac": (a / hbm_peak) if a else None}
+        stages = {
+            "preprocess": hbm(52 * P + 259 * P_vis, stage_ms.get("preprocess")),
+            "scan": hbm(8 * P, stage_ms.get("scan")),
+            "duplicate": hbm(20 * P_vis + 12 * N, stage_ms.get("duplicate")),
+            "sort": hbm(8 * N + passes * 24 * N, stage_ms.get("sort")),
+            "ranges": hbm(8 * N + 8 * ((W + 15) // 16) * ((H + 15) // 16), stage_ms.get("ranges")),
+            "preprocess_bwd": hbm(504 * P_vis + 304 * (P - P_vis) * 0 + 236 * P, stage_ms.get("preprocess_bwd")),
+        }
+        def fp32(flop, ms_):
+            a = flop / (ms_ / 1e3) / 1e12 if ms_ and ms_ > 0 and flop else None
+            return {"bound": "fp32", "algorithmic_flop": int(flop) if flop else None, "ms": ms_, "achieved": a,
+                    "peak": fp32_peak_max, "peak_at_measured_clock": fp32_peak_clk, "unit": "TFLOP/s",
+                    "frac": (a / fp32_peak_max) if a else None, "traffic": None}
+        if pairs_eval is not None:
+            stages["render_fwd"] = fp32(30 * pairs_blend + 14 * (pairs_eval - pairs_blend), stage_ms.get("render_fwd"))
+            stages["render_bwd"] = fp32(75 * pairs_blend + 14 * (pairs_bwd_eval - pairs_blend), stage_ms.get("render_bwd"))
+        else:
+            stages["render_fwd"] = fp32(None, stage_ms.get("render_fwd"))
+            stages["render_bwd"] = fp32(None, stage_ms.get("render_bwd"))
+        dominant = max(stage_ms, key=lambda k: stage_ms[k] if k != "host_sync" else -1)
+        roof = dict(stages.get(dominant, {}))
+        roof["kernel"] = dominant
+        roof.setdefault("traffic", None)
+
+        passes_launch = passes
+        launches_per_step = 1 + 1 + 1 + 1 + passes_launch + 1 + 1 + 1 + 1
+        out = {
+            "metric": "fwd+bwd renders/s", "value": value, "unit": "renders/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload + ": " + w["desc"], "P": P, "P_visible": P_vis, "num_rendered": N,
+                       "width": W, "height": H, "pairs_evaluated_fwd": pairs_eval, "pairs_blended": pairs_blend,
+                       "pairs_evaluated_bwd": pairs_bwd_eval, "l2": "inputs (708 MB of Gaussians + scratch) exceed the 126 MB L2",
+                       "parallelism": "view-parallel dp%d, replicated Gaussians, NCCL all-reduce of 59 fp32/Gaussian" % world
+                       if world > 1 else "single GPU", "peak_source": peak_src},
+            "clocks": clocks,
+            "e2e": {"value": e2e_val, "unit": "renders/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": e2e_ms / args.steps,
+                    "what": "GaussianRasterizer autograd fwd+bwd + L1 loss; camera+target image from pinned host memory, loss read back"},
+            "gpu_launches": launches_per_step * args.steps,
+            "stage_ms": stage_ms, "roofline": roof, "roofline_stages": stages, "cpu_baseline": cpu,
+        }
+        # same-box bar: the unmodified reference CUDA kernels (oracle/_ref), informational
+        if not args.no_ref_cuda and world == 1:
+            try:
+                from oracle import ref_cuda
+                if ref_cuda.available():
+                    R = ref_cuda.RefRasterizer()
+                    for _ in range(2):
+                        f = R.forward(width=W, height=H, **common)
+                        R.backward(f["radii"], dL_dcolor=dcol, dL_dinvdepth=ddep, **common)
+                    torch.cuda.synchronize()
+                    t0 = time.perf_counter()
+                    nrep = 5
+                    tf = 0.0
+                    for _ in range(nrep):
+                        t1 = time.perf_counter()
+                        f = R.forward(width=W, height=H, **common)
+                        tf += time.perf_counter() - t1
+                        R.backward(f["radii"], dL_dcolor=dcol, dL_dinvdepth=ddep, **common)
+                    torch.cuda.synchronize()
+                    dt = (time.perf_counter() - t0) / nrep
+                    out["reference_cuda_same_box"] = {"renders_per_s": 1.0 / dt, "ms_per_step": dt * 1e3,
+                                                      "fwd_ms": tf / nrep * 1e3, "note": "unmodified reference kernels + CUB, sm_100a, incl. zero-fills"}
+                    R.close()
+            except Exception as exc:  # informational leg only
+                out["reference_cuda_same_box"] = {"error": str(exc)[:200]}
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -176,15 +176,22 @@ def forward(*, means3D, opacities, viewmatrix, projmatrix, cam_pos, background, 
 
 def backward(state, *, dL_dcolor, dL_dinvdepth=None, means3D, opacities, viewmatrix, projmatrix, cam_pos,
              background, tan_fovx, tan_fovy, shs=None, colors_precomp=None, scales=None, rotations=None,
-             cov3D_precomp=None, sh_degree=3, scale_modifier=1.0, antialiasing=False, debug=False):
+             cov3D_precomp=None, sh_degree=3, scale_modifier=1.0, antialiasing=False, debug=False, out=None):
+    """gsr_backward.  `out` may map output names to preallocated contiguous tensors (e.g. views of a
+    gradient bucket) that the kernels then write directly."""
     L = lib()
     dev = means3D.device
     P, W, H, M = state["P"], state["W"], state["H"], state["M"]
+    out = out or {}
     e = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)
     g = dict(dL_dmeans2D=e(P, 3), dL_dconic=e(P, 2, 2), dL_dopacity=e(P, 1), dL_dcolors=e(P, 3),
              dL_dinvdepths=e(P, 1) if dL_dinvdepth is not None else None, dL_dmeans3D=e(P, 3), dL_dcov3D=e(P, 6),
              dL_dsh=e(P, M, 3) if M else None, dL_dscales=e(P, 3) if scales is not None else None,
              dL_drotations=e(P, 4) if scales is not None else None)
+    for k, v in out.items():
+        if g.get(k) is not None:
+            assert v.is_contiguous() and v.numel() == g[k].numel() and v.data_ptr() % 16 == 0
+            g[k] = v
     a = BackwardArgs(P, sh_degree, M, state["num_rendered"], W, H, _ptr(background), _ptr(means3D), _ptr(shs),
                      _ptr(colors_precomp), _ptr(opacities), _ptr(scales), scale_modifier, _ptr(rotations),
                      _ptr(cov3D_precomp), _ptr(viewmatrix), _ptr(projmatrix), _ptr(cam_pos), tan_fovx, tan_fovy,

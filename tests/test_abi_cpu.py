@@ -1,0 +1,86 @@
+"""The C-ABI library loads without a GPU, exports every symbol include/gsr.h declares, and its
+argument validation / layout functions work (no compute calls)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+import cases  # noqa: F401  (sys.path)
+from gsr_b200 import capi
+
+ROOT = cases.ROOT
+
+
+def _declared_functions():
+    src = open(os.path.join(ROOT, "include", "gsr.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(gsr_[a-z_0-9]+)\s*\(", src)) - {"gsr_alloc_fn"})
+
+
+def test_library_exports_every_declared_symbol():
+    L = ctypes.CDLL(capi.LIB_PATH)
+    names = _declared_functions()
+    assert len(names) >= 14
+    for n in names:
+        assert hasattr(L, n), "libgsr_b200.so does not export " + n
+    assert sorted(capi.EXPORTS) == names
+
+
+def test_version_and_layouts():
+    L = capi.lib()
+    assert b"sm_100a" in L.gsr_version()
+    g = capi.GeometryLayout()
+    L.gsr_get_geometry_layout(1000, ctypes.byref(g))
+    offs = [g.depths, g.records, g.cov3D, g.clamped, g.tiles_touched, g.point_offsets, g.total]
+    assert offs == sorted(offs) and all(o % 256 == 0 for o in offs[:-1])
+    assert g.records - g.depths >= 4000 and g.cov3D - g.records >= 48000
+    assert L.gsr_geometry_bytes(1000) == g.total
+    b = capi.BinningLayout()
+    L.gsr_get_binning_layout(12345, 640, 360, ctypes.byref(b))
+    assert b.keys - b.keys_unsorted >= 12345 * 8 and b.total == L.gsr_binning_bytes(12345, 640, 360)
+    i = capi.ImageLayout()
+    L.gsr_get_image_layout(167, 101, ctypes.byref(i))
+    assert i.n_contrib - i.final_T >= 167 * 101 * 4 and i.total == L.gsr_image_bytes(167, 101)
+    assert L.gsr_sort_temp_bytes(0) > 0 and L.gsr_sort_temp_bytes(1 << 20) > L.gsr_sort_temp_bytes(1 << 10)
+
+
+def test_argument_validation_without_gpu():
+    L = capi.lib()
+    n = ctypes.c_int(-7)
+    cb = capi.ALLOC_FN(lambda nbytes, user: None)
+    assert L.gsr_forward(None, cb, None, cb, None, cb, None, None, ctypes.byref(n)) == -1
+    assert b"null" in L.gsr_last_error()
+    a = capi.ForwardArgs()
+    a.P, a.width, a.height = 10, 0, 16
+    assert L.gsr_forward(ctypes.byref(a), cb, None, cb, None, cb, None, None, ctypes.byref(n)) == -1
+    a.width = 16
+    a.out_color = 1   # non-null sentinel; P=10 but inputs missing -> invalid before anything is touched
+    assert L.gsr_forward(ctypes.byref(a), cb, None, cb, None, cb, None, None, ctypes.byref(n)) == -1
+    assert b"missing" in L.gsr_last_error()
+    assert L.gsr_backward(None, None) == -1
+    assert L.gsr_mark_visible(-1, None, None, None, None, None) == -1
+    assert L.gsr_mark_visible(0, None, None, None, None, None) == 0
+    assert L.gsr_sort_pairs(None, None, None, None, 0, 80, None, None) == -1
+    assert L.gsr_last_stage_ms(0) == -1.0
+
+
+def test_python_api_has_no_cpu_fallback():
+    import torch
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    rs = GaussianRasterizationSettings(8, 8, 1.0, 1.0, torch.zeros(3), 1.0, torch.eye(4), torch.eye(4), 3,
+                                       torch.zeros(3), False, False, False)
+    r = GaussianRasterizer(rs)
+    with pytest.raises(Exception, match="excatly one of either SHs or precomputed colors"):
+        r(torch.zeros(4, 3), torch.zeros(4, 3), torch.zeros(4, 1), scales=torch.zeros(4, 3), rotations=torch.zeros(4, 4))
+    with pytest.raises(Exception, match="exactly one of either scale/rotation pair or precomputed 3D covariance"):
+        r(torch.zeros(4, 3), torch.zeros(4, 3), torch.zeros(4, 1), shs=torch.zeros(4, 16, 3), scales=torch.zeros(4, 3))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        r(torch.zeros(4, 3), torch.zeros(4, 3), torch.zeros(4, 1), shs=torch.zeros(4, 16, 3), scales=torch.zeros(4, 3),
+          rotations=torch.zeros(4, 4))
+    with pytest.raises(RuntimeError, match="means3D must have dimensions"):
+        r(torch.zeros(4, 2), torch.zeros(4, 3), torch.zeros(4, 1), shs=torch.zeros(4, 16, 3), scales=torch.zeros(4, 3),
+          rotations=torch.zeros(4, 4))
+    assert list(GaussianRasterizationSettings._fields) == [
+        "image_height", "image_width", "tanfovx", "tanfovy", "bg", "scale_modifier", "viewmatrix", "projmatrix",
+        "sh_degree", "campos", "prefiltered", "debug", "antialiasing"]

@@ -1,0 +1,126 @@
+"""Drop-in behaviour of the public Python package on a GPU: autograd path, markVisible, empty and
+degenerate inputs, debug flag, stream/device handling."""
+import numpy as np
+import pytest
+
+import cases
+from test_oracle_golden import GRAD_TOL
+
+pytestmark = pytest.mark.gpu
+
+
+def _settings(cam, opts, scene, dev, debug=False):
+    import torch
+    from diff_gaussian_rasterization import GaussianRasterizationSettings
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    return GaussianRasterizationSettings(
+        image_height=cam.image_height, image_width=cam.image_width, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy,
+        bg=t(np.array(opts["bg"], np.float32)), scale_modifier=1.0, viewmatrix=t(cam.world_view_transform),
+        projmatrix=t(cam.full_proj_transform), sh_degree=scene["sh_degree"], campos=t(cam.camera_center),
+        prefiltered=False, debug=debug, antialiasing=opts["antialiasing"])
+
+
+@pytest.mark.parametrize("name", ["tiny64", "aa160x96", "colors", "cov3d"])
+def test_autograd_path_matches_oracle(cuda, name):
+    import torch
+    from diff_gaussian_rasterization import GaussianRasterizer
+    scene, cam, opts = cases.get_case(name)
+    grads = cases.grads_for(cam)
+    o = cases.run_oracle(scene, cam, opts, grads)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(cuda).requires_grad_(True)
+    means3D, opac = t(scene["means3D"]), t(scene["opacities"])
+    means2D = torch.zeros_like(means3D, requires_grad=True)
+    kw, leaves = {}, {"dL_dmeans3D": means3D, "dL_dopacity": opac, "dL_dmeans2D": means2D}
+    if opts["mode"] == "colors":
+        kw["colors_precomp"] = leaves["dL_dcolors"] = t(scene["colors_precomp"])
+    else:
+        kw["shs"] = leaves["dL_dsh"] = t(scene["shs"])
+    if opts["mode"] == "cov3d":
+        kw["cov3D_precomp"] = leaves["dL_dcov3D"] = t(cases.cov3d_of(scene))
+    else:
+        kw["scales"] = leaves["dL_dscales"] = t(scene["scales"])
+        kw["rotations"] = leaves["dL_drotations"] = t(scene["rotations"])
+    color, radii, invd = GaussianRasterizer(_settings(cam, opts, scene, cuda))(means3D=means3D, means2D=means2D,
+                                                                                opacities=opac, **kw)
+    assert color.shape == (3, cam.image_height, cam.image_width) and invd.shape == (1, cam.image_height, cam.image_width)
+    assert radii.dtype == torch.int32 and np.array_equal(radii.cpu().numpy(), o["radii"])
+    ok = ~o["borderline"]
+    assert np.abs(color.detach().cpu().numpy() - o["out_color"])[:, ok].max() <= 1e-5
+    assert np.abs(invd.detach().cpu().numpy() - o["invdepth"])[:, ok].max() <= 1e-5
+    (color * torch.from_numpy(grads[0]).to(cuda)).sum().add((invd * torch.from_numpy(grads[1]).to(cuda)).sum()).backward()
+    for k, leaf in leaves.items():
+        want = o[k].astype(np.float64)
+        got = leaf.grad.cpu().numpy().astype(np.float64).reshape(want.shape)
+        if np.abs(want).max() < 1e-12:
+            continue
+        assert np.abs(got - want).max() / np.abs(want).max() <= GRAD_TOL[k], k
+    assert means2D.grad.shape == (scene["means3D"].shape[0], 3) and float(means2D.grad[:, 2].abs().max()) == 0.0
+
+
+def test_mark_visible_and_no_grad_render(cuda):
+    import torch
+    from diff_gaussian_rasterization import GaussianRasterizer
+    from oracle import gs_oracle as go
+    scene, cam, opts = cases.get_case("odd167x101")
+    r = GaussianRasterizer(_settings(cam, opts, scene, cuda))
+    vis = r.markVisible(torch.from_numpy(scene["means3D"]).to(cuda))
+    assert vis.dtype == torch.bool
+    assert np.array_equal(vis.cpu().numpy(), go.mark_visible(scene["means3D"], cam.world_view_transform))
+    with torch.no_grad():   # render.py path: forward only, scratch never handed back
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(cuda)
+        color, radii, invd = r(means3D=t(scene["means3D"]), means2D=torch.zeros(len(scene["means3D"]), 3, device=cuda),
+                               opacities=t(scene["opacities"]), shs=t(scene["shs"]), scales=t(scene["scales"]),
+                               rotations=t(scene["rotations"]))
+    assert bool(torch.isfinite(color).all())
+
+
+def test_empty_inputs_and_fully_culled_view(cuda):
+    import torch
+    from diff_gaussian_rasterization import GaussianRasterizer
+    scene, cam, opts = cases.get_case("empty_view")
+    rs = _settings(cam, dict(opts, bg=(0.25, 0.5, 0.75)), scene, cuda)
+    z = lambda *s: torch.zeros(*s, device=cuda)
+    # P = 0: the reference skips every kernel and returns the zero-initialised image (rasterize_points.cu:88)
+    color, radii, invd = GaussianRasterizer(rs)(means3D=z(0, 3), means2D=z(0, 3), opacities=z(0, 1), shs=z(0, 16, 3),
+                                                scales=z(0, 3), rotations=z(0, 4))
+    assert radii.numel() == 0 and float(color.abs().max()) == 0.0
+    # every Gaussian culled: num_rendered = 0, image = background, all gradients zero
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(cuda).requires_grad_(True)
+    m3, sh, op, sc, ro = t(scene["means3D"]), t(scene["shs"]), t(scene["opacities"]), t(scene["scales"]), t(scene["rotations"])
+    color, radii, invd = GaussianRasterizer(rs)(means3D=m3, means2D=torch.zeros_like(m3, requires_grad=True), opacities=op,
+                                                shs=sh, scales=sc, rotations=ro)
+    assert int(radii.abs().max()) == 0
+    for ch, v in enumerate((0.25, 0.5, 0.75)):
+        assert float((color[ch] - v).abs().max()) == 0.0
+    color.sum().backward()
+    for p in (m3, sh, op, sc, ro):
+        assert float(p.grad.abs().max()) == 0.0
+
+
+def test_debug_flag_and_side_stream(cuda):
+    import torch
+    from diff_gaussian_rasterization import GaussianRasterizer
+    scene, cam, opts = cases.get_case("tiny64")
+    o = cases.run_oracle(scene, cam, opts)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(cuda)
+    args = dict(means3D=t(scene["means3D"]), means2D=torch.zeros(1000, 3, device=cuda), opacities=t(scene["opacities"]),
+                shs=t(scene["shs"]), scales=t(scene["scales"]), rotations=t(scene["rotations"]))
+    s = torch.cuda.Stream()
+    torch.cuda.synchronize()
+    with torch.cuda.stream(s):      # launches follow torch's current stream (reference: legacy default stream)
+        color, radii, _ = GaussianRasterizer(_settings(cam, opts, scene, cuda, debug=True))(**args)
+    s.synchronize()
+    assert np.array_equal(radii.cpu().numpy(), o["radii"])
+    assert np.abs(color.cpu().numpy() - o["out_color"])[:, ~o["borderline"]].max() <= 1e-5
+
+
+def test_prefiltered_trap_becomes_an_error(cuda):
+    import torch
+    from diff_gaussian_rasterization import GaussianRasterizer
+    scene, cam, opts = cases.get_case("tiny64")      # contains Gaussians behind the camera
+    rs = _settings(cam, opts, scene, cuda)._replace(prefiltered=True)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(cuda)
+    with pytest.raises(RuntimeError, match="prefiltered"):
+        GaussianRasterizer(rs)(means3D=t(scene["means3D"]), means2D=torch.zeros(1000, 3, device=cuda),
+                               opacities=t(scene["opacities"]), shs=t(scene["shs"]), scales=t(scene["scales"]),
+                               rotations=t(scene["rotations"]))
