@@ -50,6 +50,58 @@ __device__ __forceinline__ float blend_power(float dx, float dy, float A, float 
     return ffma(a, -0.5f, -t4);
 }
 
+// ---- conservative tile / sub-block culling ------------------------------------------------------
+// A (pixel, Gaussian) pair is blended only if alpha = opacity*exp(power) >= 1/255, i.e.
+// q(d) = -power = 0.5(A dx^2 + C dy^2) + B dx dy <= tau := ln(255*opacity), d = centre - pixel.
+// The reference's 3-sigma bounding square puts many Gaussians in tile lists that cannot reach that
+// threshold anywhere in the tile.  rect_may_contribute() bounds min q over a pixel rectangle exactly
+// (q is a convex quadratic: the minimum over a box that does not contain the centre lies on an
+// edge) and adds a slack that dominates the fp32 rounding of the per-pixel evaluation, so a culled
+// pair is one the per-pixel test would have rejected as well: results stay bit-identical, the
+// pair is just never evaluated.  NaNs compare false -> keep.
+struct CullCoef { float gx, gy, A, B, C, nBinvA, nBinvC, tau; };
+
+__device__ __forceinline__ CullCoef make_cull(float gx, float gy, float A, float B, float C, float opacity) {
+    CullCoef c;
+    c.gx = gx; c.gy = gy; c.A = A; c.B = B; c.C = C;
+    c.nBinvA = -B / A; c.nBinvC = -B / C;
+    c.tau = __logf(255.0f * opacity);
+    return c;
+}
+
+__device__ __forceinline__ bool rect_may_contribute(const CullCoef& c, float X0, float X1, float Y0, float Y1) {
+    const float dxl = c.gx - X1, dxh = c.gx - X0, dyl = c.gy - Y1, dyh = c.gy - Y0;   // d ranges over the rect
+    const float mx = fmaxf(fabsf(dxl), fabsf(dxh)), my = fmaxf(fabsf(dyl), fabsf(dyh));
+    const float slack = c.tau + 2e-3f + 4e-6f * (0.5f * (c.A * mx * mx + c.C * my * my) + fabsf(c.B) * mx * my);
+    if (dxl <= 0.0f && dxh >= 0.0f && dyl <= 0.0f && dyh >= 0.0f) return !(0.0f > slack);
+    float qmin;
+    {   // vertical edges dx = e, dy free in [dyl, dyh]
+        float e = dxl, t = fminf(dyh, fmaxf(dyl, c.nBinvC * e));
+        qmin = 0.5f * (c.A * e * e + c.C * t * t) + c.B * e * t;
+        e = dxh; t = fminf(dyh, fmaxf(dyl, c.nBinvC * e));
+        qmin = fminf(qmin, 0.5f * (c.A * e * e + c.C * t * t) + c.B * e * t);
+        // horizontal edges dy = e, dx free in [dxl, dxh]
+        e = dyl; t = fminf(dxh, fmaxf(dxl, c.nBinvA * e));
+        qmin = fminf(qmin, 0.5f * (c.A * t * t + c.C * e * e) + c.B * t * e);
+        e = dyh; t = fminf(dxh, fmaxf(dxl, c.nBinvA * e));
+        qmin = fminf(qmin, 0.5f * (c.A * t * t + c.C * e * e) + c.B * t * e);
+    }
+    return !(qmin > slack);
+}
+
+// 8-bit mask over the 8 warps' 8x4 pixel blocks of a 16x16 tile (warp w: x0 + (w&1)*8, y0 + (w>>1)*4)
+__device__ __forceinline__ unsigned subblock_mask(const CullCoef& c, float tile_x0, float tile_y0) {
+    if (!(c.A > 0.0f && c.C > 0.0f && c.A * c.C > c.B * c.B)) return 0xffu;   // not a convex quadratic: no bound, keep
+    if (!rect_may_contribute(c, tile_x0, tile_x0 + 15.0f, tile_y0, tile_y0 + 15.0f)) return 0u;
+    unsigned m = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+        const float bx = tile_x0 + (float)((w & 1) * 8), by = tile_y0 + (float)((w >> 1) * 4);
+        if (rect_may_contribute(c, bx, bx + 7.0f, by, by + 3.0f)) m |= 1u << w;
+    }
+    return m;
+}
+
 // ---- streaming load/store helpers --------------------------------------------------------------
 __device__ __forceinline__ float4 ldg_stream_f4(const float4* p) {
     float4 v;

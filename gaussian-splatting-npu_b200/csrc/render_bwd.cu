@@ -2,25 +2,24 @@
 //
 // Replaces BACKWARD::render / renderCUDA<3> (diff-gaussian-rasterization-npu/cuda_rasterizer/
 // backward.cu:452-638).  The reference issues 9-10 global fp32 atomicAdd per contributing
-// (pixel, Gaussian) pair.  Here all 256 pixels of a tile look at the same Gaussian in the same
-// iteration, so the per-Gaussian sums are pre-reduced on chip:
-//   warp shuffle tree over the 32 pixels of a warp (skipped entirely when no lane contributes)
-//   -> shared-memory accumulators per staged Gaussian (one ATOMS per warp and value)
-//   -> ONE global atomic per value per (tile, Gaussian) when the batch retires.
-// That is 256x fewer global atomics than the reference.  Batches start at the tile's deepest
-// contributing position (block max of n_contrib) instead of the end of the list.  The per-pixel
-// recurrences are the reference's; power/alpha use the same exactly-rounded chain as the forward
-// so that every pair takes the same skip decisions it took there.
+// (pixel, Gaussian) pair and evaluates every pair of the tile list below n_contrib.  Here:
+//   * batches start at the tile's deepest blended position (block max of n_contrib);
+//   * while staging a batch, each thread tests its Gaussian against the eight 8x4 pixel blocks of
+//     the tile (rect_may_contribute, exact + conservatively rounded), and each warp walks only the
+//     Gaussians that can reach alpha >= 1/255 inside its block -- the same pairs the reference would
+//     have skipped after evaluating them;
+//   * the ten per-Gaussian sums are pre-reduced on chip: a transposing butterfly over the warp
+//     (14 shuffles instead of 50: lanes trade halves of the value vector, so after log2 steps each
+//     value's total sits in its own lane) -> ONE shared-memory atomic instruction per warp and
+//     Gaussian (10 lanes, 10 addresses) -> ONE global atomic per value per (tile, Gaussian) when the
+//     batch retires: 256x fewer global atomics than the reference;
+//   * the next batch's records are in flight in registers while the current one is processed.
+// The per-pixel recurrences are the reference's; power/alpha use the same exactly-rounded chain as
+// the forward so that every pair takes the same skip decision it took there.
 #include "gsr_common.cuh"
 
 #define RB_THREADS 256
-#define RB_NV 10     // dcolor r,g,b | dinvdepth | dmean2D x,y | dconic xx,xy,yy | dopacity
-
-__device__ __forceinline__ float warp_sum(float v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
-}
+#define RB_NV 10     // dcolor r,g,b | dinvdepth | dmean2D x,y | dconic xx,xy | dconic yy | dopacity
 
 template <bool HAS_DEPTH>
 __global__ void __launch_bounds__(RB_THREADS)
@@ -34,6 +33,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     __shared__ float4 sB[RB_THREADS];          // conic.c, opacity, r, g
     __shared__ float2 sC[RB_THREADS];          // b, 1/depth
     __shared__ uint32_t sId[RB_THREADS];
+    __shared__ unsigned char sMask[RB_THREADS];
     __shared__ float sAcc[RB_THREADS * RB_NV];
     __shared__ uint32_t sMax[RB_THREADS / 32];
 
@@ -44,6 +44,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     const int py = ty * GSR_TILE + (warp >> 1) * 4 + (lane >> 3);
     const bool inside = px < W && py < H;
     const float pxf = (float)px, pyf = (float)py;
+    const float tile_x0 = (float)(tx * GSR_TILE), tile_y0 = (float)(ty * GSR_TILE);
     const size_t pix = (size_t)py * W + px, HW = (size_t)H * W;
 
     const uint2 range = ranges[tile];
@@ -58,8 +59,8 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 
     // deepest list position any pixel of this tile blended
-    uint32_t m = __reduce_max_sync(0xffffffffu, last);
-    if (lane == 0) sMax[warp] = m;
+    const uint32_t wmax = __reduce_max_sync(0xffffffffu, last);
+    if (lane == 0) sMax[warp] = wmax;
     for (int k = tid; k < RB_THREADS * RB_NV; k += RB_THREADS) sAcc[k] = 0.0f;
     __syncthreads();
     uint32_t remaining = 0;
@@ -70,81 +71,120 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     float acc_r = 0, acc_g = 0, acc_b = 0, acc_d = 0;          // accum_rec / accum_invdepth_rec
     float last_alpha = 0, last_r = 0, last_g = 0, last_b = 0, last_d = 0;
 
+    // software pipeline: the batch after the current one travels in registers
+    uint32_t nId = 0;
+    float4 nA = make_float4(0, 0, 0, 0), nB = nA, nC = nA;
+    if ((uint32_t)tid < remaining) {
+        nId = point_list[range.x + remaining - 1 - tid];
+        const float4* rec = records + 3 * (size_t)nId;
+        nA = rec[0]; nB = rec[1]; nC = rec[2];
+    }
+
     while (remaining > 0) {
         const int n = (int)min((uint32_t)RB_THREADS, remaining);
         // stage positions [remaining-n, remaining), backmost first
         if (tid < n) {
-            const uint32_t id = point_list[range.x + remaining - 1 - tid];
-            const float4* rec = records + 3 * (size_t)id;
-            sId[tid] = id;
-            sA[tid] = rec[0];
-            sB[tid] = rec[1];
-            const float4 r2 = rec[2];
-            sC[tid] = make_float2(r2.x, r2.y);
+            sId[tid] = nId; sA[tid] = nA; sB[tid] = nB; sC[tid] = make_float2(nC.x, nC.y);
+            sMask[tid] = (unsigned char)subblock_mask(make_cull(nA.x, nA.y, nA.z, nA.w, nB.x, nB.y), tile_x0, tile_y0);
         }
         __syncthreads();
-        for (int j = 0; j < n; j++) {
-            const uint32_t pos = remaining - 1 - j;             // 0-based position in the tile's list
-            float v[RB_NV];
-            bool contrib = false;
-            if (pos < last) {
-                const float4 a = sA[j];
-                const float4 b = sB[j];
-                const float dx = fsub(a.x, pxf), dy = fsub(a.y, pyf);
-                const float power = blend_power(dx, dy, a.z, a.w, b.x);
-                if (power <= 0.0f) {
-                    const float G = expf(power);
-                    const float alpha = fminf(0.99f, fmul(b.y, G));
-                    if (alpha >= 1.0f / 255.0f) {
-                        contrib = true;
-                        const float2 c = sC[j];
-                        T = T / (1.0f - alpha);
-                        const float dch = alpha * T;
-                        float dL_dalpha;
-                        acc_r = last_alpha * last_r + (1.0f - last_alpha) * acc_r; last_r = b.z;
-                        dL_dalpha = (b.z - acc_r) * dpx0;
-                        acc_g = last_alpha * last_g + (1.0f - last_alpha) * acc_g; last_g = b.w;
-                        dL_dalpha += (b.w - acc_g) * dpx1;
-                        acc_b = last_alpha * last_b + (1.0f - last_alpha) * acc_b; last_b = c.x;
-                        dL_dalpha += (c.x - acc_b) * dpx2;
-                        v[0] = dch * dpx0; v[1] = dch * dpx1; v[2] = dch * dpx2;
-                        if (HAS_DEPTH) {
-                            acc_d = last_alpha * last_d + (1.0f - last_alpha) * acc_d; last_d = c.y;
-                            dL_dalpha += (c.y - acc_d) * dpd;
-                            v[3] = dch * dpd;
-                        } else v[3] = 0.0f;
-                        dL_dalpha *= T;
-                        last_alpha = alpha;
-                        dL_dalpha += (-T_final / (1.0f - alpha)) * bg_dot;
-                        const float dL_dG = b.y * dL_dalpha;
-                        const float gdx = G * dx, gdy = G * dy;
-                        const float dG_ddelx = -gdx * a.z - gdy * a.w;
-                        const float dG_ddely = -gdy * b.x - gdx * a.w;
-                        v[4] = dL_dG * dG_ddelx * ddelx_dx;
-                        v[5] = dL_dG * dG_ddely * ddely_dy;
-                        v[6] = -0.5f * gdx * dx * dL_dG;
-                        v[7] = -0.5f * gdx * dy * dL_dG;
-                        v[8] = -0.5f * gdy * dy * dL_dG;
-                        v[9] = G * dL_dalpha;
+        if ((uint32_t)(RB_THREADS + tid) < remaining) {
+            nId = point_list[range.x + remaining - 1 - RB_THREADS - tid];
+            const float4* rec = records + 3 * (size_t)nId;
+            nA = rec[0]; nB = rec[1]; nC = rec[2];
+        }
+        // positions this warp still has to look at: below its deepest n_contrib
+        if (remaining - (uint32_t)n < wmax) {
+#pragma unroll 1
+            for (int k = 0; k < RB_THREADS / 32; k++) {
+                const int idx = k * 32 + lane;
+                unsigned bits = __ballot_sync(0xffffffffu, idx < n && ((sMask[idx] >> warp) & 1));
+                while (bits) {
+                    const int j = k * 32 + __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    const uint32_t pos = remaining - 1 - j;     // 0-based position in the tile's list
+                    float v0 = 0, v1 = 0, v2 = 0, v3 = 0, v4 = 0, v5 = 0, v6 = 0, v7 = 0, w0 = 0, w1 = 0;
+                    bool contrib = false;
+                    if (pos < last) {
+                        const float4 a = sA[j];
+                        const float4 b = sB[j];
+                        const float dx = fsub(a.x, pxf), dy = fsub(a.y, pyf);
+                        const float power = blend_power(dx, dy, a.z, a.w, b.x);
+                        if (power <= 0.0f) {
+                            const float G = expf(power);
+                            const float alpha = fminf(0.99f, fmul(b.y, G));
+                            if (alpha >= 1.0f / 255.0f) {
+                                contrib = true;
+                                const float2 c = sC[j];
+                                T = T / (1.0f - alpha);
+                                const float dch = alpha * T;
+                                float dL_dalpha;
+                                acc_r = last_alpha * last_r + (1.0f - last_alpha) * acc_r; last_r = b.z;
+                                dL_dalpha = (b.z - acc_r) * dpx0;
+                                acc_g = last_alpha * last_g + (1.0f - last_alpha) * acc_g; last_g = b.w;
+                                dL_dalpha += (b.w - acc_g) * dpx1;
+                                acc_b = last_alpha * last_b + (1.0f - last_alpha) * acc_b; last_b = c.x;
+                                dL_dalpha += (c.x - acc_b) * dpx2;
+                                v0 = dch * dpx0; v1 = dch * dpx1; v2 = dch * dpx2;
+                                if (HAS_DEPTH) {
+                                    acc_d = last_alpha * last_d + (1.0f - last_alpha) * acc_d; last_d = c.y;
+                                    dL_dalpha += (c.y - acc_d) * dpd;
+                                    v3 = dch * dpd;
+                                }
+                                dL_dalpha *= T;
+                                last_alpha = alpha;
+                                dL_dalpha += (-T_final / (1.0f - alpha)) * bg_dot;
+                                const float dL_dG = b.y * dL_dalpha;
+                                const float gdx = G * dx, gdy = G * dy;
+                                const float dG_ddelx = -gdx * a.z - gdy * a.w;
+                                const float dG_ddely = -gdy * b.x - gdx * a.w;
+                                v4 = dL_dG * dG_ddelx * ddelx_dx;
+                                v5 = dL_dG * dG_ddely * ddely_dy;
+                                v6 = -0.5f * gdx * dx * dL_dG;
+                                v7 = -0.5f * gdx * dy * dL_dG;
+                                w0 = -0.5f * gdy * dy * dL_dG;
+                                w1 = G * dL_dalpha;
+                            }
+                        }
                     }
-                }
-            }
-            if (__any_sync(0xffffffffu, contrib)) {
-                if (!contrib) {
-#pragma unroll
-                    for (int k = 0; k < RB_NV; k++) v[k] = 0.0f;
-                }
-#pragma unroll
-                for (int k = 0; k < RB_NV; k++) {
-                    if (!HAS_DEPTH && k == 3) continue;
-                    const float s = warp_sum(v[k]);
-                    if (lane == 0) atomicAdd(&sAcc[j * RB_NV + k], s);
+                    if (!__any_sync(0xffffffffu, contrib)) continue;
+                    // transposing butterfly: 8 values -> each lane ends with the warp total of value (lane>>2)
+                    {
+                        const bool h = lane & 16;
+                        float s, kp;
+                        s = h ? v0 : v4; kp = h ? v4 : v0; v0 = kp + __shfl_xor_sync(0xffffffffu, s, 16);
+                        s = h ? v1 : v5; kp = h ? v5 : v1; v1 = kp + __shfl_xor_sync(0xffffffffu, s, 16);
+                        s = h ? v2 : v6; kp = h ? v6 : v2; v2 = kp + __shfl_xor_sync(0xffffffffu, s, 16);
+                        s = h ? v3 : v7; kp = h ? v7 : v3; v3 = kp + __shfl_xor_sync(0xffffffffu, s, 16);
+                        s = h ? w0 : w1; kp = h ? w1 : w0; w0 = kp + __shfl_xor_sync(0xffffffffu, s, 16);
+                    }
+                    {
+                        const bool h = lane & 8;
+                        float s, kp;
+                        s = h ? v0 : v2; kp = h ? v2 : v0; v0 = kp + __shfl_xor_sync(0xffffffffu, s, 8);
+                        s = h ? v1 : v3; kp = h ? v3 : v1; v1 = kp + __shfl_xor_sync(0xffffffffu, s, 8);
+                        w0 += __shfl_xor_sync(0xffffffffu, w0, 8);
+                    }
+                    {
+                        const bool h = lane & 4;
+                        const float s = h ? v0 : v1, kp = h ? v1 : v0;
+                        v0 = kp + __shfl_xor_sync(0xffffffffu, s, 4);
+                        w0 += __shfl_xor_sync(0xffffffffu, w0, 4);
+                    }
+                    v0 += __shfl_xor_sync(0xffffffffu, v0, 2); w0 += __shfl_xor_sync(0xffffffffu, w0, 2);
+                    v0 += __shfl_xor_sync(0xffffffffu, v0, 1); w0 += __shfl_xor_sync(0xffffffffu, w0, 1);
+                    // v0: total of value index (lane>>2) in 0..7 ; w0: total of value 8 + (lane>>4)
+                    const bool first = (lane & 3) == 0, second = (lane & 15) == 1;
+                    if (first || second) {
+                        const int vi = first ? (lane >> 2) : 8 + (lane >> 4);
+                        if (HAS_DEPTH || vi != 3) atomicAdd(&sAcc[j * RB_NV + vi], first ? v0 : w0);
+                    }
                 }
             }
         }
         __syncthreads();
         // retire the batch: one global atomic per value and Gaussian
-        if (tid < n) {
+        if (tid < n && sMask[tid]) {
             const uint32_t id = sId[tid];
             float* a = &sAcc[tid * RB_NV];
             if (a[0] != 0.0f) atomicAdd(&dL_dcolor[3 * (size_t)id], a[0]);
