@@ -102,6 +102,27 @@ __device__ __forceinline__ unsigned subblock_mask(const CullCoef& c, float tile_
     return m;
 }
 
+// ---- explicit shared-memory accessors --------------------------------------------------------------
+// Static __shared__ arrays indexed in a hot loop make nvcc re-materialise the shared-window base
+// (S2R SR_CgaCtaId ; LEA) on every access; a 32-bit shared address computed once and kept in a
+// register turns each access into one LDS.
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ float4 lds_f4(uint32_t a) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ float2 lds_f2(uint32_t a) {
+    float2 v;
+    asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
 // ---- streaming load/store helpers --------------------------------------------------------------
 __device__ __forceinline__ float4 ldg_stream_f4(const float4* p) {
     float4 v;

@@ -28,62 +28,67 @@
 #define SHC3_5 1.445305721320277f
 #define SHC3_6 -0.5900435899266435f
 
-// backward.cu:23-142.  sh[k*3+c] in registers; writes dsh[k*3+c] (zeros above the active degree)
-// and adds the view-direction term to dmean.
-__device__ __forceinline__ void sh_backward(int deg, const float* sh, float ox, float oy, float oz, unsigned clamp_bits,
-                                            float dr, float dg, float db, float* dsh, float& dmx, float& dmy, float& dmz) {
+// SH backward (backward.cu:23-142), streamed.  dL_dsh[k][c] = w_k(dir) * dL_dRGB_c needs only the 16
+// basis weights and the 3 colour gradients; the view-direction gradient
+//   dL_ddir = sum_k grad(w_k) * (sh[k] . dL_dRGB)
+// needs only the 16 scalars t_k = sh[k] . dL_dRGB, accumulated while the row streams by.  No
+// 48-float register arrays.  `E(i)` yields element i = k*3+c of the SH row; rows above the active
+// degree are never touched.  Returns w[16] (zeros above the degree) and d[3]; adds to dmean.
+template <typename Row>
+__device__ __forceinline__ void sh_backward(int deg, const Row& E, float ox, float oy, float oz, unsigned clamp_bits,
+                                            float dr, float dg, float db, float* w, float* d,
+                                            float& dmx, float& dmy, float& dmz) {
     const float len = sqrtf(ox * ox + oy * oy + oz * oz);
     const float x = ox / len, y = oy / len, z = oz / len;
-    const float d[3] = { (clamp_bits & 1u) ? 0.0f : dr, (clamp_bits & 2u) ? 0.0f : dg, (clamp_bits & 4u) ? 0.0f : db };
-    float w[16];
+    d[0] = (clamp_bits & 1u) ? 0.0f : dr; d[1] = (clamp_bits & 2u) ? 0.0f : dg; d[2] = (clamp_bits & 4u) ? 0.0f : db;
 #pragma unroll
     for (int k = 0; k < 16; k++) w[k] = 0.0f;
-    float gx[3] = { 0, 0, 0 }, gy[3] = { 0, 0, 0 }, gz[3] = { 0, 0, 0 };
     w[0] = SHC0;
+    float ddx = 0.0f, ddy = 0.0f, ddz = 0.0f;
+#define SH_T(k) (E(3 * (k)) * d[0] + E(3 * (k) + 1) * d[1] + E(3 * (k) + 2) * d[2])
     if (deg > 0) {
         w[1] = -SHC1 * y; w[2] = SHC1 * z; w[3] = -SHC1 * x;
-#pragma unroll
-        for (int c = 0; c < 3; c++) { gx[c] = -SHC1 * sh[9 + c]; gy[c] = -SHC1 * sh[3 + c]; gz[c] = SHC1 * sh[6 + c]; }
+        const float t1 = SH_T(1), t2 = SH_T(2), t3 = SH_T(3);
+        ddx = -SHC1 * t3; ddy = -SHC1 * t1; ddz = SHC1 * t2;
         if (deg > 1) {
             const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
             w[4] = SHC2_0 * xy; w[5] = SHC2_1 * yz; w[6] = SHC2_2 * (2.f * zz - xx - yy); w[7] = SHC2_3 * xz; w[8] = SHC2_4 * (xx - yy);
-#pragma unroll
-            for (int c = 0; c < 3; c++) {
-                const float* h = sh + c;
-                gx[c] += SHC2_0 * y * h[12] + SHC2_2 * 2.f * -x * h[18] + SHC2_3 * z * h[21] + SHC2_4 * 2.f * x * h[24];
-                gy[c] += SHC2_0 * x * h[12] + SHC2_1 * z * h[15] + SHC2_2 * 2.f * -y * h[18] + SHC2_4 * 2.f * -y * h[24];
-                gz[c] += SHC2_1 * y * h[15] + SHC2_2 * 2.f * 2.f * z * h[18] + SHC2_3 * x * h[21];
-            }
+            const float t4 = SH_T(4), t5 = SH_T(5), t6 = SH_T(6), t7 = SH_T(7), t8 = SH_T(8);
+            ddx += SHC2_0 * y * t4 + SHC2_2 * 2.f * -x * t6 + SHC2_3 * z * t7 + SHC2_4 * 2.f * x * t8;
+            ddy += SHC2_0 * x * t4 + SHC2_1 * z * t5 + SHC2_2 * 2.f * -y * t6 + SHC2_4 * 2.f * -y * t8;
+            ddz += SHC2_1 * y * t5 + SHC2_2 * 2.f * 2.f * z * t6 + SHC2_3 * x * t7;
             if (deg > 2) {
                 w[9] = SHC3_0 * y * (3.f * xx - yy); w[10] = SHC3_1 * xy * z; w[11] = SHC3_2 * y * (4.f * zz - xx - yy);
                 w[12] = SHC3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy); w[13] = SHC3_4 * x * (4.f * zz - xx - yy);
                 w[14] = SHC3_5 * z * (xx - yy); w[15] = SHC3_6 * x * (xx - 3.f * yy);
-#pragma unroll
-                for (int c = 0; c < 3; c++) {
-                    const float* h = sh + c;
-                    gx[c] += SHC3_0 * h[27] * 3.f * 2.f * xy + SHC3_1 * h[30] * yz + SHC3_2 * h[33] * -2.f * xy +
-                             SHC3_3 * h[36] * -3.f * 2.f * xz + SHC3_4 * h[39] * (-3.f * xx + 4.f * zz - yy) +
-                             SHC3_5 * h[42] * 2.f * xz + SHC3_6 * h[45] * 3.f * (xx - yy);
-                    gy[c] += SHC3_0 * h[27] * 3.f * (xx - yy) + SHC3_1 * h[30] * xz + SHC3_2 * h[33] * (-3.f * yy + 4.f * zz - xx) +
-                             SHC3_3 * h[36] * -3.f * 2.f * yz + SHC3_4 * h[39] * -2.f * xy + SHC3_5 * h[42] * -2.f * yz +
-                             SHC3_6 * h[45] * -3.f * 2.f * xy;
-                    gz[c] += SHC3_1 * h[30] * xy + SHC3_2 * h[33] * 4.f * 2.f * yz + SHC3_3 * h[36] * 3.f * (2.f * zz - xx - yy) +
-                             SHC3_4 * h[39] * 4.f * 2.f * xz + SHC3_5 * h[42] * (xx - yy);
-                }
+                const float t9 = SH_T(9), t10 = SH_T(10), t11 = SH_T(11), t12 = SH_T(12), t13 = SH_T(13), t14 = SH_T(14), t15 = SH_T(15);
+                ddx += SHC3_0 * t9 * 3.f * 2.f * xy + SHC3_1 * t10 * yz + SHC3_2 * t11 * -2.f * xy +
+                       SHC3_3 * t12 * -3.f * 2.f * xz + SHC3_4 * t13 * (-3.f * xx + 4.f * zz - yy) +
+                       SHC3_5 * t14 * 2.f * xz + SHC3_6 * t15 * 3.f * (xx - yy);
+                ddy += SHC3_0 * t9 * 3.f * (xx - yy) + SHC3_1 * t10 * xz + SHC3_2 * t11 * (-3.f * yy + 4.f * zz - xx) +
+                       SHC3_3 * t12 * -3.f * 2.f * yz + SHC3_4 * t13 * -2.f * xy + SHC3_5 * t14 * -2.f * yz +
+                       SHC3_6 * t15 * -3.f * 2.f * xy;
+                ddz += SHC3_1 * t10 * xy + SHC3_2 * t11 * 4.f * 2.f * yz + SHC3_3 * t12 * 3.f * (2.f * zz - xx - yy) +
+                       SHC3_4 * t13 * 4.f * 2.f * xz + SHC3_5 * t14 * (xx - yy);
             }
         }
     }
-#pragma unroll
-    for (int k = 0; k < 16; k++) { dsh[3 * k] = w[k] * d[0]; dsh[3 * k + 1] = w[k] * d[1]; dsh[3 * k + 2] = w[k] * d[2]; }
-    const float ddx = gx[0] * d[0] + gx[1] * d[1] + gx[2] * d[2];
-    const float ddy = gy[0] * d[0] + gy[1] * d[1] + gy[2] * d[2];
-    const float ddz = gz[0] * d[0] + gz[1] * d[1] + gz[2] * d[2];
+#undef SH_T
     const float sum2 = ox * ox + oy * oy + oz * oz;                     // dnormvdv, auxiliary.h:119-129
     const float inv32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
     dmx += ((+sum2 - ox * ox) * ddx - oy * ox * ddy - oz * ox * ddz) * inv32;
     dmy += (-ox * oy * ddx + (sum2 - oy * oy) * ddy - oz * oy * ddz) * inv32;
     dmz += (-ox * oz * ddx - oy * oz * ddy + (sum2 - oz * oz) * ddz) * inv32;
 }
+
+struct StageRow {   // element i of the lane's row in the swizzled stage
+    const float* base; int swz;
+    __device__ __forceinline__ float operator()(int i) const { return base[(((i >> 2) ^ swz) << 2) + (i & 3)]; }
+};
+struct GlobalRow {
+    const float* row; int limit;
+    __device__ __forceinline__ float operator()(int i) const { return i < limit ? row[i] : 0.0f; }
+};
 
 template <bool SH16>
 __global__ void __launch_bounds__(PB_THREADS)
@@ -209,9 +214,9 @@ preprocess_bwd_kernel(BwdParams p, GeomView g) {
             const unsigned vmask = __ballot_sync(0xffffffffu, vis);
             float4* st = stage + warp * 384;
             const size_t warp_first = (size_t)blockIdx.x * PB_THREADS + (size_t)warp * 32;
-            float dsh[48];
+            float w[16], d[3] = { 0.0f, 0.0f, 0.0f };
 #pragma unroll
-            for (int k = 0; k < 48; k++) dsh[k] = 0.0f;
+            for (int k = 0; k < 16; k++) w[k] = 0.0f;
             if (vmask) {
                 const float4* src = reinterpret_cast<const float4*>(p.shs) + warp_first * 12;
                 if (p.D > 0) {                    // degree 0 needs no coefficients
@@ -224,41 +229,45 @@ preprocess_bwd_kernel(BwdParams p, GeomView g) {
                     __syncwarp();
                 }
                 if (vis) {
-                    float sh[48];
-#pragma unroll
-                    for (int j = 0; j < 12; j++) {
-                        float4 v = make_float4(0, 0, 0, 0);
-                        if (p.D > 0) v = st[lane * 12 + (j ^ ((lane >> 1) & 3))];
-                        sh[4 * j] = v.x; sh[4 * j + 1] = v.y; sh[4 * j + 2] = v.z; sh[4 * j + 3] = v.w;
-                    }
+                    const StageRow E = { reinterpret_cast<const float*>(st + lane * 12), (lane >> 1) & 3 };
                     const float dr = p.dL_dcolor[3 * (size_t)i], dg = p.dL_dcolor[3 * (size_t)i + 1], db = p.dL_dcolor[3 * (size_t)i + 2];
-                    sh_backward(p.D, sh, mx - cam[32], my - cam[33], mz - cam[34], g.clamped[i], dr, dg, db, dsh, dmx, dmy, dmz);
+                    sh_backward(p.D, E, mx - cam[32], my - cam[33], mz - cam[34], g.clamped[i], dr, dg, db, w, d, dmx, dmy, dmz);
                 }
                 __syncwarp();
             }
-            // every row of the warp is written: values for visible Gaussians, zeros otherwise
-#pragma unroll
-            for (int j = 0; j < 12; j++)
-                st[lane * 12 + (j ^ ((lane >> 1) & 3))] = make_float4(dsh[4 * j], dsh[4 * j + 1], dsh[4 * j + 2], dsh[4 * j + 3]);
-            __syncwarp();
+            // every row of the warp is written: w_k * dL_dRGB_c for visible Gaussians, zeros otherwise
             float4* dst = reinterpret_cast<float4*>(p.dL_dsh) + warp_first * 12;
+            if (vmask) {
 #pragma unroll
-            for (int it = 0; it < 12; it++) {
-                const int f = it * 32 + lane;
-                const int row = f / 12, j = f - row * 12;
-                if (warp_first + row < (size_t)p.P) stg_stream_f4(dst + f, st[row * 12 + (j ^ ((row >> 1) & 3))]);
+                for (int j = 0; j < 12; j++)
+                    st[lane * 12 + (j ^ ((lane >> 1) & 3))] =
+                        make_float4(w[(4 * j) / 3] * d[(4 * j) % 3], w[(4 * j + 1) / 3] * d[(4 * j + 1) % 3],
+                                    w[(4 * j + 2) / 3] * d[(4 * j + 2) % 3], w[(4 * j + 3) / 3] * d[(4 * j + 3) % 3]);
+                __syncwarp();
+#pragma unroll
+                for (int it = 0; it < 12; it++) {
+                    const int f = it * 32 + lane;
+                    const int row = f / 12, j = f - row * 12;
+                    if (warp_first + row < (size_t)p.P) stg_stream_f4(dst + f, st[row * 12 + (j ^ ((row >> 1) & 3))]);
+                }
+            } else {                              // a fully culled warp: 6 KB of zeros, no staging
+                const float4 z4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll
+                for (int it = 0; it < 12; it++) {
+                    const int f = it * 32 + lane;
+                    if (warp_first + f / 12 < (size_t)p.P) stg_stream_f4(dst + f, z4);
+                }
             }
         } else if (in) {
             float* drow = p.dL_dsh + (size_t)i * p.M * 3;
             if (vis) {
-                float sh[48], dsh[48];
-                const float* row = p.shs + (size_t)i * p.M * 3;
-#pragma unroll
-                for (int k = 0; k < 48; k++) sh[k] = (k < 3 * p.M) ? row[k] : 0.0f;
+                float w[16], d[3];
+                const GlobalRow E = { p.shs + (size_t)i * p.M * 3, 3 * p.M };
                 const float dr = p.dL_dcolor[3 * (size_t)i], dg = p.dL_dcolor[3 * (size_t)i + 1], db = p.dL_dcolor[3 * (size_t)i + 2];
-                sh_backward(p.D, sh, mx - cam[32], my - cam[33], mz - cam[34], g.clamped[i], dr, dg, db, dsh, dmx, dmy, dmz);
+                sh_backward(p.D, E, mx - cam[32], my - cam[33], mz - cam[34], g.clamped[i], dr, dg, db, w, d, dmx, dmy, dmz);
 #pragma unroll
-                for (int k = 0; k < 48; k++) if (k < 3 * p.M) drow[k] = dsh[k];
+                for (int k = 0; k < 16; k++)
+                    if (k < p.M) { drow[3 * k] = w[k] * d[0]; drow[3 * k + 1] = w[k] * d[1]; drow[3 * k + 2] = w[k] * d[2]; }
             } else {
                 for (int k = 0; k < 3 * p.M; k++) drow[k] = 0.0f;
             }

@@ -91,36 +91,54 @@ __device__ __forceinline__ void cov2d_ewa(float x, float y, float z, float fx, f
 #define SHC3_5 1.445305721320277f
 #define SHC3_6 -0.5900435899266435f
 
-// colour from an SH row held in registers: sh[k*3+c]  (forward.cu:20-71)
-__device__ __forceinline__ void sh_to_rgb(int deg, const float* sh, float dx, float dy, float dz,
+// Colour from an SH row (forward.cu:20-71).  `E(i)` yields element i = k*3+c of the row; the row is
+// streamed (from the swizzled shared-memory stage, or from global for generic M) band by band so
+// that no 48-float register array is ever live, and coefficients above the active degree are
+// never touched (they may hold anything).
+template <typename Row>
+__device__ __forceinline__ void sh_to_rgb(int deg, const Row& E, float dx, float dy, float dz,
                                           float& r, float& g, float& b, unsigned& clamp_bits) {
     const float len = sqrtf(fmaf(dz, dz, fmaf(dx, dx, dy * dy)));
     const float x = dx / len, y = dy / len, z = dz / len;
     float res[3];
 #pragma unroll
-    for (int c = 0; c < 3; c++) {
-        float v = SHC0 * sh[c];
-        if (deg > 0) {
-            v = v - SHC1 * y * sh[3 + c] + SHC1 * z * sh[6 + c] - SHC1 * x * sh[9 + c];
-            if (deg > 1) {
-                const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-                v = v + SHC2_0 * xy * sh[12 + c] + SHC2_1 * yz * sh[15 + c] +
-                    SHC2_2 * (2.0f * zz - xx - yy) * sh[18 + c] + SHC2_3 * xz * sh[21 + c] +
-                    SHC2_4 * (xx - yy) * sh[24 + c];
-                if (deg > 2) {
-                    v = v + SHC3_0 * y * (3.0f * xx - yy) * sh[27 + c] + SHC3_1 * xy * z * sh[30 + c] +
-                        SHC3_2 * y * (4.0f * zz - xx - yy) * sh[33 + c] +
-                        SHC3_3 * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * sh[36 + c] +
-                        SHC3_4 * x * (4.0f * zz - xx - yy) * sh[39 + c] + SHC3_5 * z * (xx - yy) * sh[42 + c] +
-                        SHC3_6 * x * (xx - 3.0f * yy) * sh[45 + c];
-                }
+    for (int c = 0; c < 3; c++) res[c] = SHC0 * E(c);
+    if (deg > 0) {
+#pragma unroll
+        for (int c = 0; c < 3; c++) res[c] = res[c] - SHC1 * y * E(3 + c) + SHC1 * z * E(6 + c) - SHC1 * x * E(9 + c);
+        if (deg > 1) {
+            const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+#pragma unroll
+            for (int c = 0; c < 3; c++)
+                res[c] = res[c] + SHC2_0 * xy * E(12 + c) + SHC2_1 * yz * E(15 + c) +
+                         SHC2_2 * (2.0f * zz - xx - yy) * E(18 + c) + SHC2_3 * xz * E(21 + c) +
+                         SHC2_4 * (xx - yy) * E(24 + c);
+            if (deg > 2) {
+#pragma unroll
+                for (int c = 0; c < 3; c++)
+                    res[c] = res[c] + SHC3_0 * y * (3.0f * xx - yy) * E(27 + c) + SHC3_1 * xy * z * E(30 + c) +
+                             SHC3_2 * y * (4.0f * zz - xx - yy) * E(33 + c) +
+                             SHC3_3 * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * E(36 + c) +
+                             SHC3_4 * x * (4.0f * zz - xx - yy) * E(39 + c) + SHC3_5 * z * (xx - yy) * E(42 + c) +
+                             SHC3_6 * x * (xx - 3.0f * yy) * E(45 + c);
             }
         }
-        res[c] = v + 0.5f;
     }
+#pragma unroll
+    for (int c = 0; c < 3; c++) res[c] += 0.5f;
     clamp_bits = (res[0] < 0.0f ? 1u : 0u) | (res[1] < 0.0f ? 2u : 0u) | (res[2] < 0.0f ? 4u : 0u);
     r = fmaxf(res[0], 0.0f); g = fmaxf(res[1], 0.0f); b = fmaxf(res[2], 0.0f);
 }
+
+// element i of lane's row in the swizzled stage (float index (row*12 + (j ^ swz))*4 + i%4)
+struct StageRow {
+    const float* base; int swz;
+    __device__ __forceinline__ float operator()(int i) const { return base[(((i >> 2) ^ swz) << 2) + (i & 3)]; }
+};
+struct GlobalRow {
+    const float* row; int limit;
+    __device__ __forceinline__ float operator()(int i) const { return i < limit ? row[i] : 0.0f; }
+};
 
 template <bool SH16>
 __global__ void __launch_bounds__(PRE_THREADS)
@@ -207,23 +225,14 @@ preprocess_fwd_kernel(FwdParams p, GeomView g, int* __restrict__ radii) {
                 }
                 __syncwarp();
                 if (visible) {
-                    float sh[48];
-#pragma unroll
-                    for (int j = 0; j < 12; j++) {
-                        const float4 v = st[lane * 12 + (j ^ ((lane >> 1) & 3))];
-                        sh[4 * j] = v.x; sh[4 * j + 1] = v.y; sh[4 * j + 2] = v.z; sh[4 * j + 3] = v.w;
-                    }
-                    sh_to_rgb(p.D, sh, dx, dy, dz, cr, cg, cb, clamp_bits);
+                    const StageRow E = { reinterpret_cast<const float*>(st + lane * 12), (lane >> 1) & 3 };
+                    sh_to_rgb(p.D, E, dx, dy, dz, cr, cg, cb, clamp_bits);
                 }
             }
         } else if (visible) {
             // generic M (1, 4, 9 ...): strided scalar loads of the coefficients the degree uses
-            float sh[48];
-            const int used = (p.D + 1) * (p.D + 1);
-            const float* row = p.shs + (size_t)i * p.M * 3;
-#pragma unroll
-            for (int k = 0; k < 48; k++) sh[k] = (k < 3 * used && k < 3 * p.M) ? row[k] : 0.0f;
-            sh_to_rgb(p.D, sh, dx, dy, dz, cr, cg, cb, clamp_bits);
+            const GlobalRow E = { p.shs + (size_t)i * p.M * 3, 3 * p.M };
+            sh_to_rgb(p.D, E, dx, dy, dz, cr, cg, cb, clamp_bits);
         }
     } else if (visible) {
         cr = p.colors_precomp[3 * (size_t)i]; cg = p.colors_precomp[3 * (size_t)i + 1]; cb = p.colors_precomp[3 * (size_t)i + 2];

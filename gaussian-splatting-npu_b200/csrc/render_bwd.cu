@@ -22,7 +22,7 @@
 #define RB_NV 10     // dcolor r,g,b | dinvdepth | dmean2D x,y | dconic xx,xy | dconic yy | dopacity
 
 template <bool HAS_DEPTH>
-__global__ void __launch_bounds__(RB_THREADS)
+__global__ void __launch_bounds__(RB_THREADS, 4)
 render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                   const float4* __restrict__ records, int W, int H, int gx, const float* __restrict__ background,
                   const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
@@ -46,6 +46,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     const float pxf = (float)px, pyf = (float)py;
     const float tile_x0 = (float)(tx * GSR_TILE), tile_y0 = (float)(ty * GSR_TILE);
     const size_t pix = (size_t)py * W + px, HW = (size_t)H * W;
+    const uint32_t aA = smem_addr(sA), aB = smem_addr(sB), aC = smem_addr(sC);
 
     const uint2 range = ranges[tile];
     const uint32_t last = inside ? n_contrib[pix] : 0u;
@@ -55,8 +56,8 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         dpx0 = dL_dpix[pix]; dpx1 = dL_dpix[HW + pix]; dpx2 = dL_dpix[2 * HW + pix];
         if (HAS_DEPTH) dpd = dL_dinvdepth_pix[pix];
     }
-    const float bg_dot = background[0] * dpx0 + background[1] * dpx1 + background[2] * dpx2;
-    const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+    // background term of dL/dalpha: (-T_final / (1 - alpha)) * sum_c bg_c dL_dpix_c   (backward.cu:612-615)
+    const float nTf_bg = -T_final * (background[0] * dpx0 + background[1] * dpx1 + background[2] * dpx2);
 
     // deepest list position any pixel of this tile blended
     const uint32_t wmax = __reduce_max_sync(0xffffffffu, last);
@@ -102,52 +103,43 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                 while (bits) {
                     const int j = k * 32 + __ffs(bits) - 1;
                     bits &= bits - 1;
-                    const uint32_t pos = remaining - 1 - j;     // 0-based position in the tile's list
-                    float v0 = 0, v1 = 0, v2 = 0, v3 = 0, v4 = 0, v5 = 0, v6 = 0, v7 = 0, w0 = 0, w1 = 0;
-                    bool contrib = false;
-                    if (pos < last) {
-                        const float4 a = sA[j];
-                        const float4 b = sB[j];
-                        const float dx = fsub(a.x, pxf), dy = fsub(a.y, pyf);
-                        const float power = blend_power(dx, dy, a.z, a.w, b.x);
-                        if (power <= 0.0f) {
-                            const float G = expf(power);
-                            const float alpha = fminf(0.99f, fmul(b.y, G));
-                            if (alpha >= 1.0f / 255.0f) {
-                                contrib = true;
-                                const float2 c = sC[j];
-                                T = T / (1.0f - alpha);
-                                const float dch = alpha * T;
-                                float dL_dalpha;
-                                acc_r = last_alpha * last_r + (1.0f - last_alpha) * acc_r; last_r = b.z;
-                                dL_dalpha = (b.z - acc_r) * dpx0;
-                                acc_g = last_alpha * last_g + (1.0f - last_alpha) * acc_g; last_g = b.w;
-                                dL_dalpha += (b.w - acc_g) * dpx1;
-                                acc_b = last_alpha * last_b + (1.0f - last_alpha) * acc_b; last_b = c.x;
-                                dL_dalpha += (c.x - acc_b) * dpx2;
-                                v0 = dch * dpx0; v1 = dch * dpx1; v2 = dch * dpx2;
-                                if (HAS_DEPTH) {
-                                    acc_d = last_alpha * last_d + (1.0f - last_alpha) * acc_d; last_d = c.y;
-                                    dL_dalpha += (c.y - acc_d) * dpd;
-                                    v3 = dch * dpd;
-                                }
-                                dL_dalpha *= T;
-                                last_alpha = alpha;
-                                dL_dalpha += (-T_final / (1.0f - alpha)) * bg_dot;
-                                const float dL_dG = b.y * dL_dalpha;
-                                const float gdx = G * dx, gdy = G * dy;
-                                const float dG_ddelx = -gdx * a.z - gdy * a.w;
-                                const float dG_ddely = -gdy * b.x - gdx * a.w;
-                                v4 = dL_dG * dG_ddelx * ddelx_dx;
-                                v5 = dL_dG * dG_ddely * ddely_dy;
-                                v6 = -0.5f * gdx * dx * dL_dG;
-                                v7 = -0.5f * gdx * dy * dL_dG;
-                                w0 = -0.5f * gdy * dy * dL_dG;
-                                w1 = G * dL_dalpha;
-                            }
-                        }
-                    }
+                    // Straight-line body.  A lane whose pixel does not blend this Gaussian runs the same
+                    // arithmetic with alpha := 0 and G := 0, which leaves its recurrences bit-identical
+                    // (a zero-alpha layer: T/(1-0) = T, acc + 0*(c-acc) = acc at the next step) and makes
+                    // all ten of its partial sums exactly 0 -- no divergence, no zero-initialisation.
+                    const float4 a = lds_f4(aA + 16u * j);
+                    const float4 b = lds_f4(aB + 16u * j);
+                    const float dx = fsub(a.x, pxf), dy = fsub(a.y, pyf);
+                    const float power = blend_power(dx, dy, a.z, a.w, b.x);
+                    const float G = expf(power);
+                    const float alpha = fminf(0.99f, fmul(b.y, G));
+                    const bool contrib = (remaining - 1 - (uint32_t)j < last) && !(power > 0.0f) && (alpha >= 1.0f / 255.0f);
                     if (!__any_sync(0xffffffffu, contrib)) continue;
+                    const float2 c = lds_f2(aC + 8u * j);
+                    const float al = contrib ? alpha : 0.0f;
+                    const float Gc = contrib ? G : 0.0f;
+                    const float inv = rcp_approx(1.0f - al);      // exactly 1 for al == 0
+                    T *= inv;
+                    const float dch = al * T;
+                    acc_r = fmaf(last_alpha, last_r - acc_r, acc_r); last_r = b.z;
+                    acc_g = fmaf(last_alpha, last_g - acc_g, acc_g); last_g = b.w;
+                    acc_b = fmaf(last_alpha, last_b - acc_b, acc_b); last_b = c.x;
+                    float dL_dalpha = (b.z - acc_r) * dpx0;
+                    dL_dalpha = fmaf(b.w - acc_g, dpx1, dL_dalpha);
+                    dL_dalpha = fmaf(c.x - acc_b, dpx2, dL_dalpha);
+                    float v0 = dch * dpx0, v1 = dch * dpx1, v2 = dch * dpx2, v3 = 0.0f;
+                    if (HAS_DEPTH) {
+                        acc_d = fmaf(last_alpha, last_d - acc_d, acc_d); last_d = c.y;
+                        dL_dalpha = fmaf(c.y - acc_d, dpd, dL_dalpha);
+                        v3 = dch * dpd;
+                    }
+                    last_alpha = al;
+                    dL_dalpha = fmaf(dL_dalpha, T, nTf_bg * inv);
+                    // moments of w = G dL/dalpha over the warp's pixels; the per-Gaussian factors
+                    // (opacity, conic, -0.5, 0.5 W, 0.5 H) are applied once when the batch retires
+                    float w1 = Gc * dL_dalpha;
+                    float v4 = w1 * dx, v5 = w1 * dy;
+                    float v6 = v4 * dx, v7 = v4 * dy, w0 = v5 * dy;
                     // transposing butterfly: 8 values -> each lane ends with the warp total of value (lane>>2)
                     {
                         const bool h = lane & 16;
@@ -183,19 +175,26 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
             }
         }
         __syncthreads();
-        // retire the batch: one global atomic per value and Gaussian
+        // retire the batch: one global atomic per value and Gaussian.  sAcc holds, per Gaussian,
+        // [0..3] sum dch*dL_dpix (r,g,b,invdepth) | [4] S_x = sum w dx | [5] S_y = sum w dy |
+        // [6] S_xx | [7] S_xy | [8] S_yy | [9] S_w, with w = G dL/dalpha.  backward.cu:593-635:
+        //   dL_dmean2D.x = sum dL_dG dG_ddelx 0.5W, dL_dG = o dL_dalpha, dG_ddelx = -G (dx A + dy B)
         if (tid < n && sMask[tid]) {
             const uint32_t id = sId[tid];
             float* a = &sAcc[tid * RB_NV];
+            const float4 ra = sA[tid]; const float4 rb = sB[tid];
+            const float nho = -0.5f * rb.y;                       // -0.5 * opacity
+            const float mx = nho * (float)W * (ra.z * a[4] + ra.w * a[5]);
+            const float my = nho * (float)H * (rb.x * a[5] + ra.w * a[4]);
             if (a[0] != 0.0f) atomicAdd(&dL_dcolor[3 * (size_t)id], a[0]);
             if (a[1] != 0.0f) atomicAdd(&dL_dcolor[3 * (size_t)id + 1], a[1]);
             if (a[2] != 0.0f) atomicAdd(&dL_dcolor[3 * (size_t)id + 2], a[2]);
             if (HAS_DEPTH && a[3] != 0.0f) atomicAdd(&dL_dinvdepth[id], a[3]);
-            if (a[4] != 0.0f) atomicAdd(&dL_dmean2D[3 * (size_t)id], a[4]);
-            if (a[5] != 0.0f) atomicAdd(&dL_dmean2D[3 * (size_t)id + 1], a[5]);
-            if (a[6] != 0.0f) atomicAdd(&dL_dconic[4 * (size_t)id], a[6]);
-            if (a[7] != 0.0f) atomicAdd(&dL_dconic[4 * (size_t)id + 1], a[7]);
-            if (a[8] != 0.0f) atomicAdd(&dL_dconic[4 * (size_t)id + 3], a[8]);
+            if (mx != 0.0f) atomicAdd(&dL_dmean2D[3 * (size_t)id], mx);
+            if (my != 0.0f) atomicAdd(&dL_dmean2D[3 * (size_t)id + 1], my);
+            if (a[6] != 0.0f) atomicAdd(&dL_dconic[4 * (size_t)id], nho * a[6]);
+            if (a[7] != 0.0f) atomicAdd(&dL_dconic[4 * (size_t)id + 1], nho * a[7]);
+            if (a[8] != 0.0f) atomicAdd(&dL_dconic[4 * (size_t)id + 3], nho * a[8]);
             if (a[9] != 0.0f) atomicAdd(&dL_dopacity[id], a[9]);
 #pragma unroll
             for (int k = 0; k < RB_NV; k++) a[k] = 0.0f;

@@ -38,6 +38,8 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     const float pxf = (float)px, pyf = (float)py;
     const float tile_x0 = (float)(tx * GSR_TILE), tile_y0 = (float)(ty * GSR_TILE);
 
+    const uint32_t aA = smem_addr(sA), aB = smem_addr(sB), aC = smem_addr(sC);
+
     const uint2 range = ranges[tile];
     const int todo = (int)(range.y - range.x);
 
@@ -72,23 +74,26 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
             while (bits) {
                 const int j = k * 32 + __ffs(bits) - 1;
                 bits &= bits - 1;
-                if (done) continue;
-                const float4 a = sA[j];
-                const float4 b = sB[j];
+                // Straight-line body: a lane that does not blend this Gaussian runs the same arithmetic
+                // with alpha := 0, which leaves C, T bit-identical (C + (c*0)*T = C, T unchanged).
+                const float4 a = lds_f4(aA + 16u * j);
+                const float4 b = lds_f4(aB + 16u * j);
+                const float2 c = lds_f2(aC + 8u * j);
                 const float dx = fsub(a.x, pxf), dy = fsub(a.y, pyf);
                 const float power = blend_power(dx, dy, a.z, a.w, b.x);
-                if (power > 0.0f) continue;
                 const float alpha = fminf(0.99f, fmul(b.y, expf(power)));
-                if (alpha < 1.0f / 255.0f) continue;
+                const bool contrib = !done && !(power > 0.0f) && (alpha >= 1.0f / 255.0f);
                 const float test_T = fmul(T, fsub(1.0f, alpha));
-                if (test_T < 0.0001f) { done = true; continue; }
-                const float2 c = sC[j];
-                C0 = ffma(fmul(b.z, alpha), T, C0);
-                C1 = ffma(fmul(b.w, alpha), T, C1);
-                C2 = ffma(fmul(c.x, alpha), T, C2);
-                Dacc = ffma(fmul(c.y, alpha), T, Dacc);
-                T = test_T;
-                last = (uint32_t)(base + j + 1);
+                const bool stop = contrib && (test_T < 0.0001f);     // forward.cu:366-371: not blended
+                const bool blend = contrib && !stop;
+                done = done || stop;
+                const float al = blend ? alpha : 0.0f;
+                C0 = ffma(fmul(b.z, al), T, C0);
+                C1 = ffma(fmul(b.w, al), T, C1);
+                C2 = ffma(fmul(c.x, al), T, C2);
+                Dacc = ffma(fmul(c.y, al), T, Dacc);
+                T = blend ? test_T : T;
+                last = blend ? (uint32_t)(base + j + 1) : last;
             }
             if (__all_sync(0xffffffffu, done)) break;
         }
