@@ -12,7 +12,7 @@
 
 static thread_local char tl_error[512] = "";
 static thread_local int tl_profiling = 0;
-static thread_local float tl_stage_ms[10] = { -1, -1, -1, -1, -1, -1, -1, -1, -1, -1 };
+static thread_local float tl_stage_ms[12] = { -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1 };
 
 static int fail(int code, const char* fmt, ...) {
     va_list ap; va_start(ap, fmt);
@@ -36,24 +36,31 @@ static inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
 extern "C" const char* gsr_last_error(void) { return tl_error; }
 extern "C" const char* gsr_version(void) { return "gsr_b200 0.1 (sm_100a)"; }
 extern "C" void gsr_set_profiling(int enabled) { tl_profiling = enabled; }
-extern "C" float gsr_last_stage_ms(int stage) { return (stage >= 0 && stage < 10) ? tl_stage_ms[stage] : -1.0f; }
+extern "C" float gsr_last_stage_ms(int stage) { return (stage >= 0 && stage < 12) ? tl_stage_ms[stage] : -1.0f; }
 
 // ---- scratch layouts ------------------------------------------------------------------------------
-extern "C" void gsr_get_geometry_layout(int P, gsr_geometry_layout* o) {
+// Internal geometry layout = the public one + the depth-sort ping-pong buffers and scan state.
+struct GeomInternal { gsr_geometry_layout pub; size_t gkeys[2], gvals_b, gsort_temp, scan_state; };
+static GeomInternal geom_layout(int P) {
+    GeomInternal g; gsr_geometry_layout* o = &g.pub;
     size_t off = 0; const size_t p = (size_t)(P > 0 ? P : 0);
-    o->depths = off;        off = up256(off + p * 4);
-    o->records = off;       off = up256(off + p * GSR_REC_FLOATS * 4);
-    o->cov3D = off;         off = up256(off + p * 6 * 4);
-    o->clamped = off;       off = up256(off + p);
-    o->tiles_touched = off; off = up256(off + p * 4);
-    o->point_offsets = off; off = up256(off + p * 4);
-    /* scan state */        off = up256(off + gsr_scan_state_words(p) * 4);
+    o->depths = off;         off = up256(off + p * 4);
+    o->records = off;        off = up256(off + p * GSR_REC_FLOATS * 4);
+    o->cov3D = off;          off = up256(off + p * 6 * 4);
+    o->clamped = off;        off = up256(off + p);
+    o->tiles_touched = off;  off = up256(off + p * 4);
+    o->point_offsets = off;  off = up256(off + p * 4);
+    o->depth_order = off;    off = up256(off + p * 4);     // = depth-sort values, buffer (a)
+    o->sorted_offsets = off; off = up256(off + p * 4);
+    g.gkeys[0] = off;        off = up256(off + p * 4);
+    g.gkeys[1] = off;        off = up256(off + p * 4);
+    g.gvals_b = off;         off = up256(off + p * 4);
+    g.gsort_temp = off;      off = up256(off + sort_temp_bytes(p));
+    g.scan_state = off;      off = up256(off + gsr_scan_state_words(p) * 4);
     o->total = off + 256;
+    return g;
 }
-static size_t geom_scan_state_offset(int P) {
-    gsr_geometry_layout l; gsr_get_geometry_layout(P, &l);
-    return up256(l.point_offsets + (size_t)(P > 0 ? P : 0) * 4);
-}
+extern "C" void gsr_get_geometry_layout(int P, gsr_geometry_layout* o) { *o = geom_layout(P).pub; }
 extern "C" void gsr_get_image_layout(int width, int height, gsr_image_layout* o) {
     const size_t hw = (size_t)width * height;
     const size_t tiles = (size_t)((width + GSR_TILE - 1) / GSR_TILE) * ((height + GSR_TILE - 1) / GSR_TILE);
@@ -66,10 +73,10 @@ extern "C" void gsr_get_image_layout(int width, int height, gsr_image_layout* o)
 extern "C" void gsr_get_binning_layout(size_t n, int width, int height, gsr_binning_layout* o) {
     (void)width; (void)height;
     size_t off = 0;
-    o->keys_unsorted = off;   off = up256(off + n * 8);
-    o->values_unsorted = off; off = up256(off + n * 4);
-    o->keys = off;            off = up256(off + n * 8);
+    o->tile_keys = off;       off = up256(off + n * 4);
     o->point_list = off;      off = up256(off + n * 4);
+    o->tile_keys_alt = off;   off = up256(off + n * 4);
+    o->point_list_alt = off;  off = up256(off + n * 4);
     o->sort_temp = off;       off = up256(off + sort_temp_bytes(n));
     o->total = off + 256;
 }
@@ -81,7 +88,7 @@ static inline char* align_base(char* p) { return (char*)(((uintptr_t)p + 255) & 
 
 static GeomView geom_view(char* base, int P) {
     base = align_base(base);
-    gsr_geometry_layout l; gsr_get_geometry_layout(P, &l);
+    const GeomInternal gi = geom_layout(P); const gsr_geometry_layout& l = gi.pub;
     GeomView g;
     g.depths = (float*)(base + l.depths);
     g.records = (float4*)(base + l.records);
@@ -89,7 +96,14 @@ static GeomView geom_view(char* base, int P) {
     g.clamped = (unsigned char*)(base + l.clamped);
     g.tiles_touched = (uint32_t*)(base + l.tiles_touched);
     g.point_offsets = (uint32_t*)(base + l.point_offsets);
-    g.scan_state = (uint32_t*)(base + geom_scan_state_offset(P));
+    g.depth_order = (uint32_t*)(base + l.depth_order);
+    g.sorted_offsets = (uint32_t*)(base + l.sorted_offsets);
+    g.gsort_keys[0] = (uint32_t*)(base + gi.gkeys[0]);
+    g.gsort_keys[1] = (uint32_t*)(base + gi.gkeys[1]);
+    g.gsort_vals[0] = g.depth_order;
+    g.gsort_vals[1] = (uint32_t*)(base + gi.gvals_b);
+    g.gsort_temp = base + gi.gsort_temp;
+    g.scan_state = (uint32_t*)(base + gi.scan_state);
     return g;
 }
 static ImageView image_view(char* base, int w, int h) {
@@ -105,10 +119,10 @@ static BinningView binning_view(char* base, size_t n, int w, int h) {
     base = align_base(base);
     gsr_binning_layout l; gsr_get_binning_layout(n, w, h, &l);
     BinningView b;
-    b.keys_unsorted = (uint64_t*)(base + l.keys_unsorted);
-    b.values_unsorted = (uint32_t*)(base + l.values_unsorted);
-    b.keys = (uint64_t*)(base + l.keys);
+    b.tile_keys = (uint32_t*)(base + l.tile_keys);
     b.point_list = (uint32_t*)(base + l.point_list);
+    b.tile_keys_alt = (uint32_t*)(base + l.tile_keys_alt);
+    b.point_list_alt = (uint32_t*)(base + l.point_list_alt);
     b.sort_temp = base + l.sort_temp;
     return b;
 }
@@ -121,14 +135,11 @@ static uint32_t higher_msb(uint32_t n) {
     return msb;
 }
 
-void launch_sort_pairs_pingpong(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, size_t n,
-                                int end_bit, char* temp, cudaStream_t s, int* result_in_b);
-
 // ---- stage timers (profiling only) -----------------------------------------------------------------
 struct StageTimer {
-    cudaEvent_t ev[10]; int n = 0; bool on; cudaStream_t s;
+    cudaEvent_t ev[12]; int n = 0; bool on; cudaStream_t s;
     StageTimer(bool enabled, cudaStream_t st) : on(enabled), s(st) { if (on) for (auto& e : ev) cudaEventCreate(&e); }
-    void mark() { if (on && n < 10) cudaEventRecord(ev[n++], s); }
+    void mark() { if (on && n < 12) cudaEventRecord(ev[n++], s); }
     void finish(const int* stage_ids) {
         if (!on) return;
         cudaStreamSynchronize(s);
@@ -188,52 +199,85 @@ extern "C" int gsr_forward(const gsr_forward_args* a, gsr_alloc_fn geom_alloc, v
     launch_preprocess_fwd(p, g, a->radii, stream);
     STAGE_CHECK(a->debug, stream, "preprocess");
     tm.mark();
-    launch_scan(P, g, stream);
+    // depth sort of the visible Gaussians: 32 key bits = 4 passes, an even count, so starting in the
+    // (a) pair makes the sorted indices land in g.depth_order (= gsort_vals[0])
+    const int gsort_bits = 32, gsort_passes = (gsort_bits + 7) / 8;
+    const int g0 = (gsort_passes & 1) ? 1 : 0;
+    launch_scan_compact(P, g, g.gsort_keys[g0], g.gsort_vals[g0], stream);
     STAGE_CHECK(a->debug, stream, "scan");
 
-    // total instance count -> host (the reference's blocking cudaMemcpy, rasterizer_impl.cu:283-284)
+    // instance / visible counts -> host.  The reference blocks in cudaMemcpy here
+    // (rasterizer_impl.cu:283-284); we only record an event and keep the GPU busy with the depth
+    // sort (which needs no host-side sizes) while the host waits for the 12 bytes.
     static thread_local uint32_t* pinned = nullptr;
-    if (!pinned) CUDA_TRY(cudaHostAlloc((void**)&pinned, 64, cudaHostAllocDefault));
-    CUDA_TRY(cudaMemcpyAsync(pinned, g.scan_state + 1, 8, cudaMemcpyDeviceToHost, stream));
+    static thread_local cudaEvent_t counts_ready_dev[64] = {};     // one event per device this thread used
+    int dev_id = 0;
+    CUDA_TRY(cudaGetDevice(&dev_id));
+    if (dev_id < 0 || dev_id >= 64) return fail(GSR_ERR_INVALID, "device ordinal %d out of range", dev_id);
+    if (!pinned) CUDA_TRY(cudaHostAlloc((void**)&pinned, 64, cudaHostAllocPortable));
+    if (!counts_ready_dev[dev_id]) CUDA_TRY(cudaEventCreateWithFlags(&counts_ready_dev[dev_id], cudaEventDisableTiming));
+    cudaEvent_t counts_ready = counts_ready_dev[dev_id];
+    CUDA_TRY(cudaMemcpyAsync(pinned, g.scan_state + 1, 12, cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(cudaEventRecord(counts_ready, stream));
     tm.mark();
-    CUDA_TRY(cudaStreamSynchronize(stream));
+    {
+        int in_b = 0;
+        launch_sort_pairs32_pingpong(g.gsort_keys[g0], g.gsort_vals[g0], g.gsort_keys[1 - g0], g.gsort_vals[1 - g0],
+                                     (size_t)P, g.scan_state + 3, gsort_bits, g.gsort_temp, stream, &in_b);
+        STAGE_CHECK(a->debug, stream, "depth sort");
+    }
+    tm.mark();
+    CUDA_TRY(cudaEventSynchronize(counts_ready));
     const uint32_t trapped = pinned[0];
     const size_t N = pinned[1];
     if (trapped) return fail(GSR_ERR_PREFILTERED, "Point is filtered although prefiltered is set. This shouldn't happen!");
     if (N >= (1u << 30)) return fail(GSR_ERR_INVALID, "num_rendered=%zu exceeds the supported 2^30", N);
     *num_rendered = (int)N;
-    tm.mark();      // host round trip ends here (stage 8 = sync gap)
+    tm.mark();      // host wait ends here (stage 8 = device idle gap, if any)
 
     char* bin_raw = binning_alloc(gsr_binning_bytes(N, W, H), binning_user);
     if (!bin_raw) return fail(GSR_ERR_ALLOC, "binning allocator returned null");
     BinningView b = binning_view(bin_raw, N, W, H);
 
-    const int end_bit = 32 + (int)higher_msb((uint32_t)(gx * gy));
+    const int end_bit = (int)higher_msb((uint32_t)(gx * gy));     // tile-id bits (rasterizer_impl.cu:303)
     const int passes = (end_bit + 7) / 8;
-    // ping-pong: start in whichever buffer pair makes the sorted result land in (keys, point_list)
-    uint64_t* k_start = (passes & 1) ? b.keys_unsorted : b.keys;
-    uint32_t* v_start = (passes & 1) ? b.values_unsorted : b.point_list;
-    uint64_t* k_other = (passes & 1) ? b.keys : b.keys_unsorted;
-    uint32_t* v_other = (passes & 1) ? b.point_list : b.values_unsorted;
+    // ping-pong: start in whichever buffer pair makes the sorted result land in (tile_keys, point_list)
+    uint32_t* k_start = (passes & 1) ? b.tile_keys_alt : b.tile_keys;
+    uint32_t* v_start = (passes & 1) ? b.point_list_alt : b.point_list;
+    uint32_t* k_other = (passes & 1) ? b.tile_keys : b.tile_keys_alt;
+    uint32_t* v_other = (passes & 1) ? b.point_list : b.point_list_alt;
     if (N > 0) {
-        launch_duplicate_keys(P, gx, gy, g, a->radii, k_start, v_start, stream);
+        launch_sorted_scan(P, g, g.depth_order, g.sorted_offsets, stream);
+        launch_emit_tiles(P, gx, gy, g, g.depth_order, g.sorted_offsets, a->radii, k_start, v_start, stream);
         STAGE_CHECK(a->debug, stream, "duplicateWithKeys");
         tm.mark();
         int in_b = 0;
-        launch_sort_pairs_pingpong(k_start, v_start, k_other, v_other, N, end_bit, b.sort_temp, stream, &in_b);
+        launch_sort_pairs32_pingpong(k_start, v_start, k_other, v_other, N, nullptr, end_bit, b.sort_temp, stream, &in_b);
         STAGE_CHECK(a->debug, stream, "radix sort");
         tm.mark();
     } else { tm.mark(); tm.mark(); }
-    launch_tile_ranges(N, b.keys, im.ranges, gx * gy, stream);
+    launch_tile_ranges(N, b.tile_keys, im.ranges, gx * gy, stream);
     STAGE_CHECK(a->debug, stream, "identifyTileRanges");
     tm.mark();
     launch_render_fwd(W, H, gx, gy, im.ranges, b.point_list, g.records, a->background, im.final_T, im.n_contrib,
                       a->out_color, a->out_invdepth, stream);
     STAGE_CHECK(a->debug, stream, "render");
     tm.mark();
-    // marks: start | preprocess | scan+copy | host sync | duplicate | sort | ranges | render
-    static const int ids[] = { 0, 1, 8, 2, 3, 4, 5 };
+    // marks: start | preprocess | scan+copy | depth sort | host wait | scan2+emit | tile sort | ranges | render
+    static const int ids[] = { 0, 1, 9, 8, 2, 3, 4, 5 };
     tm.finish(ids);
+    return GSR_OK;
+}
+
+extern "C" int gsr_materialize_keys(int P, int num_rendered, int width, int height, const char* geom_buffer,
+                                    const char* binning_buffer, uint64_t* out_keys, void* stream_) {
+    if (P < 0 || num_rendered < 0 || width <= 0 || height <= 0) return fail(GSR_ERR_INVALID, "bad sizes");
+    if (num_rendered == 0) return GSR_OK;
+    if (!geom_buffer || !binning_buffer || !out_keys) return fail(GSR_ERR_INVALID, "null argument");
+    GeomView g = geom_view(const_cast<char*>(geom_buffer), P);
+    BinningView b = binning_view(const_cast<char*>(binning_buffer), (size_t)num_rendered, width, height);
+    launch_materialize_keys((size_t)num_rendered, b.tile_keys, b.point_list, g.depths, out_keys, (cudaStream_t)stream_);
+    STAGE_CHECK(0, (cudaStream_t)stream_, "materialize keys");
     return GSR_OK;
 }
 

@@ -143,7 +143,12 @@ struct GeomView {
     unsigned char* clamped;   // [P]
     uint32_t* tiles_touched;  // [P]
     uint32_t* point_offsets;  // [P]
-    uint32_t* scan_state;     // scan tile counter + per-tile status words + error counter
+    uint32_t* depth_order;    // [P] (first P_vis valid): visible Gaussians sorted by depth bits, stable
+    uint32_t* sorted_offsets; // [P] (first P_vis valid): inclusive sum of tiles_touched in depth order
+    uint32_t* gsort_keys[2];  // depth-sort ping-pong keys   (gsort_vals[0] aliases depth_order)
+    uint32_t* gsort_vals[2];
+    char* gsort_temp;
+    uint32_t* scan_state;     // tickets, counters, totals, per-tile status words
 };
 struct ImageView {
     float* final_T;           // [H*W]
@@ -151,10 +156,10 @@ struct ImageView {
     uint2* ranges;            // [T]
 };
 struct BinningView {
-    uint64_t* keys_unsorted;
-    uint32_t* values_unsorted;
-    uint64_t* keys;
-    uint32_t* point_list;
+    uint32_t* tile_keys;      // [N] sorted tile ids
+    uint32_t* point_list;     // [N] sorted Gaussian indices
+    uint32_t* tile_keys_alt;  // ping-pong partners (scratch after the sort)
+    uint32_t* point_list_alt;
     char* sort_temp;
 };
 
@@ -169,15 +174,19 @@ struct FwdParams {
 
 #define GSR_SCAN_ITEMS 4096   // tiles_touched values handled per scan tile
 __host__ __device__ inline size_t gsr_scan_tiles(size_t P) { return (P + GSR_SCAN_ITEMS - 1) / GSR_SCAN_ITEMS; }
-// scan_state words: [0] dynamic tile counter, [1] prefiltered-error counter, [2] total (num_rendered),
-// [3] reserved, [4..4+2*tiles) 64-bit status words
-__host__ __device__ inline size_t gsr_scan_state_words(size_t P) { return 4 + 2 * gsr_scan_tiles(P) + 2; }
+// scan_state words: [0] ticket of scan_compact, [1] prefiltered-error counter, [2] N (num_rendered),
+// [3] P_vis, [4] ticket of sorted_scan, [5..7] reserved, then three arrays of 64-bit status words
+// (instances, visible count, sorted instances), one word per scan tile each
+__host__ __device__ inline size_t gsr_scan_state_words(size_t P) { return 8 + 6 * gsr_scan_tiles(P) + 2; }
 
 void launch_preprocess_fwd(const FwdParams& p, const GeomView& g, int* radii, cudaStream_t s);
-void launch_scan(int P, const GeomView& g, cudaStream_t s);
-void launch_duplicate_keys(int P, int gx, int gy, const GeomView& g, const int* radii,
-                           uint64_t* keys, uint32_t* values, cudaStream_t s);
-void launch_tile_ranges(size_t N, const uint64_t* keys, uint2* ranges, int num_tiles, cudaStream_t s);
+void launch_scan_compact(int P, const GeomView& g, uint32_t* gkeys, uint32_t* gvals, cudaStream_t s);
+void launch_sorted_scan(int P, const GeomView& g, const uint32_t* order, uint32_t* sorted_offsets, cudaStream_t s);
+void launch_emit_tiles(int P, int gx, int gy, const GeomView& g, const uint32_t* order, const uint32_t* sorted_offsets,
+                       const int* radii, uint32_t* keys, uint32_t* values, cudaStream_t s);
+void launch_tile_ranges(size_t N, const uint32_t* tile_keys, uint2* ranges, int num_tiles, cudaStream_t s);
+void launch_materialize_keys(size_t N, const uint32_t* tile_keys, const uint32_t* point_list, const float* depths,
+                             uint64_t* out, cudaStream_t s);
 void launch_render_fwd(int W, int H, int gx, int gy, const uint2* ranges, const uint32_t* point_list,
                        const float4* records, const float* background, float* final_T,
                        uint32_t* n_contrib, float* out_color, float* out_invdepth, cudaStream_t s);
@@ -185,7 +194,13 @@ void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, u
                          cudaStream_t s);
 
 size_t sort_temp_bytes(size_t n);
-// Sorts on bits [0,end_bit). Result lands in keys_out/vals_out; keys_in/vals_in are scratch afterwards.
+// Stable LSD sorts on key bits [0,end_bit), ping-ponging between the (a) and (b) pairs; *result_in_b
+// tells where the result ended.  n_dev (optional): device-side element count <= n_max.
+void launch_sort_pairs_pingpong(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, size_t n,
+                                int end_bit, char* temp, cudaStream_t s, int* result_in_b);
+void launch_sort_pairs32_pingpong(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b, size_t n_max,
+                                  const uint32_t* n_dev, int end_bit, char* temp, cudaStream_t s, int* result_in_b);
+// 64-bit keys, result always in keys_out/vals_out; keys_in/vals_in are scratch afterwards.
 void launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
                        size_t n, int end_bit, char* temp, cudaStream_t s);
 

@@ -38,20 +38,26 @@ size_t sort_temp_bytes(size_t n) {
 #define HIST_THREADS 256
 #define HIST_KPT 8
 
+// n_dev != nullptr: the element count lives on the device (the Gaussian-level depth sort runs before
+// the host knows how many Gaussians are visible); grids are then sized for the upper bound n_max.
+template <typename KeyT>
 __global__ void __launch_bounds__(HIST_THREADS)
-sort_hist_kernel(const uint64_t* __restrict__ keys, size_t n, int num_passes, int end_bit, uint32_t* __restrict__ ghist) {
+sort_hist_kernel(const KeyT* __restrict__ keys, size_t n_host, const uint32_t* __restrict__ n_dev, int num_passes,
+                 int end_bit, uint32_t* __restrict__ ghist) {
     __shared__ uint32_t sh[SORT_MAX_PASSES * RADIX];
+    const size_t n = n_dev ? (size_t)*n_dev : n_host;
     for (int k = threadIdx.x; k < num_passes * RADIX; k += HIST_THREADS) sh[k] = 0;
     __syncthreads();
     const size_t chunk = (size_t)HIST_THREADS * HIST_KPT;
     for (size_t c = blockIdx.x; c * chunk < n; c += gridDim.x) {
         const size_t base = c * chunk + (size_t)threadIdx.x * HIST_KPT;
-        uint64_t k[HIST_KPT];
+        KeyT k[HIST_KPT];
         int cnt = 0;
         if (base + HIST_KPT <= n) {
-            const ulonglong2* src = reinterpret_cast<const ulonglong2*>(keys + base);
+            const uint4* src = reinterpret_cast<const uint4*>(keys + base);      // 16-byte vector loads
+            uint4* dstv = reinterpret_cast<uint4*>(k);
 #pragma unroll
-            for (int j = 0; j < HIST_KPT / 2; j++) { const ulonglong2 q = src[j]; k[2 * j] = q.x; k[2 * j + 1] = q.y; }
+            for (int j = 0; j < (int)(HIST_KPT * sizeof(KeyT) / 16); j++) dstv[j] = src[j];
             cnt = HIST_KPT;
         } else {
 #pragma unroll
@@ -91,24 +97,27 @@ __device__ __forceinline__ void st_volatile_u32(uint32_t* p, uint32_t v) {
     asm volatile("st.volatile.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
 }
 
+template <typename KeyT>
 struct OnesweepSmem {
-    uint64_t keys[SORT_TILE];                 // 32 KB
-    uint32_t vals[SORT_TILE];                 // 16 KB
-    uint32_t warp_hist[SORT_WARPS][RADIX];    //  8 KB : per-warp digit counts -> exclusive warp offsets
+    KeyT keys[SORT_TILE];
+    uint32_t vals[SORT_TILE];
+    uint32_t warp_hist[SORT_WARPS][RADIX];    // per-warp digit counts -> exclusive warp offsets
     uint32_t bin_base[RADIX];                 // exclusive offset of each digit inside the tile
     uint32_t gofs[RADIX];                     // global offset of the digit's first key minus bin_base
     uint32_t scan_tmp[2 * SORT_WARPS];
     uint32_t tile;
 };
 
-__global__ void __launch_bounds__(SORT_THREADS)
-onesweep_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ vin, uint64_t* __restrict__ kout,
-                uint32_t* __restrict__ vout, size_t n, int shift, uint32_t mask, const uint32_t* __restrict__ ghist,
-                uint32_t* counter, uint32_t* status) {
+template <typename KeyT>
+__global__ void __launch_bounds__(SORT_THREADS, sizeof(KeyT) == 8 ? 3 : 4)
+onesweep_kernel(const KeyT* __restrict__ kin, const uint32_t* __restrict__ vin, KeyT* __restrict__ kout,
+                uint32_t* __restrict__ vout, size_t n_host, const uint32_t* __restrict__ n_dev, int shift, uint32_t mask,
+                const uint32_t* __restrict__ ghist, uint32_t* counter, uint32_t* status) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    OnesweepSmem& sm = *reinterpret_cast<OnesweepSmem*>(smem_raw);
+    OnesweepSmem<KeyT>& sm = *reinterpret_cast<OnesweepSmem<KeyT>*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t lt_mask = (1u << lane) - 1;
+    const size_t n = n_dev ? (size_t)*n_dev : n_host;
 
     if (tid == 0) sm.tile = atomicAdd(counter, 1u);
 #pragma unroll
@@ -116,11 +125,12 @@ onesweep_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ v
     __syncthreads();
     const uint32_t tile = sm.tile;
     const size_t tile_base = (size_t)tile * SORT_TILE;
+    if (tile_base >= n) return;                // grid sized for an upper bound (device-side n)
     const uint32_t tile_n = (uint32_t)min((size_t)SORT_TILE, n - tile_base);
     const size_t my_base = tile_base + (size_t)warp * (32 * SORT_IPT) + lane;
 
     // 1. load keys, warp-striped: item i of this warp covers 32 consecutive keys
-    uint64_t key[SORT_IPT];
+    KeyT key[SORT_IPT];
     const bool full = tile_n == SORT_TILE;
     if (full) {
 #pragma unroll
@@ -129,13 +139,14 @@ onesweep_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ v
 #pragma unroll
         for (int i = 0; i < SORT_IPT; i++) {
             const size_t idx = my_base + i * 32;
-            key[i] = (idx < n) ? kin[idx] : ~0ull;
+            key[i] = (idx < n) ? kin[idx] : (KeyT)~(KeyT)0;
         }
     }
 
     // 2. stable in-warp ranking: match_any groups equal digits, the group's first lane bumps the
-    //    warp's counter for that digit, every lane gets (old count + #equal lanes before it)
-    uint16_t rank[SORT_IPT];
+    //    warp's counter for that digit, every lane gets (old count + #equal lanes before it).
+    //    Ranks (< 4096) are packed two per register.
+    uint32_t rank2[SORT_IPT / 2];
     uint32_t* wh = sm.warp_hist[warp];
 #pragma unroll
     for (int i = 0; i < SORT_IPT; i++) {
@@ -146,7 +157,8 @@ onesweep_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ v
         uint32_t old = 0;
         if (lane == leader && valid) { old = wh[d]; wh[d] = old + __popc(peers); }
         old = __shfl_sync(0xffffffffu, old, leader);
-        rank[i] = (uint16_t)(old + __popc(peers & lt_mask));
+        const uint32_t r = old + __popc(peers & lt_mask);
+        if (i & 1) rank2[i >> 1] |= r << 16; else rank2[i >> 1] = r;
         __syncwarp();
     }
     __syncthreads();
@@ -198,7 +210,8 @@ onesweep_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ v
         const size_t idx = my_base + i * 32;
         if (full || idx < n) {
             const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
-            const uint32_t pos = sm.bin_base[d] + wh[d] + rank[i];
+            const uint32_t r = (i & 1) ? (rank2[i >> 1] >> 16) : (rank2[i >> 1] & 0xffffu);
+            const uint32_t pos = sm.bin_base[d] + wh[d] + r;
             sm.keys[pos] = key[i];
             sm.vals[pos] = vin[idx];
         }
@@ -207,7 +220,7 @@ onesweep_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ v
 
     // 7. scatter in sorted runs
     for (uint32_t j = tid; j < tile_n; j += SORT_THREADS) {
-        const uint64_t k = sm.keys[j];
+        const KeyT k = sm.keys[j];
         const uint32_t d = (uint32_t)(k >> shift) & mask;
         const size_t pos = (size_t)(uint32_t)(sm.gofs[d] + j);
         kout[pos] = k;
@@ -215,36 +228,49 @@ onesweep_kernel(const uint64_t* __restrict__ kin, const uint32_t* __restrict__ v
     }
 }
 
-// Returns through *result_in_b whether the sorted data ended in (keys_b, vals_b).
-void launch_sort_pairs_pingpong(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, size_t n,
-                                int end_bit, char* temp, cudaStream_t s, int* result_in_b) {
+// Stable LSD sort of (KeyT key, u32 value) pairs on key bits [0, end_bit), ping-ponging between the
+// (a) and (b) buffer pairs; *result_in_b tells where the sorted data ended.  n_dev (optional) is a
+// device-side element count <= n_max.
+template <typename KeyT>
+void sort_pairs_pingpong_t(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint32_t* vals_b, size_t n_max,
+                           const uint32_t* n_dev, int end_bit, char* temp, cudaStream_t s, int* result_in_b) {
     const int passes = (end_bit + RADIX_BITS - 1) / RADIX_BITS;
     *result_in_b = passes & 1;
-    if (n == 0 || passes == 0) { *result_in_b = 0; return; }
-    const size_t tiles = sort_tiles(n);
+    if (n_max == 0 || passes == 0) { *result_in_b = 0; return; }
+    const size_t tiles = sort_tiles(n_max);
     uint32_t* ghist = reinterpret_cast<uint32_t*>(temp);
     uint32_t* counters = ghist + SORT_MAX_PASSES * RADIX;
     const size_t head = align_up(SORT_MAX_PASSES * RADIX * 4 + 64, 256);
     uint32_t* status = reinterpret_cast<uint32_t*>(temp + head);
     cudaMemsetAsync(temp, 0, head + (size_t)passes * tiles * RADIX * 4, s);
 
-    int hist_blocks = (int)min((size_t)148 * 8, (n + (size_t)HIST_THREADS * HIST_KPT - 1) / ((size_t)HIST_THREADS * HIST_KPT));
-    sort_hist_kernel<<<hist_blocks, HIST_THREADS, 0, s>>>(keys_a, n, passes, end_bit, ghist);
+    int hist_blocks = (int)min((size_t)148 * 8, (n_max + (size_t)HIST_THREADS * HIST_KPT - 1) / ((size_t)HIST_THREADS * HIST_KPT));
+    sort_hist_kernel<KeyT><<<hist_blocks, HIST_THREADS, 0, s>>>(keys_a, n_max, n_dev, passes, end_bit, ghist);
 
-    static bool attr_set = false;
+    static bool attr_set = false;      // per instantiation
     if (!attr_set) {
-        cudaFuncSetAttribute(onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(OnesweepSmem));
+        cudaFuncSetAttribute(onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(OnesweepSmem<KeyT>));
         attr_set = true;
     }
-    uint64_t* kin = keys_a; uint32_t* vin = vals_a; uint64_t* kout = keys_b; uint32_t* vout = vals_b;
+    KeyT* kin = keys_a; uint32_t* vin = vals_a; KeyT* kout = keys_b; uint32_t* vout = vals_b;
     for (int p = 0; p < passes; p++) {
         const int shift = p * RADIX_BITS;
         const uint32_t mask = (end_bit - shift >= RADIX_BITS) ? (RADIX - 1) : ((1u << (end_bit - shift)) - 1);
-        onesweep_kernel<<<(unsigned)tiles, SORT_THREADS, sizeof(OnesweepSmem), s>>>(
-            kin, vin, kout, vout, n, shift, mask, ghist + p * RADIX, counters + p, status + (size_t)p * tiles * RADIX);
-        uint64_t* tk = kin; kin = kout; kout = tk;
+        onesweep_kernel<KeyT><<<(unsigned)tiles, SORT_THREADS, sizeof(OnesweepSmem<KeyT>), s>>>(
+            kin, vin, kout, vout, n_max, n_dev, shift, mask, ghist + p * RADIX, counters + p, status + (size_t)p * tiles * RADIX);
+        KeyT* tk = kin; kin = kout; kout = tk;
         uint32_t* tv = vin; vin = vout; vout = tv;
     }
+}
+
+void launch_sort_pairs_pingpong(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, size_t n,
+                                int end_bit, char* temp, cudaStream_t s, int* result_in_b) {
+    sort_pairs_pingpong_t<uint64_t>(keys_a, vals_a, keys_b, vals_b, n, nullptr, end_bit, temp, s, result_in_b);
+}
+
+void launch_sort_pairs32_pingpong(uint32_t* keys_a, uint32_t* vals_a, uint32_t* keys_b, uint32_t* vals_b, size_t n_max,
+                                  const uint32_t* n_dev, int end_bit, char* temp, cudaStream_t s, int* result_in_b) {
+    sort_pairs_pingpong_t<uint32_t>(keys_a, vals_a, keys_b, vals_b, n_max, n_dev, end_bit, temp, s, result_in_b);
 }
 
 void launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out, size_t n,

@@ -47,11 +47,11 @@ class BackwardArgs(Structure):
 
 class GeometryLayout(Structure):
     _fields_ = [(n, c_size_t) for n in ("depths", "records", "cov3D", "clamped", "tiles_touched",
-                                        "point_offsets", "total")]
+                                        "point_offsets", "depth_order", "sorted_offsets", "total")]
 
 
 class BinningLayout(Structure):
-    _fields_ = [(n, c_size_t) for n in ("keys_unsorted", "values_unsorted", "keys", "point_list",
+    _fields_ = [(n, c_size_t) for n in ("tile_keys", "point_list", "tile_keys_alt", "point_list_alt",
                                         "sort_temp", "total")]
 
 
@@ -61,7 +61,8 @@ class ImageLayout(Structure):
 
 EXPORTS = ["gsr_forward", "gsr_backward", "gsr_mark_visible", "gsr_geometry_bytes", "gsr_image_bytes",
            "gsr_binning_bytes", "gsr_sort_temp_bytes", "gsr_sort_pairs", "gsr_get_geometry_layout",
-           "gsr_get_binning_layout", "gsr_get_image_layout", "gsr_set_profiling", "gsr_last_stage_ms",
+           "gsr_get_binning_layout", "gsr_get_image_layout", "gsr_materialize_keys", "gsr_set_profiling",
+           "gsr_last_stage_ms",
            "gsr_last_error", "gsr_version"]
 
 _lib = None
@@ -95,6 +96,8 @@ def lib():
         L.gsr_get_geometry_layout.argtypes = [c_int, POINTER(GeometryLayout)]
         L.gsr_get_binning_layout.argtypes = [c_size_t, c_int, c_int, POINTER(BinningLayout)]
         L.gsr_get_image_layout.argtypes = [c_int, c_int, POINTER(ImageLayout)]
+        L.gsr_materialize_keys.restype = c_int
+        L.gsr_materialize_keys.argtypes = [c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]
         L.gsr_set_profiling.argtypes = [c_int]
         L.gsr_last_stage_ms.restype = c_float
         L.gsr_last_stage_ms.argtypes = [c_int]
@@ -138,7 +141,7 @@ class _Buf:
 
 
 STAGES = ["preprocess", "scan", "duplicate", "sort", "ranges", "render_fwd", "render_bwd",
-          "preprocess_bwd", "host_sync"]
+          "preprocess_bwd", "host_sync", "depth_sort"]
 
 
 def stage_times_ms():
@@ -245,11 +248,20 @@ def introspect(state):
         ranges=_view(state["img"], il.ranges, T * 2, torch.int32).view(T, 2),
     )
     if N:
-        o["keys"] = _view(state["binning"], bl.keys, N, torch.int64)
+        o["tile_keys"] = _view(state["binning"], bl.tile_keys, N, torch.int32)
         o["point_list"] = _view(state["binning"], bl.point_list, N, torch.int32)
+        # the reference's 64-bit sorted keys, rebuilt on demand (the hot path never materialises them)
+        keys = torch.empty(N, dtype=torch.int64, device=state["geom"].device)
+        _check(L.gsr_materialize_keys(P, N, W, H, c_void_p(state["geom"].data_ptr()), c_void_p(state["binning"].data_ptr()),
+                                      c_void_p(keys.data_ptr()), _stream()))
+        o["keys"] = keys
     else:
+        o["tile_keys"] = torch.empty(0, dtype=torch.int32, device=state["geom"].device)
         o["keys"] = torch.empty(0, dtype=torch.int64, device=state["geom"].device)
         o["point_list"] = torch.empty(0, dtype=torch.int32, device=state["geom"].device)
+    P_vis = int((state["radii"] > 0).sum().item())
+    o["depth_order"] = _view(state["geom"], gl.depth_order, P, torch.int32)[:P_vis]
+    o["sorted_offsets"] = _view(state["geom"], gl.sorted_offsets, P, torch.int32)[:P_vis]
     return o
 
 

@@ -138,7 +138,8 @@ size_t gsr_binning_bytes(size_t num_rendered, int width, int height);
 
 /*
  * Stable LSD radix sort of n (u64 key, u32 value) pairs on key bits [0, end_bit): the hand-written
- * onesweep that replaces cub::DeviceRadixSort::SortPairs (rasterizer_impl.cu:306-311).  `temp` must
+ * onesweep that replaces cub::DeviceRadixSort::SortPairs (rasterizer_impl.cu:306-311) as a
+ * stand-alone primitive (gsr_forward uses the same kernel template on 32-bit keys, twice).  `temp` must
  * hold gsr_sort_temp_bytes(n) bytes.  keys_in/vals_in are clobbered (ping-pong); the result is in
  * keys_out/vals_out.  Exposed so the sort can be tested and timed alone.
  */
@@ -157,14 +158,16 @@ typedef struct gsr_geometry_layout {
     size_t cov3D;         /* f32[P,6] */
     size_t clamped;       /* u8[P]: bit c set <=> colour channel c was clamped */
     size_t tiles_touched; /* u32[P] */
-    size_t point_offsets; /* u32[P] inclusive scan */
+    size_t point_offsets; /* u32[P] inclusive scan (index order, as the reference's) */
+    size_t depth_order;   /* u32[P], first P_vis valid: visible Gaussians in (depth bits, index) order */
+    size_t sorted_offsets;/* u32[P], first P_vis valid: inclusive scan of tiles_touched in depth order */
     size_t total;
 } gsr_geometry_layout;
 typedef struct gsr_binning_layout {
-    size_t keys_unsorted; /* u64[N] ping-pong partner of `keys`   (scratch after the sort) */
-    size_t values_unsorted; /* u32[N] ping-pong partner of `point_list` (scratch after the sort) */
-    size_t keys;          /* u64[N] sorted */
-    size_t point_list;    /* u32[N] sorted values */
+    size_t tile_keys;     /* u32[N] sorted tile ids = high words of the reference's sorted keys */
+    size_t point_list;    /* u32[N] sorted Gaussian indices */
+    size_t tile_keys_alt; /* u32[N] ping-pong partners (scratch after the sort) */
+    size_t point_list_alt;
     size_t sort_temp;
     size_t total;
 } gsr_binning_layout;
@@ -178,10 +181,20 @@ void gsr_get_geometry_layout(int P, gsr_geometry_layout* out);
 void gsr_get_binning_layout(size_t num_rendered, int width, int height, gsr_binning_layout* out);
 void gsr_get_image_layout(int width, int height, gsr_image_layout* out);
 
+/*
+ * Rebuilds the reference's sorted 64-bit keys (tile id << 32 | float bits of depth,
+ * rasterizer_impl.cu:100-104) from the scratch buffers of a forward into out_keys (u64[num_rendered],
+ * device).  The hot path never materialises them: it sorts Gaussians by depth once and instances
+ * by tile id (see DESIGN.md "binning"); this entry point exists for parity tests and debugging.
+ */
+int gsr_materialize_keys(int P, int num_rendered, int width, int height, const char* geom_buffer,
+                         const char* binning_buffer, uint64_t* out_keys, void* stream);
+
 /* Per-stage device times of the calling thread's last gsr_forward/gsr_backward when profiling is
  * enabled with gsr_set_profiling(1) (adds event records + one extra sync; off by default).
- * Stage ids: 0 preprocess, 1 scan, 2 duplicate, 3 sort, 4 ranges, 5 render_fwd,
- *            6 render_bwd, 7 preprocess_bwd, 8 host round trip for num_rendered.
+ * Stage ids: 0 preprocess, 1 scan+compact, 2 duplicate (sorted scan + tile emission), 3 tile sort,
+ *            4 ranges, 5 render_fwd, 6 render_bwd, 7 preprocess_bwd, 8 host wait for num_rendered
+ *            (device idle gap), 9 depth sort of the visible Gaussians.
  * Returns milliseconds or -1. */
 void gsr_set_profiling(int enabled);
 float gsr_last_stage_ms(int stage);

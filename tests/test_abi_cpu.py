@@ -32,13 +32,15 @@ def test_version_and_layouts():
     assert b"sm_100a" in L.gsr_version()
     g = capi.GeometryLayout()
     L.gsr_get_geometry_layout(1000, ctypes.byref(g))
-    offs = [g.depths, g.records, g.cov3D, g.clamped, g.tiles_touched, g.point_offsets, g.total]
+    offs = [g.depths, g.records, g.cov3D, g.clamped, g.tiles_touched, g.point_offsets, g.depth_order,
+            g.sorted_offsets, g.total]
     assert offs == sorted(offs) and all(o % 256 == 0 for o in offs[:-1])
     assert g.records - g.depths >= 4000 and g.cov3D - g.records >= 48000
     assert L.gsr_geometry_bytes(1000) == g.total
     b = capi.BinningLayout()
     L.gsr_get_binning_layout(12345, 640, 360, ctypes.byref(b))
-    assert b.keys - b.keys_unsorted >= 12345 * 8 and b.total == L.gsr_binning_bytes(12345, 640, 360)
+    assert b.point_list - b.tile_keys >= 12345 * 4 and b.sort_temp > b.point_list_alt > b.tile_keys_alt
+    assert b.total == L.gsr_binning_bytes(12345, 640, 360)
     i = capi.ImageLayout()
     L.gsr_get_image_layout(167, 101, ctypes.byref(i))
     assert i.n_contrib - i.final_T >= 167 * 101 * 4 and i.total == L.gsr_image_bytes(167, 101)

@@ -98,10 +98,19 @@ def test_full_size_properties(cuda):
     same = keys[1:] == keys[:-1]
     pl = it["point_list"].to(torch.int64)
     assert bool((pl[1:][same] > pl[:-1][same]).all()), "stability"
-    depth_bits = it["depths"].view(torch.int32)[pl].to(torch.int64) & 0xFFFFFFFF
+    depth_bits_all = it["depths"].view(torch.int32).to(torch.int64) & 0xFFFFFFFF
+    depth_bits = depth_bits_all[pl]
     assert torch.equal(keys & 0xFFFFFFFF, depth_bits), "key low word = depth bits of its Gaussian"
     # checksum: the multiset of (tile, gaussian) instances is what the rects say
     T = ((w["W"] + 15) // 16) * ((w["H"] + 15) // 16)
+    # the binning split: visible Gaussians in (depth bits, index) order, instances emitted in that order
+    vis_idx = torch.nonzero(tiles > 0).flatten()
+    order = it["depth_order"].to(torch.int64)
+    assert order.numel() == vis_idx.numel() and torch.equal(torch.sort(order).values, vis_idx), "depth_order is a permutation of the visible set"
+    dkey = (depth_bits_all[order] << 32) | order
+    assert bool((dkey[1:] > dkey[:-1]).all()), "depth_order sorted by (depth bits, Gaussian index)"
+    assert torch.equal(it["sorted_offsets"].to(torch.int64), torch.cumsum(tiles[order], 0)), "sorted_offsets"
+    assert torch.equal(it["tile_keys"].to(torch.int64), keys >> 32)
     cnt = torch.bincount(keys >> 32, minlength=T)
     r = it["ranges"].to(torch.int64)
     assert torch.equal(r[:, 1] - r[:, 0], cnt)
