@@ -348,16 +348,20 @@ def main():
             cpu = {"value": 1.0 / sec, "unit": "renders/s", "cores": go.num_threads(), "kind": "port",
                    "sample": "one full %dx%d view of %d Gaussians, fwd+bwd, %.1f s" % (W, H, P, sec)}
 
-        passes = (32 + int(np.ceil(np.log2(max(((W + 15) // 16) * ((H + 15) // 16), 2)))) + 7) // 8
+        # binning = depth sort of the P_vis visible Gaussians (32 key bits -> 4 onesweep passes on 32-bit
+        # key/value pairs) + stable tile-id sort of the N instances (tile_bits -> tile_passes passes)
+        tile_bits = max(int(np.ceil(np.log2(((W + 15) // 16) * ((H + 15) // 16) + 1))), 1)
+        tile_passes = (tile_bits + 7) // 8
         def hbm(bytes_, ms_):
             a = bytes_ / (ms_ / 1e3) / 1e9 if ms_ and ms_ > 0 else None
             return {"bound": "hbm", "algorithmic_bytes": int(bytes_), "ms": ms_, "achieved": a, "peak": hbm_peak,
                     "unit": "GB/s", "frac": (a / hbm_peak) if a else None}
         stages = {
             "preprocess": hbm(52 * P + 259 * P_vis, stage_ms.get("preprocess")),
-            "scan": hbm(8 * P, stage_ms.get("scan")),
-            "duplicate": hbm(20 * P_vis + 12 * N, stage_ms.get("duplicate")),
-            "sort": hbm(8 * N + passes * 24 * N, stage_ms.get("sort")),
+            "scan": hbm(8 * P + 12 * P_vis, stage_ms.get("scan")),                       # + compacted depth key/index out
+            "depth_sort": hbm(4 * P_vis + 4 * 16 * P_vis, stage_ms.get("depth_sort")),    # histogram read + 4 x (8 in + 8 out)
+            "duplicate": hbm(40 * P_vis + 8 * N, stage_ms.get("duplicate")),             # sorted scan + emit (32-bit key + value out)
+            "sort": hbm(4 * N + tile_passes * 16 * N, stage_ms.get("sort")),
             "ranges": hbm(8 * N + 8 * ((W + 15) // 16) * ((H + 15) // 16), stage_ms.get("ranges")),
             "preprocess_bwd": hbm(504 * P_vis + 304 * (P - P_vis) * 0 + 236 * P, stage_ms.get("preprocess_bwd")),
         }
@@ -372,13 +376,25 @@ def main():
         else:
             stages["render_fwd"] = fp32(None, stage_ms.get("render_fwd"))
             stages["render_bwd"] = fp32(None, stage_ms.get("render_bwd"))
+        # measured DRAM traffic per launch from the newest committed `ncu --set full` capture of this workload
+        import glob
+        for tf in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json")), reverse=True):
+            with open(tf) as f:
+                tj = json.load(f)
+            if tj.get("workload") == args.workload:
+                for k_, v_ in tj["traffic_bytes"].items():
+                    if k_ in stages:
+                        stages[k_]["traffic"] = v_
+                        stages[k_]["traffic_source"] = "profiles/" + os.path.basename(tf)
+                break
         dominant = max(stage_ms, key=lambda k: stage_ms[k] if k != "host_sync" else -1)
         roof = dict(stages.get(dominant, {}))
         roof["kernel"] = dominant
         roof.setdefault("traffic", None)
 
-        passes_launch = passes
-        launches_per_step = 1 + 1 + 1 + 1 + passes_launch + 1 + 1 + 1 + 1
+        # preprocess, scan_compact, depth sort (hist + 4), sorted_scan, emit_tiles, tile sort (hist + passes),
+        # tile_ranges, render_fwd, render_bwd, preprocess_bwd
+        launches_per_step = 1 + 1 + (1 + 4) + 1 + 1 + (1 + tile_passes) + 1 + 1 + 1 + 1
         out = {
             "metric": "fwd+bwd renders/s", "value": value, "unit": "renders/s", "n_gpus": world, "steps": args.steps,
             "warmup": n_warm, "ms_per_step": ms / args.steps,
