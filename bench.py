@@ -233,13 +233,22 @@ def main():
     # second after context creation (clock/power-state ramp, allocator growth, lazy module loads) ran
     # up to 2x slower than steady state, which a 3-step warm-up of a 3 ms step does not cover
     n_warm, t_w0 = 0, time.perf_counter()
-    while n_warm < max(args.warmup, 3) or (time.perf_counter() - t_w0 < 1.5 and n_warm < 2000):
+    while True:
         st, g = abi_step()
         if world > 1:
             G.allreduce_from(g)
         n_warm += 1
-        if n_warm % 8 == 0:
+        if n_warm % 8 == 0 or n_warm == max(args.warmup, 3):
             torch.cuda.synchronize()
+            # every rank must leave the loop after the same number of steps (each step holds a collective):
+            # the decision is rank-agreed through a MAX all-reduce of "I still want to warm up"
+            more = n_warm < max(args.warmup, 3) or (time.perf_counter() - t_w0 < 1.5 and n_warm < 2000)
+            if world > 1:
+                flag = torch.tensor([1.0 if more else 0.0], device=dev)
+                dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+                more = bool(flag.item() > 0)
+            if not more:
+                break
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     step_ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]

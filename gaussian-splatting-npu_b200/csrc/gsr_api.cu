@@ -123,6 +123,7 @@ static BinningView binning_view(char* base, size_t n, int w, int h) {
     b.point_list = (uint32_t*)(base + l.point_list);
     b.tile_keys_alt = (uint32_t*)(base + l.tile_keys_alt);
     b.point_list_alt = (uint32_t*)(base + l.point_list_alt);
+    b.block_masks = (unsigned char*)b.tile_keys_alt;
     b.sort_temp = base + l.sort_temp;
     return b;
 }
@@ -259,7 +260,7 @@ extern "C" int gsr_forward(const gsr_forward_args* a, gsr_alloc_fn geom_alloc, v
     launch_tile_ranges(N, b.tile_keys, im.ranges, gx * gy, stream);
     STAGE_CHECK(a->debug, stream, "identifyTileRanges");
     tm.mark();
-    launch_render_fwd(W, H, gx, gy, im.ranges, b.point_list, g.records, a->background, im.final_T, im.n_contrib,
+    launch_render_fwd(W, H, gx, gy, im.ranges, b.point_list, b.block_masks, g.records, a->background, im.final_T, im.n_contrib,
                       a->out_color, a->out_invdepth, stream);
     STAGE_CHECK(a->debug, stream, "render");
     tm.mark();
@@ -325,7 +326,7 @@ extern "C" int gsr_backward(const gsr_backward_args* a, void* stream_) {
     CUDA_TRY(cudaMemsetAsync(a->dL_dcolor, 0, sp * 3 * 4, stream));
     if (p.dL_dinvdepth) CUDA_TRY(cudaMemsetAsync(p.dL_dinvdepth, 0, sp * 4, stream));
     if (a->R > 0) {
-        launch_render_bwd(p, im.ranges, b.point_list, g.records, im.final_T, im.n_contrib, stream);
+        launch_render_bwd(p, im.ranges, b.point_list, b.block_masks, g.records, im.final_T, im.n_contrib, stream);
         STAGE_CHECK(a->debug, stream, "render backward");
     }
     tm.mark();

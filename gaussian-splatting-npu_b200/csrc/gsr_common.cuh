@@ -160,6 +160,8 @@ struct BinningView {
     uint32_t* point_list;     // [N] sorted Gaussian indices
     uint32_t* tile_keys_alt;  // ping-pong partners (scratch after the sort)
     uint32_t* point_list_alt;
+    unsigned char* block_masks; // [N] 8x4-block masks of the sorted instances, written by the forward blend, read by
+                                // the backward blend; aliases tile_keys_alt (free once the sort is done)
     char* sort_temp;
 };
 
@@ -188,7 +190,7 @@ void launch_tile_ranges(size_t N, const uint32_t* tile_keys, uint2* ranges, int 
 void launch_materialize_keys(size_t N, const uint32_t* tile_keys, const uint32_t* point_list, const float* depths,
                              uint64_t* out, cudaStream_t s);
 void launch_render_fwd(int W, int H, int gx, int gy, const uint2* ranges, const uint32_t* point_list,
-                       const float4* records, const float* background, float* final_T,
+                       unsigned char* block_masks, const float4* records, const float* background, float* final_T,
                        uint32_t* n_contrib, float* out_color, float* out_invdepth, cudaStream_t s);
 void launch_mark_visible(int P, const float* means3D, const float* viewmatrix, unsigned char* present,
                          cudaStream_t s);
@@ -216,6 +218,6 @@ struct BwdParams {
         *dL_dsh, *dL_dscale, *dL_drot;
 };
 void launch_render_bwd(const BwdParams& p, const uint2* ranges, const uint32_t* point_list,
-                       const float4* records, const float* final_T, const uint32_t* n_contrib,
+                       const unsigned char* block_masks, const float4* records, const float* final_T, const uint32_t* n_contrib,
                        cudaStream_t s);
 void launch_preprocess_bwd(const BwdParams& p, const GeomView& g, cudaStream_t s);

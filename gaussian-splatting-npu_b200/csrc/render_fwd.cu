@@ -12,6 +12,10 @@
 //     (rect_may_contribute): every warp then walks only the staged Gaussians that can reach
 //     alpha >= 1/255 somewhere in its block.  On trained-scene-shaped input ~85% of the
 //     (pixel, Gaussian) evaluations of the reference are of pairs that fail that test;
+//   * the 8-bit block masks are also written to the binning buffer (1 byte per instance) so that the
+//     backward pass does not repeat the nine rectangle tests per instance;
+//   * the stage is double-buffered: ONE CTA barrier per 256-Gaussian batch (it also carries the
+//     "all pixels done" count), and a warp with a short list runs up to a batch ahead;
 //   * the per-pair arithmetic that decides n_contrib (power, alpha, T) is written with exactly
 //     rounded intrinsics in the reference build's FFMA placement; expf is CUDA's, as there --
 //     culling only removes pairs that arithmetic would have rejected, so outputs are bit-identical.
@@ -21,13 +25,13 @@
 
 __global__ void __launch_bounds__(RF_THREADS)
 render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
-                  const float4* __restrict__ records, int W, int H, int gx,
+                  unsigned char* __restrict__ block_masks, const float4* __restrict__ records, int W, int H, int gx,
                   const float* __restrict__ background, float* __restrict__ final_T,
                   uint32_t* __restrict__ n_contrib, float* __restrict__ out_color, float* __restrict__ out_invdepth) {
-    __shared__ float4 sA[RF_THREADS];          // x, y, conic.a, conic.b
-    __shared__ float4 sB[RF_THREADS];          // conic.c, opacity, r, g
-    __shared__ float2 sC[RF_THREADS];          // b, 1/depth
-    __shared__ unsigned char sMask[RF_THREADS];
+    __shared__ float4 sA[2][RF_THREADS];          // x, y, conic.a, conic.b
+    __shared__ float4 sB[2][RF_THREADS];          // conic.c, opacity, r, g
+    __shared__ float2 sC[2][RF_THREADS];          // b, 1/depth
+    __shared__ unsigned char sMask[2][RF_THREADS];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.x;
@@ -37,8 +41,6 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     const bool inside = px < W && py < H;
     const float pxf = (float)px, pyf = (float)py;
     const float tile_x0 = (float)(tx * GSR_TILE), tile_y0 = (float)(ty * GSR_TILE);
-
-    const uint32_t aA = smem_addr(sA), aB = smem_addr(sB), aC = smem_addr(sC);
 
     const uint2 range = ranges[tile];
     const int todo = (int)(range.y - range.x);
@@ -54,23 +56,29 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         nA = rec[0]; nB = rec[1]; nC = rec[2];
     }
 
-    for (int base = 0; base < todo; base += RF_THREADS) {
-        if (__syncthreads_count(done) == RF_THREADS) break;     // also fences reuse of the stage
+    int buf = 0;
+    for (int base = 0; base < todo; base += RF_THREADS, buf ^= 1) {
         const int n = min(RF_THREADS, todo - base);
+        // Writing buffer `buf` is safe: every warp that passed the previous barrier had finished the
+        // batch before it, the last user of `buf`.
         if (tid < n) {
-            sA[tid] = nA; sB[tid] = nB; sC[tid] = make_float2(nC.x, nC.y);
-            sMask[tid] = (unsigned char)subblock_mask(make_cull(nA.x, nA.y, nA.z, nA.w, nB.x, nB.y), tile_x0, tile_y0);
+            sA[buf][tid] = nA; sB[buf][tid] = nB; sC[buf][tid] = make_float2(nC.x, nC.y);
+            const unsigned m = subblock_mask(make_cull(nA.x, nA.y, nA.z, nA.w, nB.x, nB.y), tile_x0, tile_y0);
+            sMask[buf][tid] = (unsigned char)m;
+            block_masks[(size_t)range.x + base + tid] = (unsigned char)m;
         }
-        __syncthreads();
+        if (__syncthreads_count(done) == RF_THREADS) break;
         if (base + RF_THREADS + tid < todo) {
             const float4* rec = records + 3 * (size_t)point_list[range.x + base + RF_THREADS + tid];
             nA = rec[0]; nB = rec[1]; nC = rec[2];
         }
+        const uint32_t aA = smem_addr(sA[buf]), aB = smem_addr(sB[buf]), aC = smem_addr(sC[buf]);
+        const unsigned char* masks = sMask[buf];
         if (__all_sync(0xffffffffu, done)) continue;           // this warp's 32 pixels are saturated
 #pragma unroll 1
         for (int k = 0; k < RF_THREADS / 32; k++) {
             const int idx = k * 32 + lane;
-            unsigned bits = __ballot_sync(0xffffffffu, idx < n && ((sMask[idx] >> warp) & 1));
+            unsigned bits = __ballot_sync(0xffffffffu, idx < n && ((masks[idx] >> warp) & 1));
             while (bits) {
                 const int j = k * 32 + __ffs(bits) - 1;
                 bits &= bits - 1;
@@ -111,8 +119,8 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
 }
 
 void launch_render_fwd(int W, int H, int gx, int gy, const uint2* ranges, const uint32_t* point_list,
-                       const float4* records, const float* background, float* final_T, uint32_t* n_contrib,
+                       unsigned char* block_masks, const float4* records, const float* background, float* final_T, uint32_t* n_contrib,
                        float* out_color, float* out_invdepth, cudaStream_t s) {
-    render_fwd_kernel<<<gx * gy, RF_THREADS, 0, s>>>(ranges, point_list, records, W, H, gx, background, final_T,
+    render_fwd_kernel<<<gx * gy, RF_THREADS, 0, s>>>(ranges, point_list, block_masks, records, W, H, gx, background, final_T,
                                                        n_contrib, out_color, out_invdepth);
 }
