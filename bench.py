@@ -61,6 +61,14 @@ def make_workload(name, cam_index=0):
     return w, scene, cam
 
 
+def make_workload_camera(name, cam_index):
+    w = WORKLOADS[name]
+    if w["kind"] == "random_init":
+        import cases
+        return cases._lego_cam(1 + cam_index % 8, w["W"], w["H"])
+    return synth.orbit_cameras(8, w["W"], w["H"], w["seed"])[cam_index % 8]
+
+
 def oracle_step(scene, cam, w, grads):
     """One fwd+bwd of the CPU oracle; returns (seconds, forward dict)."""
     from oracle import gs_oracle as go
@@ -180,7 +188,8 @@ def main():
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true")
-    ap.add_argument("--views-per-rank", type=int, default=1)
+    ap.add_argument("--views-per-rank", type=int, default=8,
+                    help="views every rank renders per step (gradients accumulate in the bucket; one all-reduce per step)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -199,25 +208,31 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
 
-    w, scene, cam = make_workload(args.workload, cam_index=rank)
+    V = max(1, args.views_per_rank)
+    # this rank's slice of the step's camera batch: V views, global view index rank*V + v
+    w, scene, cam = make_workload(args.workload, cam_index=rank * V)
+    cams = [cam] + [make_workload_camera(args.workload, rank * V + v) for v in range(1, V)]
     W, H, P = w["W"], w["H"], w["P"]
     t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
     # replicated Gaussians, resident in HBM; parameters live in one flat [P,59] gradient-bucket layout
     from gsr_b200.dist import FlatGaussians
     G = FlatGaussians.from_numpy(scene, dev)
     bg = torch.zeros(3, device=dev)
-    view, proj, campos = t(cam.world_view_transform), t(cam.full_proj_transform), t(cam.camera_center)
     dcol_np, ddep_np = synth.upstream_grads(H, W, 5)
     dcol, ddep = t(dcol_np), t(ddep_np)
-    common = dict(means3D=G.xyz, opacities=G.opacity, viewmatrix=view, projmatrix=proj, cam_pos=campos, background=bg,
-                  tan_fovx=cam.tanfovx, tan_fovy=cam.tanfovy, shs=G.shs, scales=G.scales, rotations=G.rotations,
+    shared = dict(means3D=G.xyz, opacities=G.opacity, background=bg, shs=G.shs, scales=G.scales, rotations=G.rotations,
                   sh_degree=3, antialiasing=w["aa"])
+    per_view = [dict(viewmatrix=t(c.world_view_transform), projmatrix=t(c.full_proj_transform), cam_pos=t(c.camera_center),
+                     tan_fovx=c.tanfovx, tan_fovy=c.tanfovy, **shared) for c in cams]
+    common = per_view[0]
 
     grad_views = G.grad_views()     # the backward kernels write straight into the all-reduce bucket
 
     def abi_step():
-        st = capi.forward(width=W, height=H, **common)
-        g = capi.backward(st, dL_dcolor=dcol, dL_dinvdepth=ddep, out=grad_views, **common)
+        # one step = this rank's V views: the first backward overwrites the bucket, the others add into it
+        for v in range(V):
+            st = capi.forward(width=W, height=H, **per_view[v])
+            g = capi.backward(st, dL_dcolor=dcol, dL_dinvdepth=ddep, out=grad_views, accumulate=(v > 0), **per_view[v])
         return st, g
 
     def barrier():
@@ -269,14 +284,16 @@ def main():
         tms = torch.tensor([ms], device=dev)
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
         ms = float(tms.item())
-    value = world * args.steps / (ms / 1000.0)
+    value = world * V * args.steps / (ms / 1000.0)
     N = st["num_rendered"]
 
     # ---------------- per-stage device times (profiling mode, separate pass) ----------------
     capi.set_profiling(True)
     stage = {}
-    for _ in range(3):
-        st, g = abi_step()
+    for _ in range(3):      # view 0 of this rank, write mode: the single-view fwd+bwd the roofline figures describe
+        st = capi.forward(width=W, height=H, **per_view[0])
+        fwd_t = capi.stage_times_ms()
+        g = capi.backward(st, dL_dcolor=dcol, dL_dinvdepth=ddep, out=grad_views, **per_view[0])
         for k, v in capi.stage_times_ms().items():
             stage.setdefault(k, []).append(v)
     capi.set_profiling(False)
@@ -286,32 +303,61 @@ def main():
     P_vis = int((st["radii"] > 0).sum().item())
 
     # ---------------- e2e leg: public Python API, host inputs, loss read back ----------------
-    rs_kw = dict(image_height=H, image_width=W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=bg, scale_modifier=1.0,
+    rs_kw = dict(image_height=H, image_width=W, bg=bg, scale_modifier=1.0,
                  sh_degree=3, prefiltered=False, debug=False, antialiasing=w["aa"])
-    target_host = torch.from_numpy(np.random.default_rng(9).random((3, H, W), dtype=np.float32)).pin_memory()
-    cam_host = torch.from_numpy(np.concatenate([cam.world_view_transform.ravel(), cam.full_proj_transform.ravel(),
-                                                cam.camera_center.ravel()]).astype(np.float32)).pin_memory()
-    target_dev = torch.empty(3, H, W, device=dev)
-    cam_dev = torch.empty(35, device=dev)
+    from diff_gaussian_rasterization import grad_sink
+    rng9 = np.random.default_rng(9)
+    target_host = [torch.from_numpy(rng9.random((3, H, W), dtype=np.float32)).pin_memory() for _ in range(min(V, 2))]
+    cam_host = [torch.from_numpy(np.concatenate([c.world_view_transform.ravel(), c.full_proj_transform.ravel(),
+                                                 c.camera_center.ravel()]).astype(np.float32)).pin_memory() for c in cams]
+    target_dev = [torch.empty(3, H, W, device=dev) for _ in range(2)]       # double-buffered: the copy of view v+1
+    cam_dev = [torch.empty(35, device=dev) for _ in range(2)]               # may run under view v's kernels
     params = G.as_leaf_params()
     loss_host = torch.empty(1).pin_memory()
+    loss_dev = torch.zeros(1, device=dev)
+    copy_stream = torch.cuda.Stream(device=dev)
+    uploaded = [torch.cuda.Event() for _ in range(2)]
+    buf_free = [torch.cuda.Event() for _ in range(2)]
+    for e_ in buf_free:
+        e_.record(torch.cuda.current_stream())
+    sink = (grad_views["dL_dmeans3D"], grad_views["dL_dsh"], grad_views["dL_dopacity"], grad_views["dL_dscales"],
+            grad_views["dL_drotations"])
 
     def api_step():
-        cam_dev.copy_(cam_host, non_blocking=True)
-        target_dev.copy_(target_host, non_blocking=True)
-        rs = GaussianRasterizationSettings(viewmatrix=cam_dev[0:16].view(4, 4), projmatrix=cam_dev[16:32].view(4, 4),
-                                           campos=cam_dev[32:35], **rs_kw)
-        means2D = torch.zeros_like(params["xyz"], requires_grad=True)
-        color, radii, invd = GaussianRasterizer(rs)(means3D=params["xyz"], means2D=means2D, opacities=params["opacity"],
-                                                    shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
-        loss = (color - target_dev).abs().mean()
-        loss.backward()
+        """One training-step's worth of rendering through the public API: for each of this rank's V views the camera
+        and the target image come from pinned host memory, GaussianRasterizer renders, an L1 loss is taken and
+        backpropagated; parameter gradients of the V views add up in the flat bucket (grad_sink), which is
+        all-reduced over ranks; the step's loss is read back to the host."""
+        loss_dev.zero_()
+        main = torch.cuda.current_stream()
+
+        def upload(v):      # H2D of view v's camera + target on the copy stream, into buffer v & 1
+            copy_stream.wait_event(buf_free[v & 1])          # the view that last used this buffer is done with it
+            with torch.cuda.stream(copy_stream):
+                cam_dev[v & 1].copy_(cam_host[v], non_blocking=True)
+                target_dev[v & 1].copy_(target_host[v % len(target_host)], non_blocking=True)
+                uploaded[v & 1].record(copy_stream)
+
+        upload(0)
+        for v in range(V):
+            cd, td = cam_dev[v & 1], target_dev[v & 1]
+            main.wait_event(uploaded[v & 1])
+            if v + 1 < V:
+                upload(v + 1)                                 # travels while this view renders
+            rs = GaussianRasterizationSettings(viewmatrix=cd[0:16].view(4, 4), projmatrix=cd[16:32].view(4, 4),
+                                               campos=cd[32:35], tanfovx=cams[v].tanfovx, tanfovy=cams[v].tanfovy, **rs_kw)
+            means2D = torch.zeros_like(params["xyz"], requires_grad=True)
+            color, radii, invd = GaussianRasterizer(rs)(means3D=params["xyz"], means2D=means2D, opacities=params["opacity"],
+                                                        shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
+            loss = (color - td).abs().mean()
+            with grad_sink(*sink, accumulate=(v > 0)):
+                loss.backward()
+            loss_dev.add_(loss.detach())
+            buf_free[v & 1].record(main)
         if world > 1:
-            G.allreduce_param_grads(params)
-        loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+            dist.all_reduce(G.bucket, op=dist.ReduceOp.SUM)
+        loss_host.copy_(loss_dev, non_blocking=True)
         torch.cuda.current_stream().synchronize()
-        for p_ in params.values():
-            p_.grad = None
         return float(loss_host[0])
 
     for _ in range(max(args.warmup, 3)):
@@ -329,9 +375,9 @@ def main():
         tms = torch.tensor([e2e_ms], device=dev)
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
         e2e_ms = float(tms.item())
-    e2e_val = world * args.steps / (e2e_ms / 1000.0)
-    h2d = target_host.numel() * 4 + cam_host.numel() * 4
-    d2h = 4 + 4    # loss + num_rendered
+    e2e_val = world * V * args.steps / (e2e_ms / 1000.0)
+    h2d = V * (target_host[0].numel() * 4 + cam_host[0].numel() * 4)
+    d2h = 4 + 12 * V    # the step's loss + the 12-byte instance/visible counts of every forward
 
     out = None
     if rank == 0:
@@ -406,19 +452,23 @@ def main():
         launches_per_step = 1 + 1 + (1 + 4) + 1 + 1 + (1 + tile_passes) + 1 + 1 + 1 + 1
         out = {
             "metric": "fwd+bwd renders/s", "value": value, "unit": "renders/s", "n_gpus": world, "steps": args.steps,
-            "warmup": n_warm, "ms_per_step": ms / args.steps,
+            "warmup": n_warm, "ms_per_step": ms / args.steps, "ms_per_view": ms / args.steps / V,
             "step_ms": {"min": step_ms[0], "median": step_ms[len(step_ms) // 2], "max": step_ms[-1]}, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload + ": " + w["desc"], "P": P, "P_visible": P_vis, "num_rendered": N,
                        "width": W, "height": H, "pairs_evaluated_fwd": pairs_eval, "pairs_blended": pairs_blend,
                        "pairs_evaluated_bwd": pairs_bwd_eval, "l2": "inputs (708 MB of Gaussians + scratch) exceed the 126 MB L2",
+                       "views_per_rank_per_step": V, "global_views_per_step": V * world,
+                       "step": "each rank renders its %d views (fwd+bwd, parameter gradients accumulated in one flat bucket)%s" % (
+                           V, ", then ONE NCCL all-reduce of the 59 fp32/Gaussian bucket" if world > 1 else ""),
+                       "roofline_view": "stage times / roofline figures are of view 0 (single-view fwd+bwd, write mode)",
                        "parallelism": "view-parallel dp%d, replicated Gaussians, NCCL all-reduce of 59 fp32/Gaussian" % world
                        if world > 1 else "single GPU", "peak_source": peak_src},
             "clocks": clocks,
             "e2e": {"value": e2e_val, "unit": "renders/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms / args.steps,
-                    "what": "GaussianRasterizer autograd fwd+bwd + L1 loss; camera+target image from pinned host memory, loss read back"},
-            "gpu_launches": launches_per_step * args.steps,
+                    "what": "per view: camera + target image from pinned host memory (copy stream, double-buffered, overlapping the previous view's kernels), GaussianRasterizer autograd fwd+bwd + L1 loss; per step: gradients of the rank's views summed in the bucket (grad_sink), all-reduce when N>1, loss read back"},
+            "gpu_launches": launches_per_step * V * args.steps,
             "stage_ms": stage_ms, "roofline": roof, "roofline_stages": stages, "cpu_baseline": cpu,
         }
         # same-box bar: the unmodified reference CUDA kernels (oracle/_ref), informational

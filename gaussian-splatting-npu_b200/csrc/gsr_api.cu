@@ -311,6 +311,10 @@ extern "C" int gsr_backward(const gsr_backward_args* a, void* stream_) {
     p.scale_modifier = a->scale_modifier; p.tan_fovx = a->tan_fovx; p.tan_fovy = a->tan_fovy;
     p.focal_y = H / (2.0f * a->tan_fovy); p.focal_x = W / (2.0f * a->tan_fovx);
     p.antialiasing = a->antialiasing; p.radii = a->radii;
+    p.accumulate = a->accumulate != 0;
+    // per-view opacity gradient: the blend accumulates it in scratch (the depth-sort key buffer of the
+    // forward, dead by now); preprocess_bwd applies the antialiasing factor and writes / adds the output
+    p.dop_view = reinterpret_cast<float*>(g.gsort_keys[0]);
     p.dL_dpix = a->dL_dpix; p.dL_dinvdepth_pix = a->dL_dinvdepth_pix;
     p.dL_dmean2D = a->dL_dmean2D; p.dL_dconic = a->dL_dconic; p.dL_dopacity = a->dL_dopacity; p.dL_dcolor = a->dL_dcolor;
     p.dL_dinvdepth = a->dL_dinvdepth_pix ? a->dL_dinvdepth : nullptr;
@@ -318,11 +322,11 @@ extern "C" int gsr_backward(const gsr_backward_args* a, void* stream_) {
 
     StageTimer tm(tl_profiling != 0, stream);
     tm.mark();
-    // the five atomically accumulated outputs start from zero; everything else is fully written below
+    // the five atomically accumulated arrays start from zero; everything else is fully written below
     const size_t sp = (size_t)P;
     CUDA_TRY(cudaMemsetAsync(a->dL_dmean2D, 0, sp * 3 * 4, stream));
     CUDA_TRY(cudaMemsetAsync(a->dL_dconic, 0, sp * 4 * 4, stream));
-    CUDA_TRY(cudaMemsetAsync(a->dL_dopacity, 0, sp * 4, stream));
+    CUDA_TRY(cudaMemsetAsync(p.dop_view, 0, sp * 4, stream));
     CUDA_TRY(cudaMemsetAsync(a->dL_dcolor, 0, sp * 3 * 4, stream));
     if (p.dL_dinvdepth) CUDA_TRY(cudaMemsetAsync(p.dL_dinvdepth, 0, sp * 4, stream));
     if (a->R > 0) {

@@ -212,6 +212,8 @@ struct BwdParams {
         *cov3D_precomp, *viewmatrix, *projmatrix, *cam_pos;
     float scale_modifier, tan_fovx, tan_fovy, focal_x, focal_y;
     int antialiasing;
+    int accumulate;              // parameter gradients are added to the outputs (visible rows only)
+    float* dop_view;             // [P] this view's dL/dopacity before the antialiasing factor (scratch)
     const int* radii;
     const float *dL_dpix, *dL_dinvdepth_pix;
     float *dL_dmean2D, *dL_dconic, *dL_dopacity, *dL_dcolor, *dL_dinvdepth, *dL_dmean3D, *dL_dcov3D,

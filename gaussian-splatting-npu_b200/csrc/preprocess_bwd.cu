@@ -7,7 +7,9 @@
 //   * keeps dL_dcov3D / the partial dL_dmean in registers between the two reference stages,
 //   * reads the 192-byte SH row and writes the 192-byte dL_dsh row through a swizzled
 //     shared-memory stage with coalesced 128-bit streaming accesses,
-//   * writes EVERY output row (zeros for culled Gaussians), so the caller needs no zero-fill.
+//   * writes EVERY output row (zeros for culled Gaussians), so the caller needs no zero-fill;
+//   * or, in accumulate mode, ADDS the five parameter gradients into the visible rows only, so that
+//     the views of one training step sum into one all-reduce bucket without a per-view copy.
 #include "gsr_common.cuh"
 
 #define PB_THREADS 128
@@ -90,8 +92,8 @@ struct GlobalRow {
     __device__ __forceinline__ float operator()(int i) const { return i < limit ? row[i] : 0.0f; }
 };
 
-template <bool SH16>
-__global__ void __launch_bounds__(PB_THREADS)
+template <bool SH16, bool ACC>
+__global__ void __launch_bounds__(PB_THREADS, 8)
 preprocess_bwd_kernel(BwdParams p, GeomView g) {
     __shared__ float cam[35];
     __shared__ float4 stage[SH16 ? PB_WARPS * 384 : 1];
@@ -108,7 +110,7 @@ preprocess_bwd_kernel(BwdParams p, GeomView g) {
 
     float dmx = 0, dmy = 0, dmz = 0;
     float dcov[6] = { 0, 0, 0, 0, 0, 0 };
-    float mx = 0, my = 0, mz = 0;
+    float mx = 0, my = 0, mz = 0, dop_out = 0;
     if (vis) {
         mx = p.means3D[3 * (size_t)i]; my = p.means3D[3 * (size_t)i + 1]; mz = p.means3D[3 * (size_t)i + 2];
         // ---------------- computeCov2DCUDA (backward.cu:147-326) ----------------
@@ -144,16 +146,17 @@ preprocess_bwd_kernel(BwdParams p, GeomView g) {
         float c_yy = tv1[0] * T1[0] + tv1[1] * T1[1] + tv1[2] * T1[2];
         const float h_var = 0.3f;
         float d_inside_root = 0.0f;
+        float dop = p.dop_view[i];                 // sum over pixels of G dL/dalpha (render_bwd)
         if (p.antialiasing) {
             const float det_cov = c_xx * c_yy - c_xy * c_xy;
             c_xx += h_var; c_yy += h_var;
             const float det_h = c_xx * c_yy - c_xy * c_xy;
             const float hs = sqrtf(fmaxf(0.000025f, det_cov / det_h));
-            const float dop = p.dL_dopacity[i];
             const float d_hs = dop * p.opacities[i];
-            p.dL_dopacity[i] = dop * hs;
+            dop = dop * hs;
             d_inside_root = (det_cov / det_h) <= 0.000025f ? 0.0f : d_hs / (2 * hs);
         } else { c_xx += h_var; c_yy += h_var; }
+        dop_out = dop;
         float dL_dc_xx = 0, dL_dc_xy = 0, dL_dc_yy = 0;
         if (p.antialiasing) {
             const float x = c_xx, y = c_yy, z = c_xy, w = h_var;
@@ -248,9 +251,16 @@ preprocess_bwd_kernel(BwdParams p, GeomView g) {
                 for (int it = 0; it < 12; it++) {
                     const int f = it * 32 + lane;
                     const int row = f / 12, j = f - row * 12;
-                    if (warp_first + row < (size_t)p.P) stg_stream_f4(dst + f, st[row * 12 + (j ^ ((row >> 1) & 3))]);
+                    if (ACC) {           // add into the visible rows, leave the others alone
+                        if ((vmask >> row) & 1u) {
+                            float4 v = st[row * 12 + (j ^ ((row >> 1) & 3))];
+                            const float4 o = dst[f];
+                            v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+                            dst[f] = v;
+                        }
+                    } else if (warp_first + row < (size_t)p.P) stg_stream_f4(dst + f, st[row * 12 + (j ^ ((row >> 1) & 3))]);
                 }
-            } else {                              // a fully culled warp: 6 KB of zeros, no staging
+            } else if (!ACC) {                              // a fully culled warp: 6 KB of zeros, no staging
                 const float4 z4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
 #pragma unroll
                 for (int it = 0; it < 12; it++) {
@@ -267,19 +277,26 @@ preprocess_bwd_kernel(BwdParams p, GeomView g) {
                 sh_backward(p.D, E, mx - cam[32], my - cam[33], mz - cam[34], g.clamped[i], dr, dg, db, w, d, dmx, dmy, dmz);
 #pragma unroll
                 for (int k = 0; k < 16; k++)
-                    if (k < p.M) { drow[3 * k] = w[k] * d[0]; drow[3 * k + 1] = w[k] * d[1]; drow[3 * k + 2] = w[k] * d[2]; }
-            } else {
+                    if (k < p.M) {
+                        if (ACC) { drow[3 * k] += w[k] * d[0]; drow[3 * k + 1] += w[k] * d[1]; drow[3 * k + 2] += w[k] * d[2]; }
+                        else { drow[3 * k] = w[k] * d[0]; drow[3 * k + 1] = w[k] * d[1]; drow[3 * k + 2] = w[k] * d[2]; }
+                    }
+            } else if (!ACC) {
                 for (int k = 0; k < 3 * p.M; k++) drow[k] = 0.0f;
             }
         }
     }
 
     if (!in) return;
-    p.dL_dmean3D[3 * (size_t)i] = dmx; p.dL_dmean3D[3 * (size_t)i + 1] = dmy; p.dL_dmean3D[3 * (size_t)i + 2] = dmz;
     {
         float2* dc = reinterpret_cast<float2*>(p.dL_dcov3D + 6 * (size_t)i);
         dc[0] = make_float2(dcov[0], dcov[1]); dc[1] = make_float2(dcov[2], dcov[3]); dc[2] = make_float2(dcov[4], dcov[5]);
     }
+    const bool acc = ACC;
+    if (acc && !vis) return;                 // accumulate mode: invisible rows keep what they hold
+    float* om = p.dL_dmean3D + 3 * (size_t)i;
+    if (acc) { om[0] += dmx; om[1] += dmy; om[2] += dmz; p.dL_dopacity[i] += dop_out; }
+    else { om[0] = dmx; om[1] = dmy; om[2] = dmz; p.dL_dopacity[i] = dop_out; }
     // ---------------- computeCov3D backward (backward.cu:330-393) ----------------
     if (p.scales) {
         float ds[3] = { 0, 0, 0 };
@@ -318,15 +335,27 @@ preprocess_bwd_kernel(BwdParams p, GeomView g) {
             dq.z = 2 * x * (dMt[1][0] + dMt[0][1]) + 2 * r * (dMt[2][0] - dMt[0][2]) + 2 * z * (dMt[1][2] + dMt[2][1]) - 4 * y * (dMt[2][2] + dMt[0][0]);
             dq.w = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) - 4 * z * (dMt[1][1] + dMt[0][0]);
         }
-        p.dL_dscale[3 * (size_t)i] = ds[0]; p.dL_dscale[3 * (size_t)i + 1] = ds[1]; p.dL_dscale[3 * (size_t)i + 2] = ds[2];
-        reinterpret_cast<float4*>(p.dL_drot)[i] = dq;
+        float* os = p.dL_dscale + 3 * (size_t)i;
+        float4* oq = reinterpret_cast<float4*>(p.dL_drot) + i;
+        if (acc) {
+            os[0] += ds[0]; os[1] += ds[1]; os[2] += ds[2];
+            const float4 o = *oq;
+            *oq = make_float4(o.x + dq.x, o.y + dq.y, o.z + dq.z, o.w + dq.w);
+        } else {
+            os[0] = ds[0]; os[1] = ds[1]; os[2] = ds[2];
+            *oq = dq;
+        }
     }
 }
 
 void launch_preprocess_bwd(const BwdParams& p, const GeomView& g, cudaStream_t s) {
     const int blocks = (p.P + PB_THREADS - 1) / PB_THREADS;
-    if (p.shs && p.M == 16)
-        preprocess_bwd_kernel<true><<<blocks, PB_THREADS, 0, s>>>(p, g);
-    else
-        preprocess_bwd_kernel<false><<<blocks, PB_THREADS, 0, s>>>(p, g);
+    const bool sh16 = p.shs && p.M == 16;
+    if (p.accumulate) {
+        if (sh16) preprocess_bwd_kernel<true, true><<<blocks, PB_THREADS, 0, s>>>(p, g);
+        else preprocess_bwd_kernel<false, true><<<blocks, PB_THREADS, 0, s>>>(p, g);
+    } else {
+        if (sh16) preprocess_bwd_kernel<true, false><<<blocks, PB_THREADS, 0, s>>>(p, g);
+        else preprocess_bwd_kernel<false, false><<<blocks, PB_THREADS, 0, s>>>(p, g);
+    }
 }

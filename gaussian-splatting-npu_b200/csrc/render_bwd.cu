@@ -216,9 +216,9 @@ void launch_render_bwd(const BwdParams& p, const uint2* ranges, const uint32_t* 
     const int tiles = p.gx * p.gy;
     if (p.dL_dinvdepth_pix)
         render_bwd_kernel<true><<<tiles, RB_THREADS, 0, s>>>(ranges, point_list, block_masks, records, p.W, p.H, p.gx, p.background,
-            final_T, n_contrib, p.dL_dpix, p.dL_dinvdepth_pix, p.dL_dmean2D, p.dL_dconic, p.dL_dopacity, p.dL_dcolor,
+            final_T, n_contrib, p.dL_dpix, p.dL_dinvdepth_pix, p.dL_dmean2D, p.dL_dconic, p.dop_view, p.dL_dcolor,
             p.dL_dinvdepth);
     else
         render_bwd_kernel<false><<<tiles, RB_THREADS, 0, s>>>(ranges, point_list, block_masks, records, p.W, p.H, p.gx, p.background,
-            final_T, n_contrib, p.dL_dpix, nullptr, p.dL_dmean2D, p.dL_dconic, p.dL_dopacity, p.dL_dcolor, nullptr);
+            final_T, n_contrib, p.dL_dpix, nullptr, p.dL_dmean2D, p.dL_dconic, p.dop_view, p.dL_dcolor, nullptr);
 }

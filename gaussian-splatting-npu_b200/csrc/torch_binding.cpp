@@ -96,8 +96,15 @@ RasterizeGaussiansCUDA(const torch::Tensor& background, const torch::Tensor& mea
     return std::make_tuple(rendered, out_color, radii, geomBuffer, binningBuffer, imgBuffer, out_invdepth);
 }
 
-std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
-RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+// Optional gradient sink (extension over the reference API, see diff_gaussian_rasterization.grad_sink):
+// the five parameter gradients are written -- or, with accumulate, added -- straight into caller-owned
+// tensors (views of an all-reduce bucket) instead of fresh allocations.
+struct GradSink { torch::Tensor means3D, sh, opacity, scales, rotations; bool accumulate = false; bool active = false; };
+
+typedef std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor> BwdTuple;
+
+static BwdTuple
+backward_impl(const GradSink& sink, const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
                                const torch::Tensor& colors, const torch::Tensor& opacities, const torch::Tensor& scales,
                                const torch::Tensor& rotations, const float scale_modifier, const torch::Tensor& cov3D_precomp,
                                const torch::Tensor& viewmatrix, const torch::Tensor& projmatrix, const float tan_fovx,
@@ -120,15 +127,23 @@ RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Ten
     auto mk = [&](std::initializer_list<int64_t> shape, bool written) {
         return (live && written) ? torch::empty(shape, opts) : torch::zeros(shape, opts);
     };
-    torch::Tensor dL_dmeans3D = mk({P, 3}, true);
+    auto sunk = [&](const torch::Tensor& t, std::initializer_list<int64_t> shape, bool written, const char* name) {
+        if (!(sink.active && live && written)) return mk(shape, written);
+        int64_t n = 1; for (auto d : shape) n *= d;
+        TORCH_CHECK(t.defined() && t.is_cuda() && t.device() == means3D.device() && t.scalar_type() == torch::kFloat32 &&
+                    t.is_contiguous() && t.numel() == n && (reinterpret_cast<uintptr_t>(t.data_ptr()) & 15) == 0,
+                    "grad sink tensor '", name, "' must be a contiguous, 16-byte aligned fp32 CUDA tensor of ", n, " elements");
+        return t;
+    };
+    torch::Tensor dL_dmeans3D = sunk(sink.means3D, {P, 3}, true, "means3D");
     torch::Tensor dL_dmeans2D = mk({P, 3}, true);
     torch::Tensor dL_dcolors = mk({P, 3}, true);
     torch::Tensor dL_dconic = mk({P, 2, 2}, true);
-    torch::Tensor dL_dopacity = mk({P, 1}, true);
+    torch::Tensor dL_dopacity = sunk(sink.opacity, {P, 1}, true, "opacity");
     torch::Tensor dL_dcov3D = mk({P, 6}, true);
-    torch::Tensor dL_dsh = mk({P, M, 3}, M > 0);
-    torch::Tensor dL_dscales = mk({P, 3}, has_scales);
-    torch::Tensor dL_drotations = mk({P, 4}, has_scales);
+    torch::Tensor dL_dsh = sunk(sink.sh, {P, M, 3}, M > 0, "sh");
+    torch::Tensor dL_dscales = sunk(sink.scales, {P, 3}, has_scales, "scales");
+    torch::Tensor dL_drotations = sunk(sink.rotations, {P, 4}, has_scales, "rotations");
     torch::Tensor dL_dinvdepths = has_depth ? mk({P, 1}, true) : torch::zeros({0, 1}, opts);
 
     if (live) {
@@ -167,9 +182,44 @@ RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Ten
         a.dL_dscale = has_scales ? dL_dscales.data_ptr<float>() : nullptr;
         a.dL_drot = has_scales ? dL_drotations.data_ptr<float>() : nullptr;
         a.antialiasing = antialiasing; a.debug = debug;
+        a.accumulate = (sink.active && sink.accumulate) ? 1 : 0;            // the reference API always overwrites
         check(gsr_backward(&a, stream));
     }
     return std::make_tuple(dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations);
+}
+
+BwdTuple
+RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+                               const torch::Tensor& colors, const torch::Tensor& opacities, const torch::Tensor& scales,
+                               const torch::Tensor& rotations, const float scale_modifier, const torch::Tensor& cov3D_precomp,
+                               const torch::Tensor& viewmatrix, const torch::Tensor& projmatrix, const float tan_fovx,
+                               const float tan_fovy, const torch::Tensor& dL_dout_color, const torch::Tensor& dL_dout_invdepth,
+                               const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
+                               const torch::Tensor& geomBuffer, const int R, const torch::Tensor& binningBuffer,
+                               const torch::Tensor& imageBuffer, const bool antialiasing, const bool debug) {
+    return backward_impl(GradSink(), background, means3D, radii, colors, opacities, scales, rotations, scale_modifier, cov3D_precomp,
+                         viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_invdepth, sh, degree, campos,
+                         geomBuffer, R, binningBuffer, imageBuffer, antialiasing, debug);
+}
+
+// Same arguments + the sink tensors and the accumulate flag.
+BwdTuple
+RasterizeGaussiansBackwardInto(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+                               const torch::Tensor& colors, const torch::Tensor& opacities, const torch::Tensor& scales,
+                               const torch::Tensor& rotations, const float scale_modifier, const torch::Tensor& cov3D_precomp,
+                               const torch::Tensor& viewmatrix, const torch::Tensor& projmatrix, const float tan_fovx,
+                               const float tan_fovy, const torch::Tensor& dL_dout_color, const torch::Tensor& dL_dout_invdepth,
+                               const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
+                               const torch::Tensor& geomBuffer, const int R, const torch::Tensor& binningBuffer,
+                               const torch::Tensor& imageBuffer, const bool antialiasing, const bool debug,
+                               const torch::Tensor& sink_means3D, const torch::Tensor& sink_sh, const torch::Tensor& sink_opacity,
+                               const torch::Tensor& sink_scales, const torch::Tensor& sink_rotations, const bool accumulate) {
+    GradSink sink;
+    sink.means3D = sink_means3D; sink.sh = sink_sh; sink.opacity = sink_opacity; sink.scales = sink_scales;
+    sink.rotations = sink_rotations; sink.accumulate = accumulate; sink.active = true;
+    return backward_impl(sink, background, means3D, radii, colors, opacities, scales, rotations, scale_modifier, cov3D_precomp,
+                         viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_invdepth, sh, degree, campos,
+                         geomBuffer, R, binningBuffer, imageBuffer, antialiasing, debug);
 }
 
 torch::Tensor markVisible(torch::Tensor& means3D, torch::Tensor& viewmatrix, torch::Tensor& projmatrix) {
@@ -189,6 +239,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.def("rasterize_gaussians", &RasterizeGaussiansCUDA);
     m.def("rasterize_gaussians_backward", &RasterizeGaussiansBackwardCUDA);
     m.def("mark_visible", &markVisible);
+    m.def("rasterize_gaussians_backward_into", &RasterizeGaussiansBackwardInto);
     // the fork's spellings (DGR/ext.cpp:16, rasterize_points.h:18,41)
     m.def("rasterize_gaussians_npu", &RasterizeGaussiansCUDA);
     m.def("rasterize_gaussians_backward_npu", &RasterizeGaussiansBackwardCUDA);

@@ -24,7 +24,37 @@ except ImportError as exc:  # pragma: no cover - exercised only on a broken buil
         "loaded; run `python gaussian-splatting-npu_b200/build.py`. There is no fallback path."
     ) from exc
 
-__all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians"]
+__all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians", "grad_sink"]
+
+import contextlib
+
+
+class _SinkState:      # process-wide on purpose: autograd runs CUDA backward nodes on its own device threads
+    sink = None
+
+
+_tls = _SinkState
+
+
+@contextlib.contextmanager
+def grad_sink(means3D, shs, opacities, scales, rotations, accumulate=False):
+    """Extension over the reference API (opt-in; nothing changes unless it is used).
+
+    Inside this context every `backward()` through the rasterizer writes the five PARAMETER gradients
+    straight into the given preallocated tensors -- typically views of one flat all-reduce bucket
+    (`gsr_b200.dist.FlatGaussians.grad_views()`) -- and hands autograd `None` for those inputs, so no
+    [P,59] gradient is allocated, copied or added by AccumulateGrad.  With `accumulate=True` the kernels
+    ADD into the visible rows (second and later views of one training step); with False they overwrite
+    every row (first view).  means2D / colors_precomp / cov3D_precomp gradients flow through autograd
+    as usual (densification reads means2D.grad per view).
+    """
+    prev = getattr(_tls, "sink", None)
+    none = torch.empty(0)
+    _tls.sink = tuple(none if t is None else t for t in (means3D, shs, opacities, scales, rotations)) + (bool(accumulate),)
+    try:
+        yield
+    finally:
+        _tls.sink = prev
 
 
 class GaussianRasterizationSettings(NamedTuple):
@@ -74,6 +104,14 @@ class _RasterizeGaussians(torch.autograd.Function):
         (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, opacities,
          geom_buf, binning_buf, img_buf) = ctx.saved_tensors
         (mod,), cam = _camera_args(rs)
+        sink = getattr(_tls, "sink", None)
+        if sink is not None:
+            (grad_means2D, grad_colors_precomp, _o, _m, grad_cov3Ds_precomp, _s, _sc, _r) = \
+                _C.rasterize_gaussians_backward_into(
+                    rs.bg, means3D, radii, colors_precomp, opacities, scales, rotations, mod, cov3Ds_precomp,
+                    *cam, grad_out_color, grad_out_depth, sh, rs.sh_degree, rs.campos, geom_buf,
+                    ctx.num_rendered, binning_buf, img_buf, rs.antialiasing, rs.debug, *sink)
+            return (None, grad_means2D, None, grad_colors_precomp, None, None, None, grad_cov3Ds_precomp, None)
         # argument order of RasterizeGaussiansBackwardCUDA (rasterize_points.cu:126-151)
         (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp,
          grad_sh, grad_scales, grad_rotations) = _C.rasterize_gaussians_backward(

@@ -42,7 +42,7 @@ class BackwardArgs(Structure):
                 ("dL_dconic", c_void_p), ("dL_dopacity", c_void_p), ("dL_dcolor", c_void_p),
                 ("dL_dinvdepth", c_void_p), ("dL_dmean3D", c_void_p), ("dL_dcov3D", c_void_p),
                 ("dL_dsh", c_void_p), ("dL_dscale", c_void_p), ("dL_drot", c_void_p),
-                ("antialiasing", c_int), ("debug", c_int)]
+                ("antialiasing", c_int), ("debug", c_int), ("accumulate", c_int)]
 
 
 class GeometryLayout(Structure):
@@ -179,9 +179,11 @@ def forward(*, means3D, opacities, viewmatrix, projmatrix, cam_pos, background, 
 
 def backward(state, *, dL_dcolor, dL_dinvdepth=None, means3D, opacities, viewmatrix, projmatrix, cam_pos,
              background, tan_fovx, tan_fovy, shs=None, colors_precomp=None, scales=None, rotations=None,
-             cov3D_precomp=None, sh_degree=3, scale_modifier=1.0, antialiasing=False, debug=False, out=None):
+             cov3D_precomp=None, sh_degree=3, scale_modifier=1.0, antialiasing=False, debug=False, out=None,
+             accumulate=False):
     """gsr_backward.  `out` may map output names to preallocated contiguous tensors (e.g. views of a
-    gradient bucket) that the kernels then write directly."""
+    gradient bucket) that the kernels then write directly; with `accumulate` the five parameter
+    gradients are added into them (visible rows only) instead of overwriting."""
     L = lib()
     dev = means3D.device
     P, W, H, M = state["P"], state["W"], state["H"], state["M"]
@@ -202,7 +204,7 @@ def backward(state, *, dL_dcolor, dL_dinvdepth=None, means3D, opacities, viewmat
                      _ptr(dL_dcolor), _ptr(dL_dinvdepth), _ptr(g["dL_dmeans2D"]), _ptr(g["dL_dconic"]),
                      _ptr(g["dL_dopacity"]), _ptr(g["dL_dcolors"]), _ptr(g["dL_dinvdepths"]), _ptr(g["dL_dmeans3D"]),
                      _ptr(g["dL_dcov3D"]), _ptr(g["dL_dsh"]), _ptr(g["dL_dscales"]), _ptr(g["dL_drotations"]),
-                     int(antialiasing), int(debug))
+                     int(antialiasing), int(debug), int(accumulate))
     with torch.cuda.device(dev):
         _check(L.gsr_backward(ctypes.byref(a), _stream()))
     return g

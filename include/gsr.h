@@ -109,6 +109,13 @@ typedef struct gsr_backward_args {
     float* dL_drot;              /* [P,4] or NULL when rotations==NULL */
     int antialiasing;
     int debug;
+    /* 0 (the reference's behaviour): the outputs are overwritten.  1: the five PARAMETER gradients
+     * (dL_dmean3D, dL_dsh, dL_dopacity, dL_dscale, dL_drot) are ADDED to what the buffers hold, rows
+     * of invisible Gaussians are left untouched -- several views of one training step accumulate
+     * into one gradient bucket (what autograd does for the reference when a step renders more than
+     * one camera) without a per-view buffer and add pass.  The per-view intermediates (dL_dmean2D,
+     * dL_dconic, dL_dcolor, dL_dinvdepth, dL_dcov3D) are overwritten in both modes. */
+    int accumulate;
 } gsr_backward_args;
 
 /*
