@@ -123,6 +123,28 @@ __device__ __forceinline__ float rcp_approx(float x) {
     return r;
 }
 
+// ---- packed fp32x2 arithmetic (Blackwell FADD2 / FMUL2 / FFMA2) -----------------------------------
+// sm_100 executes two IEEE-rn fp32 operations per issued instruction on a 64-bit register pair.  The
+// blend kernels are issue-bound, not FMA-pipe-bound, so pairing (x,y), (r,g), (b,1/depth) halves
+// the issue slots of that arithmetic; each half rounds exactly like the scalar instruction, so the
+// bit-exact chains stay bit-exact.  A scalar operand broadcasts for free (pk(a, a) becomes the
+// `.F32` operand form, no MOV).
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void upk(f32x2 v, float& lo, float& hi) { asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) { f32x2 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ void lds_2x64(uint32_t a, f32x2& v0, f32x2& v1) {
+    asm volatile("ld.shared.v2.b64 {%0,%1}, [%2];" : "=l"(v0), "=l"(v1) : "r"(a));
+}
+__device__ __forceinline__ f32x2 lds_64(uint32_t a) {
+    f32x2 v;
+    asm volatile("ld.shared.b64 %0, [%1];" : "=l"(v) : "r"(a));
+    return v;
+}
+
 // ---- streaming load/store helpers --------------------------------------------------------------
 __device__ __forceinline__ float4 ldg_stream_f4(const float4* p) {
     float4 v;

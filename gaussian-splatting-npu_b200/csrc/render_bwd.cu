@@ -32,8 +32,8 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvdepth_pix,
                   float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity,
                   float* __restrict__ dL_dcolor, float* __restrict__ dL_dinvdepth) {
-    __shared__ float4 sA[2][RB_THREADS];          // x, y, conic.a, conic.b
-    __shared__ float4 sB[2][RB_THREADS];          // conic.c, opacity, r, g
+    __shared__ float4 sA[2][RB_THREADS];          // x, y, conic.a, conic.c   (register pairs for the packed fp32x2 ops)
+    __shared__ float4 sB[2][RB_THREADS];          // conic.b, opacity, r, g
     __shared__ float2 sC[2][RB_THREADS];          // b, 1/depth
     __shared__ uint32_t sId[2][RB_THREADS];
     __shared__ unsigned char sMask[2][RB_THREADS];
@@ -93,7 +93,9 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     for (int w = 0; w < RB_THREADS / 32; w++) remaining = max(remaining, sMax[w]);
 
     float T = T_final;
-    float acc_r = 0, acc_g = 0, acc_b = 0, acc_d = 0;          // colour / inverse depth accumulated behind the current layer
+    // colour / inverse depth accumulated behind the current layer, as fp32x2 pairs (r,g), (b,1/depth)
+    f32x2 ACC01 = pk(0.0f, 0.0f), ACC2D = pk(0.0f, 0.0f);
+    const f32x2 DP01 = pk(dpx0, dpx1), DP2D = pk(dpx2, HAS_DEPTH ? dpd : 0.0f), negP = pk(-pxf, -pyf);
 
     // software pipeline: the batch after the current one travels in registers
     uint32_t nId = 0, nMask = 0;
@@ -111,7 +113,8 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         // stage positions [remaining-n, remaining), backmost first.  Writing buffer `buf` is safe: every
         // warp that passed the previous barrier had finished the batch before it, the last user of `buf`.
         if (tid < n) {
-            sId[buf][tid] = nId; sA[buf][tid] = nA; sB[buf][tid] = nB; sC[buf][tid] = make_float2(nC.x, nC.y);
+            sId[buf][tid] = nId; sA[buf][tid] = make_float4(nA.x, nA.y, nA.z, nB.x);
+            sB[buf][tid] = make_float4(nA.w, nB.y, nB.z, nB.w); sC[buf][tid] = make_float2(nC.x, nC.y);
             sMask[buf][tid] = (unsigned char)nMask;
         }
         __syncthreads();
@@ -137,70 +140,80 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                     // arithmetic with alpha := 0 and G := 0, which leaves its recurrences bit-identical
                     // (a zero-alpha layer: T/(1-0) = T, acc + 0*(c-acc) = acc) and makes all ten of its
                     // partial sums exactly 0 -- no divergence, no zero-initialisation.
-                    const float4 a = lds_f4(aA + 16u * j);
-                    const float4 b = lds_f4(aB + 16u * j);
-                    const float dx = fsub(a.x, pxf), dy = fsub(a.y, pyf);
+                    f32x2 XY, AC, BO, RG;
+                    lds_2x64(aA + 16u * j, XY, AC);
+                    lds_2x64(aB + 16u * j, BO, RG);
+                    const f32x2 D = add2(XY, negP);             // (x - px, y - py): same rounding as fsub
+                    const f32x2 M = mul2(D, AC);                // (dx A, dy C)
+                    float dx, dy, dxA, dyC, cB, opac;
+                    upk(D, dx, dy); upk(M, dxA, dyC); upk(BO, cB, opac);
                     // power with the forward's rounding (blend_power), keeping the partial products
-                    const float dyC = fmul(dy, b.x), dxA = fmul(dx, a.z), dxB = fmul(dx, a.w);
+                    const float dxB = fmul(dx, cB);
                     const float power = ffma(ffma(dx, dxA, fmul(dy, dyC)), -0.5f, -fmul(dy, dxB));
                     const float G = expf(power);
-                    const float alpha = fminf(0.99f, fmul(b.y, G));
+                    const float alpha = fminf(0.99f, fmul(opac, G));
                     const bool contrib = (remaining - 1 - (uint32_t)j < last) && !(power > 0.0f) && (alpha >= 1.0f / 255.0f);
                     if (!__any_sync(0xffffffffu, contrib)) continue;
-                    const float2 c = lds_f2(aC + 8u * j);
+                    const f32x2 BD = lds_64(aC + 8u * j);
                     const float al = contrib ? alpha : 0.0f;
                     const float Gc = contrib ? G : 0.0f;
                     const float inv = rcp_approx(1.0f - al);      // exactly 1 for al == 0
                     T *= inv;
                     const float dch = al * T;
-                    // accum_rec recurrence (backward.cu:569-581), folded: acc holds the colour behind this
-                    // layer; once used it absorbs this layer, acc += alpha (c - acc)
-                    float d = b.z - acc_r;
-                    float dL_dalpha = d * dpx0;               acc_r = fmaf(al, d, acc_r);
-                    d = b.w - acc_g;
-                    dL_dalpha = fmaf(d, dpx1, dL_dalpha);     acc_g = fmaf(al, d, acc_g);
-                    d = c.x - acc_b;
-                    dL_dalpha = fmaf(d, dpx2, dL_dalpha);     acc_b = fmaf(al, d, acc_b);
-                    float v0 = dch * dpx0, v1 = dch * dpx1, v2 = dch * dpx2, v3 = 0.0f;
-                    if (HAS_DEPTH) {
-                        d = c.y - acc_d;
-                        dL_dalpha = fmaf(d, dpd, dL_dalpha);  acc_d = fmaf(al, d, acc_d);
-                        v3 = dch * dpd;
-                    }
-                    dL_dalpha = fmaf(dL_dalpha, T, nTf_bg * inv);
+                    // accum_rec recurrence (backward.cu:569-581), folded: ACC holds the colour behind this
+                    // layer; once used it absorbs this layer, acc += alpha (c - acc).  Two channels per
+                    // instruction; without a depth gradient the fourth lane carries DP = 0.
+                    const f32x2 d01 = sub2(RG, ACC01), d2d = sub2(BD, ACC2D);
+                    const f32x2 dots = fma2(d2d, DP2D, mul2(d01, DP01));
+                    ACC01 = fma2(pk(al, al), d01, ACC01);
+                    ACC2D = fma2(pk(al, al), d2d, ACC2D);
+                    float dot_lo, dot_hi;
+                    upk(dots, dot_lo, dot_hi);
+                    const float dL_dalpha = fmaf(dot_lo + dot_hi, T, nTf_bg * inv);
+                    const f32x2 V01 = mul2(DP01, pk(dch, dch)), V23 = mul2(DP2D, pk(dch, dch));
                     // moments of w = G dL/dalpha over the warp's pixels
                     float w1 = Gc * dL_dalpha;
-                    const float wdx = w1 * dx, wdy = w1 * dy;
-                    float v4 = w1 * fmaf(dy, a.w, dxA), v5 = w1 * (dxB + dyC);
-                    float v6 = wdx * dx, v7 = wdx * dy, w0 = wdy * dy;
-                    // transposing butterfly: 8 values -> each lane ends with the warp total of value (lane>>2)
+                    const f32x2 WD = mul2(D, pk(w1, w1));                       // (w dx, w dy)
+                    const f32x2 V68 = mul2(WD, D);                              // (w dx^2, w dy^2)
+                    const f32x2 V45 = mul2(pk(fmaf(dy, cB, dxA), dxB + dyC), pk(w1, w1));   // w (A dx + B dy), w (B dx + C dy)
+                    float v0, v1, v2, v3, v4, v5, v6, v7, w0, wdx, wdy;
+                    upk(V01, v0, v1); upk(V23, v2, v3); upk(V45, v4, v5); upk(V68, v6, w0); upk(WD, wdx, wdy);
+                    v7 = wdx * dy;
+                    // transposing butterfly: 8 values -> each lane ends with the warp total of value (lane>>2);
+                    // the adds go two per instruction
+                    f32x2 S01, S23;
                     {
                         const bool h = lane & 16;
-                        float s, kp;
-                        s = h ? v0 : v4; kp = h ? v4 : v0; v0 = kp + __shfl_xor_sync(0xffffffffu, s, 16);
-                        s = h ? v1 : v5; kp = h ? v5 : v1; v1 = kp + __shfl_xor_sync(0xffffffffu, s, 16);
-                        s = h ? v2 : v6; kp = h ? v6 : v2; v2 = kp + __shfl_xor_sync(0xffffffffu, s, 16);
-                        s = h ? v3 : v7; kp = h ? v7 : v3; v3 = kp + __shfl_xor_sync(0xffffffffu, s, 16);
-                        s = h ? w0 : w1; kp = h ? w1 : w0; w0 = kp + __shfl_xor_sync(0xffffffffu, s, 16);
+                        const f32x2 kp01 = pk(h ? v4 : v0, h ? v5 : v1), kp23 = pk(h ? v6 : v2, h ? v7 : v3);
+                        const float r0 = __shfl_xor_sync(0xffffffffu, h ? v0 : v4, 16), r1 = __shfl_xor_sync(0xffffffffu, h ? v1 : v5, 16);
+                        const float r2 = __shfl_xor_sync(0xffffffffu, h ? v2 : v6, 16), r3 = __shfl_xor_sync(0xffffffffu, h ? v3 : v7, 16);
+                        const float s = h ? w0 : w1, kp = h ? w1 : w0;
+                        w0 = kp + __shfl_xor_sync(0xffffffffu, s, 16);
+                        S01 = add2(kp01, pk(r0, r1)); S23 = add2(kp23, pk(r2, r3));
                     }
                     {
                         const bool h = lane & 8;
-                        float s, kp;
-                        s = h ? v0 : v2; kp = h ? v2 : v0; v0 = kp + __shfl_xor_sync(0xffffffffu, s, 8);
-                        s = h ? v1 : v3; kp = h ? v3 : v1; v1 = kp + __shfl_xor_sync(0xffffffffu, s, 8);
+                        upk(S01, v0, v1); upk(S23, v2, v3);
+                        const f32x2 kp = pk(h ? v2 : v0, h ? v3 : v1);
+                        const float r0 = __shfl_xor_sync(0xffffffffu, h ? v0 : v2, 8), r1 = __shfl_xor_sync(0xffffffffu, h ? v1 : v3, 8);
+                        S01 = add2(kp, pk(r0, r1));
                         w0 += __shfl_xor_sync(0xffffffffu, w0, 8);
                     }
+                    f32x2 VW;    // (v0, w0) from here on
                     {
                         const bool h = lane & 4;
+                        upk(S01, v0, v1);
                         const float s = h ? v0 : v1, kp = h ? v1 : v0;
-                        v0 = kp + __shfl_xor_sync(0xffffffffu, s, 4);
-                        w0 += __shfl_xor_sync(0xffffffffu, w0, 4);
+                        VW = add2(pk(kp, w0), pk(__shfl_xor_sync(0xffffffffu, s, 4), __shfl_xor_sync(0xffffffffu, w0, 4)));
                     }
-                    v0 += __shfl_xor_sync(0xffffffffu, v0, 2); w0 += __shfl_xor_sync(0xffffffffu, w0, 2);
-                    v0 += __shfl_xor_sync(0xffffffffu, v0, 1); w0 += __shfl_xor_sync(0xffffffffu, w0, 1);
+                    upk(VW, v0, w0);
+                    VW = add2(VW, pk(__shfl_xor_sync(0xffffffffu, v0, 2), __shfl_xor_sync(0xffffffffu, w0, 2)));
+                    upk(VW, v0, w0);
+                    VW = add2(VW, pk(__shfl_xor_sync(0xffffffffu, v0, 1), __shfl_xor_sync(0xffffffffu, w0, 1)));
+                    upk(VW, v0, w0);
                     // v0: total of value index (lane>>2) in 0..7 ; w0: total of value 8 + (lane>>4)
                     if (emits) {
-                        const float val = (first ? v0 : w0) * fmaf(oc_b, b.y, oc_a);
+                        const float val = (first ? v0 : w0) * fmaf(oc_b, opac, oc_a);
                         if (val != 0.0f) atomicAdd(obase + (size_t)ostride * ids[j], val);
                     }
                 }

@@ -28,8 +28,8 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   unsigned char* __restrict__ block_masks, const float4* __restrict__ records, int W, int H, int gx,
                   const float* __restrict__ background, float* __restrict__ final_T,
                   uint32_t* __restrict__ n_contrib, float* __restrict__ out_color, float* __restrict__ out_invdepth) {
-    __shared__ float4 sA[2][RF_THREADS];          // x, y, conic.a, conic.b
-    __shared__ float4 sB[2][RF_THREADS];          // conic.c, opacity, r, g
+    __shared__ float4 sA[2][RF_THREADS];          // x, y, conic.a, conic.c   (register pairs for the packed fp32x2 ops)
+    __shared__ float4 sB[2][RF_THREADS];          // conic.b, opacity, r, g
     __shared__ float2 sC[2][RF_THREADS];          // b, 1/depth
     __shared__ unsigned char sMask[2][RF_THREADS];
 
@@ -46,7 +46,9 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     const int todo = (int)(range.y - range.x);
 
     bool done = !inside;
-    float T = 1.0f, C0 = 0.0f, C1 = 0.0f, C2 = 0.0f, Dacc = 0.0f;
+    float T = 1.0f;
+    f32x2 C01 = pk(0.0f, 0.0f), C2D = pk(0.0f, 0.0f);     // (C0, C1), (C2, inverse depth)
+    const f32x2 negP = pk(-pxf, -pyf);
     uint32_t last = 0;
 
     // software pipeline: records of the batch after the current one travel in registers
@@ -62,7 +64,8 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         // Writing buffer `buf` is safe: every warp that passed the previous barrier had finished the
         // batch before it, the last user of `buf`.
         if (tid < n) {
-            sA[buf][tid] = nA; sB[buf][tid] = nB; sC[buf][tid] = make_float2(nC.x, nC.y);
+            sA[buf][tid] = make_float4(nA.x, nA.y, nA.z, nB.x); sB[buf][tid] = make_float4(nA.w, nB.y, nB.z, nB.w);
+            sC[buf][tid] = make_float2(nC.x, nC.y);
             const unsigned m = subblock_mask(make_cull(nA.x, nA.y, nA.z, nA.w, nB.x, nB.y), tile_x0, tile_y0);
             sMask[buf][tid] = (unsigned char)m;
             block_masks[(size_t)range.x + base + tid] = (unsigned char)m;
@@ -84,22 +87,26 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                 bits &= bits - 1;
                 // Straight-line body: a lane that does not blend this Gaussian runs the same arithmetic
                 // with alpha := 0, which leaves C, T bit-identical (C + (c*0)*T = C, T unchanged).
-                const float4 a = lds_f4(aA + 16u * j);
-                const float4 b = lds_f4(aB + 16u * j);
-                const float2 c = lds_f2(aC + 8u * j);
-                const float dx = fsub(a.x, pxf), dy = fsub(a.y, pyf);
-                const float power = blend_power(dx, dy, a.z, a.w, b.x);
-                const float alpha = fminf(0.99f, fmul(b.y, expf(power)));
+                f32x2 XY, AC, BO, RG;
+                lds_2x64(aA + 16u * j, XY, AC);
+                lds_2x64(aB + 16u * j, BO, RG);
+                const f32x2 BD = lds_64(aC + 8u * j);
+                const f32x2 D = add2(XY, negP);             // (x - px, y - py): same rounding as fsub
+                const f32x2 M = mul2(D, AC);                // (dx A, dy C)
+                float dx, dy, dxA, dyC, cB, opac;
+                upk(D, dx, dy); upk(M, dxA, dyC); upk(BO, cB, opac);
+                // blend_power(): FMUL(dy,dyC) ; FFMA(dx,dxA,.) ; FMUL(dx,B) ; FMUL(dy,.) ; FFMA(.,-0.5,-.)
+                const float power = ffma(ffma(dx, dxA, fmul(dy, dyC)), -0.5f, -fmul(dy, fmul(dx, cB)));
+                const float alpha = fminf(0.99f, fmul(opac, expf(power)));
                 const bool contrib = !done && !(power > 0.0f) && (alpha >= 1.0f / 255.0f);
                 const float test_T = fmul(T, fsub(1.0f, alpha));
                 const bool stop = contrib && (test_T < 0.0001f);     // forward.cu:366-371: not blended
                 const bool blend = contrib && !stop;
                 done = done || stop;
                 const float al = blend ? alpha : 0.0f;
-                C0 = ffma(fmul(b.z, al), T, C0);
-                C1 = ffma(fmul(b.w, al), T, C1);
-                C2 = ffma(fmul(c.x, al), T, C2);
-                Dacc = ffma(fmul(c.y, al), T, Dacc);
+                // C += (c * alpha) * T per channel: FMUL2 + FFMA2, each half rounded like FMUL ; FFMA
+                C01 = fma2(mul2(RG, pk(al, al)), pk(T, T), C01);
+                C2D = fma2(mul2(BD, pk(al, al)), pk(T, T), C2D);
                 T = blend ? test_T : T;
                 last = blend ? (uint32_t)(base + j + 1) : last;
             }
@@ -111,6 +118,8 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         const size_t pix = (size_t)py * W + px, HW = (size_t)H * W;
         final_T[pix] = T;
         n_contrib[pix] = last;
+        float C0, C1, C2, Dacc;
+        upk(C01, C0, C1); upk(C2D, C2, Dacc);
         out_color[pix] = ffma(T, background[0], C0);
         out_color[HW + pix] = ffma(T, background[1], C1);
         out_color[2 * HW + pix] = ffma(T, background[2], C2);
