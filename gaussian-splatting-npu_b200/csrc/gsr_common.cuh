@@ -6,7 +6,8 @@
 
 #define GSR_TILE 16
 #define GSR_TILE_PIX 256
-#define GSR_REC_FLOATS 12          // packed per-Gaussian render record, 48 bytes = 3 x float4
+#define GSR_REC_FLOATS 12          // packed per-Gaussian render record, 48 bytes = 3 x float4:
+                                   // (x, y, conic.a, conic.c | conic.b, opacity, r, g | b, 1/depth, 0, 0)
 
 // ---- exactly-rounded arithmetic helpers ------------------------------------------------------
 // The chain that decides depth keys, radii, tile rects and n_contrib must round exactly like the
@@ -144,6 +145,13 @@ __device__ __forceinline__ f32x2 lds_64(uint32_t a) {
     asm volatile("ld.shared.b64 %0, [%1];" : "=l"(v) : "r"(a));
     return v;
 }
+
+// ---- asynchronous global -> shared copies (LDGSTS): the staged batch never occupies registers -----
+__device__ __forceinline__ void cp_async16(uint32_t smem_dst, const void* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(smem_dst), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 // ---- streaming load/store helpers --------------------------------------------------------------
 __device__ __forceinline__ float4 ldg_stream_f4(const float4* p) {

@@ -245,8 +245,8 @@ preprocess_fwd_kernel(FwdParams p, GeomView g, int* __restrict__ radii) {
             g.depths[i] = pvz;
             g.clamped[i] = (unsigned char)clamp_bits;
             float4* rec = g.records + 3 * (size_t)i;
-            rec[0] = make_float4(px, py, conx, cony);
-            rec[1] = make_float4(conz, opac, cr, cg);
+            rec[0] = make_float4(px, py, conx, conz);      // (x, y, conic.a, conic.c): register pairs for the blend's fp32x2 ops
+            rec[1] = make_float4(cony, opac, cr, cg);      // (conic.b, opacity, r, g)
             rec[2] = make_float4(cb, frcp(pvz), 0.0f, 0.0f);
         }
     }

@@ -16,15 +16,19 @@
 //     no retire phase;
 //   * the stage is double-buffered: one CTA barrier per 256-Gaussian batch, and a warp with a short
 //     list runs up to a batch ahead of its neighbours instead of waiting for them;
-//   * the next batch's records are in flight in registers while the current one is processed.
+//   * the next batch's records travel global -> shared with cp.async (LDGSTS) while the current one is
+//     processed: the pipeline holds two registers (a point_list entry and a mask), not fourteen.
 // The per-pixel recurrences are the reference's; power/alpha use the same exactly-rounded chain as
 // the forward so that every pair takes the same skip decision it took there.
 #include "gsr_common.cuh"
 
 #define RB_THREADS 256
+#ifndef RB_MIN_CTAS
+#define RB_MIN_CTAS 5
+#endif
 
 template <bool HAS_DEPTH>
-__global__ void __launch_bounds__(RB_THREADS, 4)
+__global__ void __launch_bounds__(RB_THREADS, RB_MIN_CTAS)
 render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                   const unsigned char* __restrict__ block_masks,
                   const float4* __restrict__ records, int W, int H, int gx, const float* __restrict__ background,
@@ -32,9 +36,9 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvdepth_pix,
                   float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity,
                   float* __restrict__ dL_dcolor, float* __restrict__ dL_dinvdepth) {
-    __shared__ float4 sA[2][RB_THREADS];          // x, y, conic.a, conic.c   (register pairs for the packed fp32x2 ops)
-    __shared__ float4 sB[2][RB_THREADS];          // conic.b, opacity, r, g
-    __shared__ float2 sC[2][RB_THREADS];          // b, 1/depth
+    // stage: the raw 48-byte records (x,y,A,C | B,opacity,r,g | b,1/depth,0,0) of a 256-Gaussian batch,
+    // double-buffered, filled by cp.async
+    __shared__ float4 sRec[2][RB_THREADS * 3];
     __shared__ uint32_t sId[2][RB_THREADS];
     __shared__ unsigned char sMask[2][RB_THREADS];
     __shared__ uint32_t sMax[RB_THREADS / 32];
@@ -97,36 +101,43 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     f32x2 ACC01 = pk(0.0f, 0.0f), ACC2D = pk(0.0f, 0.0f);
     const f32x2 DP01 = pk(dpx0, dpx1), DP2D = pk(dpx2, HAS_DEPTH ? dpd : 0.0f), negP = pk(-pxf, -pyf);
 
-    // software pipeline: the batch after the current one travels in registers
-    uint32_t nId = 0, nMask = 0;
-    float4 nA = make_float4(0, 0, 0, 0), nB = nA, nC = nA;
+    // Software pipeline without staging registers: while batch b is processed, the records of batch b+1
+    // travel global -> shared by cp.async, and the point_list entry + block mask of batch b+2 sit in two
+    // registers.  Batches walk the list backwards: batch k covers positions [remaining-256(k+1), remaining-256k).
+    const uint32_t my_rec0 = smem_addr(&sRec[0][tid * 3]);
+    auto fetch = [&](uint32_t id, uint32_t mask, int b) {
+        const float4* rec = records + 3 * (size_t)id;
+        const uint32_t dst = my_rec0 + (uint32_t)b * (RB_THREADS * 48u);
+        cp_async16(dst, rec); cp_async16(dst + 16u, rec + 1); cp_async16(dst + 32u, rec + 2);
+        sId[b][tid] = id; sMask[b][tid] = (unsigned char)mask;
+    };
+    uint32_t next_id = 0, next_mask = 0;
     if ((uint32_t)tid < remaining) {
         const size_t pos = (size_t)range.x + remaining - 1 - tid;
-        nId = point_list[pos]; nMask = block_masks[pos];
-        const float4* rec = records + 3 * (size_t)nId;
-        nA = rec[0]; nB = rec[1]; nC = rec[2];
+        fetch(point_list[pos], block_masks[pos], 0);
+    }
+    cp_async_commit();
+    if ((uint32_t)(RB_THREADS + tid) < remaining) {
+        const size_t pos = (size_t)range.x + remaining - 1 - RB_THREADS - tid;
+        next_id = point_list[pos]; next_mask = block_masks[pos];
     }
 
     int buf = 0;
     while (remaining > 0) {
         const int n = (int)min((uint32_t)RB_THREADS, remaining);
-        // stage positions [remaining-n, remaining), backmost first.  Writing buffer `buf` is safe: every
-        // warp that passed the previous barrier had finished the batch before it, the last user of `buf`.
-        if (tid < n) {
-            sId[buf][tid] = nId; sA[buf][tid] = make_float4(nA.x, nA.y, nA.z, nB.x);
-            sB[buf][tid] = make_float4(nA.w, nB.y, nB.z, nB.w); sC[buf][tid] = make_float2(nC.x, nC.y);
-            sMask[buf][tid] = (unsigned char)nMask;
-        }
+        cp_async_wait_all();                   // this thread's record of the current batch has landed
+        // One barrier per batch: publishes stage `buf` and proves that every warp has left the batch before
+        // this one -- the last reader of stage `buf ^ 1`, which is refilled right below.
         __syncthreads();
-        if ((uint32_t)(RB_THREADS + tid) < remaining) {
-            const size_t pos = (size_t)range.x + remaining - 1 - RB_THREADS - tid;
-            nId = point_list[pos]; nMask = block_masks[pos];
-            const float4* rec = records + 3 * (size_t)nId;
-            nA = rec[0]; nB = rec[1]; nC = rec[2];
+        if ((uint32_t)(RB_THREADS + tid) < remaining) fetch(next_id, next_mask, buf ^ 1);
+        cp_async_commit();
+        if ((uint32_t)(2 * RB_THREADS + tid) < remaining) {
+            const size_t pos = (size_t)range.x + remaining - 1 - 2 * RB_THREADS - tid;
+            next_id = point_list[pos]; next_mask = block_masks[pos];
         }
         // positions this warp still has to look at: below its deepest n_contrib
         if (remaining - (uint32_t)n < wmax) {
-            const uint32_t aA = smem_addr(sA[buf]), aB = smem_addr(sB[buf]), aC = smem_addr(sC[buf]);
+            const uint32_t aRec = smem_addr(sRec[buf]);
             const uint32_t* ids = sId[buf];
             const unsigned char* masks = sMask[buf];
 #pragma unroll 1
@@ -141,8 +152,8 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                     // (a zero-alpha layer: T/(1-0) = T, acc + 0*(c-acc) = acc) and makes all ten of its
                     // partial sums exactly 0 -- no divergence, no zero-initialisation.
                     f32x2 XY, AC, BO, RG;
-                    lds_2x64(aA + 16u * j, XY, AC);
-                    lds_2x64(aB + 16u * j, BO, RG);
+                    lds_2x64(aRec + 48u * j, XY, AC);
+                    lds_2x64(aRec + 48u * j + 16u, BO, RG);
                     const f32x2 D = add2(XY, negP);             // (x - px, y - py): same rounding as fsub
                     const f32x2 M = mul2(D, AC);                // (dx A, dy C)
                     float dx, dy, dxA, dyC, cB, opac;
@@ -154,7 +165,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                     const float alpha = fminf(0.99f, fmul(opac, G));
                     const bool contrib = (remaining - 1 - (uint32_t)j < last) && !(power > 0.0f) && (alpha >= 1.0f / 255.0f);
                     if (!__any_sync(0xffffffffu, contrib)) continue;
-                    const f32x2 BD = lds_64(aC + 8u * j);
+                    const f32x2 BD = lds_64(aRec + 48u * j + 32u);
                     const float al = contrib ? alpha : 0.0f;
                     const float Gc = contrib ? G : 0.0f;
                     const float inv = rcp_approx(1.0f - al);      // exactly 1 for al == 0
@@ -222,6 +233,7 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         remaining -= n;
         buf ^= 1;
     }
+    cp_async_wait_all();
 }
 
 void launch_render_bwd(const BwdParams& p, const uint2* ranges, const uint32_t* point_list, const unsigned char* block_masks,

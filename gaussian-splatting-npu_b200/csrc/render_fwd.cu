@@ -6,7 +6,8 @@
 //   * a Gaussian's whole blend record (xy, conic, opacity, rgb, 1/depth) is staged in shared
 //     memory by the cooperative fetch, so the inner loop never touches global memory (the
 //     reference fetches colour and depth from global for every contributing pair); the NEXT
-//     batch's records are already in flight in registers while the current batch is blended;
+//     batch's records travel global -> shared with cp.async (LDGSTS) while the current batch is
+//     blended, so the pipeline holds one register (a point_list entry), not twelve;
 //   * a warp covers an 8x4 pixel block, and while staging, each thread tests ITS Gaussian against
 //     the eight 8x4 blocks of the tile with an exact, conservatively rounded bound
 //     (rect_may_contribute): every warp then walks only the staged Gaussians that can reach
@@ -22,15 +23,17 @@
 #include "gsr_common.cuh"
 
 #define RF_THREADS 256
+#ifndef RF_MIN_CTAS
+#define RF_MIN_CTAS 5
+#endif
 
-__global__ void __launch_bounds__(RF_THREADS)
+__global__ void __launch_bounds__(RF_THREADS, RF_MIN_CTAS)
 render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                   unsigned char* __restrict__ block_masks, const float4* __restrict__ records, int W, int H, int gx,
                   const float* __restrict__ background, float* __restrict__ final_T,
                   uint32_t* __restrict__ n_contrib, float* __restrict__ out_color, float* __restrict__ out_invdepth) {
-    __shared__ float4 sA[2][RF_THREADS];          // x, y, conic.a, conic.c   (register pairs for the packed fp32x2 ops)
-    __shared__ float4 sB[2][RF_THREADS];          // conic.b, opacity, r, g
-    __shared__ float2 sC[2][RF_THREADS];          // b, 1/depth
+    // stage: the raw 48-byte records of a 256-Gaussian batch, double-buffered, filled by cp.async
+    __shared__ float4 sRec[2][RF_THREADS * 3];
     __shared__ unsigned char sMask[2][RF_THREADS];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -51,31 +54,35 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     const f32x2 negP = pk(-pxf, -pyf);
     uint32_t last = 0;
 
-    // software pipeline: records of the batch after the current one travel in registers
-    float4 nA = make_float4(0, 0, 0, 0), nB = nA, nC = nA;
-    if (tid < todo) {
-        const float4* rec = records + 3 * (size_t)point_list[range.x + tid];
-        nA = rec[0]; nB = rec[1]; nC = rec[2];
-    }
+    // Software pipeline without staging registers: while batch b is blended, the records of batch b+1
+    // travel global -> shared by cp.async and the point_list entry of batch b+2 sits in ONE register.
+    const uint32_t my_rec0 = smem_addr(&sRec[0][tid * 3]);
+    auto fetch = [&](uint32_t id, int b) {
+        const float4* rec = records + 3 * (size_t)id;
+        const uint32_t dst = my_rec0 + (uint32_t)b * (RF_THREADS * 48u);
+        cp_async16(dst, rec); cp_async16(dst + 16u, rec + 1); cp_async16(dst + 32u, rec + 2);
+    };
+    if (tid < todo) fetch(point_list[range.x + tid], 0);
+    cp_async_commit();
+    uint32_t next_id = (RF_THREADS + tid < todo) ? point_list[range.x + RF_THREADS + tid] : 0u;
 
     int buf = 0;
     for (int base = 0; base < todo; base += RF_THREADS, buf ^= 1) {
         const int n = min(RF_THREADS, todo - base);
-        // Writing buffer `buf` is safe: every warp that passed the previous barrier had finished the
-        // batch before it, the last user of `buf`.
+        cp_async_wait_all();                   // this thread's record of batch `base` has landed
         if (tid < n) {
-            sA[buf][tid] = make_float4(nA.x, nA.y, nA.z, nB.x); sB[buf][tid] = make_float4(nA.w, nB.y, nB.z, nB.w);
-            sC[buf][tid] = make_float2(nC.x, nC.y);
-            const unsigned m = subblock_mask(make_cull(nA.x, nA.y, nA.z, nA.w, nB.x, nB.y), tile_x0, tile_y0);
+            const float4 rA = sRec[buf][tid * 3], rB = sRec[buf][tid * 3 + 1];      // (x,y,A,C) (B,opacity,r,g)
+            const unsigned m = subblock_mask(make_cull(rA.x, rA.y, rA.z, rB.x, rA.w, rB.y), tile_x0, tile_y0);
             sMask[buf][tid] = (unsigned char)m;
             block_masks[(size_t)range.x + base + tid] = (unsigned char)m;
         }
+        // One barrier per batch: publishes stage `buf`, carries the "all pixels done" count, and proves that
+        // every warp has left the batch before this one -- the last reader of stage `buf ^ 1`, refilled next.
         if (__syncthreads_count(done) == RF_THREADS) break;
-        if (base + RF_THREADS + tid < todo) {
-            const float4* rec = records + 3 * (size_t)point_list[range.x + base + RF_THREADS + tid];
-            nA = rec[0]; nB = rec[1]; nC = rec[2];
-        }
-        const uint32_t aA = smem_addr(sA[buf]), aB = smem_addr(sB[buf]), aC = smem_addr(sC[buf]);
+        if (base + RF_THREADS + tid < todo) fetch(next_id, buf ^ 1);
+        cp_async_commit();
+        if (base + 2 * RF_THREADS + tid < todo) next_id = point_list[range.x + base + 2 * RF_THREADS + tid];
+        const uint32_t aRec = smem_addr(sRec[buf]);
         const unsigned char* masks = sMask[buf];
         if (__all_sync(0xffffffffu, done)) continue;           // this warp's 32 pixels are saturated
 #pragma unroll 1
@@ -88,9 +95,9 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                 // Straight-line body: a lane that does not blend this Gaussian runs the same arithmetic
                 // with alpha := 0, which leaves C, T bit-identical (C + (c*0)*T = C, T unchanged).
                 f32x2 XY, AC, BO, RG;
-                lds_2x64(aA + 16u * j, XY, AC);
-                lds_2x64(aB + 16u * j, BO, RG);
-                const f32x2 BD = lds_64(aC + 8u * j);
+                lds_2x64(aRec + 48u * j, XY, AC);
+                lds_2x64(aRec + 48u * j + 16u, BO, RG);
+                const f32x2 BD = lds_64(aRec + 48u * j + 32u);
                 const f32x2 D = add2(XY, negP);             // (x - px, y - py): same rounding as fsub
                 const f32x2 M = mul2(D, AC);                // (dx A, dy C)
                 float dx, dy, dxA, dyC, cB, opac;
@@ -114,6 +121,7 @@ render_fwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         }
     }
 
+    cp_async_wait_all();      // nothing may still be in flight into this CTA's shared memory at exit
     if (inside) {
         const size_t pix = (size_t)py * W + px, HW = (size_t)H * W;
         final_T[pix] = T;

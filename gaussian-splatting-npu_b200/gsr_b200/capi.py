@@ -14,7 +14,7 @@ from ctypes import (CFUNCTYPE, POINTER, Structure, c_char_p, c_float, c_int, c_s
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgsr_b200.so")
+LIB_PATH = os.environ.get("GSR_B200_LIB") or os.path.join(_HERE, "libgsr_b200.so")   # override: kernel A/B experiments only
 
 ALLOC_FN = CFUNCTYPE(c_void_p, c_size_t, c_void_p)
 
@@ -240,7 +240,7 @@ def introspect(state):
     clamp = _view(state["geom"], gl.clamped, P, torch.uint8)
     o = dict(
         depths=_view(state["geom"], gl.depths, P, torch.float32),
-        means2D=rec[:, 0:2], conic_opacity=rec[:, 2:6], rgb=rec[:, 6:9], invdepth_g=rec[:, 9],
+        means2D=rec[:, 0:2], conic_opacity=rec[:, [2, 4, 3, 5]], rgb=rec[:, 6:9], invdepth_g=rec[:, 9],
         cov3D=_view(state["geom"], gl.cov3D, P * 6, torch.float32).view(P, 6),
         clamped=torch.stack([(clamp >> c) & 1 for c in range(3)], dim=1),
         tiles_touched=_view(state["geom"], gl.tiles_touched, P, torch.int32),
