@@ -16,6 +16,7 @@
 #include "gsr_common.cuh"
 
 #define SCAN_THREADS 256
+#define SCAN_LOOKBACK 8
 #define SCAN_IPT (GSR_SCAN_ITEMS / SCAN_THREADS)   // 16
 
 __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
@@ -35,14 +36,25 @@ __device__ __forceinline__ uint32_t lookback(unsigned long long* status, uint32_
         st_volatile_u64(&status[0], (2ull << 32) | aggregate);
     } else {
         st_volatile_u64(&status[tile], (1ull << 32) | aggregate);
+        // SCAN_LOOKBACK predecessors per round trip (independent volatile loads), consumed in order; an
+        // unpublished word stops the round and is re-read by the next one
         int t = (int)tile - 1;
-        while (true) {
-            const unsigned long long w = ld_volatile_u64(&status[t]);
-            const uint32_t flag = (uint32_t)(w >> 32);
-            if (flag == 0) continue;
-            excl += (uint32_t)w;
-            if (flag == 2) break;
-            t--;
+        bool found = false;
+        while (!found) {
+            unsigned long long w[SCAN_LOOKBACK];
+#pragma unroll
+            for (int k = 0; k < SCAN_LOOKBACK; k++) w[k] = (t - k >= 0) ? ld_volatile_u64(&status[t - k]) : (2ull << 32);
+            int used = 0;
+#pragma unroll
+            for (int k = 0; k < SCAN_LOOKBACK; k++) {
+                const uint32_t flag = (uint32_t)(w[k] >> 32);
+                if (!found && used == k && flag != 0) {
+                    excl += (uint32_t)w[k];
+                    used = k + 1;
+                    found = flag == 2;
+                }
+            }
+            t -= used;
         }
         st_volatile_u64(&status[tile], (2ull << 32) | (uint32_t)(excl + aggregate));
     }

@@ -159,6 +159,15 @@ preprocess_fwd_kernel(FwdParams p, GeomView g, int* __restrict__ radii) {
     int rad = 0, tiles = 0;
     if (in) {
         x = p.means3D[3 * (size_t)i]; y = p.means3D[3 * (size_t)i + 1]; z = p.means3D[3 * (size_t)i + 2];
+        // scale / rotation / opacity are fetched together with the mean, before the near-plane test: one
+        // round trip to HBM instead of three dependent ones (the kernel is latency-bound, not byte-bound)
+        float4 q = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f;
+        if (!p.cov3D_precomp) {
+            q = reinterpret_cast<const float4*>(p.rotations)[i];
+            s0 = p.scales[3 * (size_t)i]; s1 = p.scales[3 * (size_t)i + 1]; s2 = p.scales[3 * (size_t)i + 2];
+        }
+        const float opacity_in = p.opacities[i];
         pvz = xform_row(V, 2, x, y, z);
         if (pvz <= 0.2f) {
             if (p.prefiltered) atomicAdd(&g.scan_state[1], 1u);
@@ -171,9 +180,7 @@ preprocess_fwd_kernel(FwdParams p, GeomView g, int* __restrict__ radii) {
 #pragma unroll
                 for (int k = 0; k < 6; k++) c6[k] = p.cov3D_precomp[6 * (size_t)i + k];
             } else {
-                const float4 q = reinterpret_cast<const float4*>(p.rotations)[i];
-                cov3d_from_scale_rot(p.scales[3 * (size_t)i], p.scales[3 * (size_t)i + 1], p.scales[3 * (size_t)i + 2],
-                                     p.scale_modifier, q, c6);
+                cov3d_from_scale_rot(s0, s1, s2, p.scale_modifier, q, c6);
             }
             float cxx, cxy, cyy;
             cov2d_ewa(x, y, z, p.focal_x, p.focal_y, p.tan_fovx, p.tan_fovy, c6, V, cxx, cxy, cyy);
@@ -197,7 +204,7 @@ preprocess_fwd_kernel(FwdParams p, GeomView g, int* __restrict__ radii) {
                 tiles = (x1 - x0) * (y1 - y0);
                 if (tiles != 0) {
                     visible = true;
-                    opac = fmul(p.opacities[i], hscale);
+                    opac = fmul(opacity_in, hscale);
                     if (!p.cov3D_precomp) {
                         float2* cv = reinterpret_cast<float2*>(g.cov3D + 6 * (size_t)i);
                         cv[0] = make_float2(c6[0], c6[1]); cv[1] = make_float2(c6[2], c6[3]); cv[2] = make_float2(c6[4], c6[5]);

@@ -22,6 +22,7 @@
 #define RADIX 256
 #define SORT_MAX_PASSES 8
 
+#define LOOKBACK_UNROLL 8
 #define STATUS_LOCAL 0x40000000u
 #define STATUS_INCL 0x80000000u
 #define STATUS_VMASK 0x3fffffffu
@@ -120,12 +121,16 @@ onesweep_kernel(const KeyT* __restrict__ kin, const uint32_t* __restrict__ vin, 
     const size_t n = n_dev ? (size_t)*n_dev : n_host;
 
     if (tid == 0) sm.tile = atomicAdd(counter, 1u);
-#pragma unroll
-    for (int w = 0; w < SORT_WARPS; w++) sm.warp_hist[w][tid] = 0;
     __syncthreads();
     const uint32_t tile = sm.tile;
     const size_t tile_base = (size_t)tile * SORT_TILE;
-    if (tile_base >= n) return;                // grid sized for an upper bound (device-side n)
+    if (tile_base >= n) return;                // grid sized for an upper bound (device-side n): leave at once
+    {   // each warp clears its own digit counters (read back only by this warp in step 2)
+        uint32_t* whz = sm.warp_hist[warp];
+#pragma unroll
+        for (int k = 0; k < RADIX / 32; k++) whz[k * 32 + lane] = 0;
+        __syncwarp();
+    }
     const uint32_t tile_n = (uint32_t)min((size_t)SORT_TILE, n - tile_base);
     const size_t my_base = tile_base + (size_t)warp * (32 * SORT_IPT) + lane;
 
@@ -188,15 +193,31 @@ onesweep_kernel(const KeyT* __restrict__ kin, const uint32_t* __restrict__ vin, 
     const uint32_t g_excl = offb + b - gh;            // exclusive, whole array
 
     // 5. decoupled look-back: sum of this digit's counts over all predecessor tiles
+    //    The walk reads LOOKBACK_UNROLL predecessors per round trip (independent volatile loads in
+    //    flight together) and consumes them in order: when all CTAs of a pass are resident at once the
+    //    nearest INCLUSIVE word can be dozens of tiles back, and one L2 round trip per tile was the
+    //    critical path of the small (Gaussian-level) sort.
     uint32_t prefix = 0;
     if (tile > 0) {
         int t = (int)tile - 1;
-        while (true) {
-            const uint32_t w = ld_volatile_u32(status + (size_t)t * RADIX + tid);
-            if ((w & (STATUS_LOCAL | STATUS_INCL)) == 0) continue;
-            prefix += w & STATUS_VMASK;
-            if (w & STATUS_INCL) break;
-            t--;
+        bool found = false;
+        while (!found) {
+            uint32_t w[LOOKBACK_UNROLL];
+#pragma unroll
+            for (int k = 0; k < LOOKBACK_UNROLL; k++)
+                w[k] = (t - k >= 0) ? ld_volatile_u32(status + (size_t)(t - k) * RADIX + tid) : STATUS_INCL;
+            int used = 0;
+#pragma unroll
+            for (int k = 0; k < LOOKBACK_UNROLL; k++) {
+                if (!found && used == k) {
+                    if (w[k] & (STATUS_LOCAL | STATUS_INCL)) {
+                        prefix += w[k] & STATUS_VMASK;
+                        used = k + 1;
+                        found = (w[k] & STATUS_INCL) != 0;
+                    }
+                }
+            }
+            t -= used;          // an unpublished word stops the round; it is re-read in the next one
         }
         st_volatile_u32(my_status, STATUS_INCL | (prefix + count));
     }
