@@ -296,8 +296,13 @@ def main():
         g = capi.backward(st, dL_dcolor=dcol, dL_dinvdepth=ddep, out=grad_views, **per_view[0])
         for k, v in capi.stage_times_ms().items():
             stage.setdefault(k, []).append(v)
+    acc_ms = []
+    for _ in range(3):      # the same view once more in accumulate mode (views 2..V of a step)
+        capi.backward(st, dL_dcolor=dcol, dL_dinvdepth=ddep, out=grad_views, accumulate=True, **per_view[0])
+        acc_ms.append(capi.stage_times_ms()["preprocess_bwd"])
     capi.set_profiling(False)
     stage_ms = {k: float(np.median(v)) for k, v in stage.items()}
+    stage_ms["preprocess_bwd_accumulate"] = float(np.median(acc_ms))
     it = capi.introspect(st)
     pairs_bwd_eval = int(it["n_contrib"].to(torch.int64).sum().item())
     P_vis = int((st["radii"] > 0).sum().item())
@@ -442,7 +447,7 @@ def main():
                         stages[k_]["traffic"] = v_
                         stages[k_]["traffic_source"] = "profiles/" + os.path.basename(tf)
                 break
-        dominant = max(stage_ms, key=lambda k: stage_ms[k] if k != "host_sync" else -1)
+        dominant = max(stage_ms, key=lambda k: stage_ms[k] if k not in ("host_sync", "preprocess_bwd_accumulate") else -1)
         roof = dict(stages.get(dominant, {}))
         roof["kernel"] = dominant
         roof.setdefault("traffic", None)

@@ -165,6 +165,13 @@ __device__ __forceinline__ void stg_stream_f4(float4* p, float4 v) {
                  :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
+// fire-and-forget 16-byte add into global memory (REDG.ADD.F32x4): the L2 does the read-modify-write,
+// the SM never waits for the old value
+__device__ __forceinline__ void red_add_f4(float4* p, float4 v) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
 // ---- scratch buffer views ----------------------------------------------------------------------
 struct GeomView {
     float* depths;            // [P]

@@ -251,13 +251,8 @@ preprocess_bwd_kernel(BwdParams p, GeomView g) {
                 for (int it = 0; it < 12; it++) {
                     const int f = it * 32 + lane;
                     const int row = f / 12, j = f - row * 12;
-                    if (ACC) {           // add into the visible rows, leave the others alone
-                        if ((vmask >> row) & 1u) {
-                            float4 v = st[row * 12 + (j ^ ((row >> 1) & 3))];
-                            const float4 o = dst[f];
-                            v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
-                            dst[f] = v;
-                        }
+                    if (ACC) {           // add into the visible rows, leave the others alone: one vector RED per 16 bytes
+                        if ((vmask >> row) & 1u) red_add_f4(dst + f, st[row * 12 + (j ^ ((row >> 1) & 3))]);
                     } else if (warp_first + row < (size_t)p.P) stg_stream_f4(dst + f, st[row * 12 + (j ^ ((row >> 1) & 3))]);
                 }
             } else if (!ACC) {                              // a fully culled warp: 6 KB of zeros, no staging
@@ -295,7 +290,7 @@ preprocess_bwd_kernel(BwdParams p, GeomView g) {
     const bool acc = ACC;
     if (acc && !vis) return;                 // accumulate mode: invisible rows keep what they hold
     float* om = p.dL_dmean3D + 3 * (size_t)i;
-    if (acc) { om[0] += dmx; om[1] += dmy; om[2] += dmz; p.dL_dopacity[i] += dop_out; }
+    if (acc) { atomicAdd(om, dmx); atomicAdd(om + 1, dmy); atomicAdd(om + 2, dmz); atomicAdd(p.dL_dopacity + i, dop_out); }
     else { om[0] = dmx; om[1] = dmy; om[2] = dmz; p.dL_dopacity[i] = dop_out; }
     // ---------------- computeCov3D backward (backward.cu:330-393) ----------------
     if (p.scales) {
@@ -338,9 +333,8 @@ preprocess_bwd_kernel(BwdParams p, GeomView g) {
         float* os = p.dL_dscale + 3 * (size_t)i;
         float4* oq = reinterpret_cast<float4*>(p.dL_drot) + i;
         if (acc) {
-            os[0] += ds[0]; os[1] += ds[1]; os[2] += ds[2];
-            const float4 o = *oq;
-            *oq = make_float4(o.x + dq.x, o.y + dq.y, o.z + dq.z, o.w + dq.w);
+            atomicAdd(os, ds[0]); atomicAdd(os + 1, ds[1]); atomicAdd(os + 2, ds[2]);
+            red_add_f4(oq, dq);
         } else {
             os[0] = ds[0]; os[1] = ds[1]; os[2] = ds[2];
             *oq = dq;
