@@ -153,6 +153,92 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi"}
 
 
+def loss_stage_report(dev, H, W, hbm_peak, reps=30):
+    """Loss stage next to the path: fused L1 + D-SSIM forward + backward on one [3,H,W] view.
+    CUDA-event times, L2 flushed between repetitions (the 25 MB images would otherwise stay in the 126 MB L2).
+    Rows: ours fused (2 kernels + 1 reduction), ours through the reference's fused_ssim API + torch L1, and -- when
+    oracle/_ref holds it -- the unmodified reference fused-ssim CUDA kernels + torch L1 on this GPU."""
+    import torch
+    from gsr_b200 import capi
+    from fused_ssim import fused_ssim as our_fused_ssim
+    torch.manual_seed(3)
+    img = torch.rand(3, H, W, device=dev)
+    gt = (img + 0.05 * torch.randn_like(img)).clamp(0, 1)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    scratch = capi.LossScratch((3, H, W), dev)
+    n = 3 * H * W
+
+    def timed(fn):
+        for _ in range(3):
+            fn()
+        ts = []
+        for _ in range(reps):
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b))
+        return float(np.median(ts))
+
+    def ours_fused():
+        capi.l1_ssim_loss_forward(img, gt, 0.2, scratch, train=True)
+        capi.l1_ssim_loss_backward(img, gt, 0.2, scratch, upstream=None)
+
+    def composed(ssim_fn):
+        def run():
+            a = img.detach().requires_grad_(True)
+            loss = 0.8 * torch.abs(a - gt).mean() + 0.2 * (1.0 - ssim_fn(a.unsqueeze(0), gt.unsqueeze(0)))
+            loss.backward()
+        return run
+
+    t_fwd = timed(lambda: capi.l1_ssim_loss_forward(img, gt, 0.2, scratch, train=True))
+    t_bwd = timed(lambda: capi.l1_ssim_loss_backward(img, gt, 0.2, scratch, upstream=None))
+    t_ours = timed(ours_fused)
+    # algorithmic bytes per pixel-channel: fwd reads image + gt (8) and writes 3 derivative maps (12);
+    # bwd reads the 3 maps + image + gt (20) and writes the gradient (4)
+    bytes_fwd, bytes_bwd = 20 * n, 24 * n
+    rep = {"workload": "one [3,%d,%d] view, loss = 0.8*L1 + 0.2*(1-SSIM), forward + backward" % (H, W),
+           "ours_fused_ms": t_ours, "ours_fused_fwd_ms": t_fwd, "ours_fused_bwd_ms": t_bwd, "gpu_launches": 3,
+           "roofline": {"bound": "hbm", "algorithmic_bytes": bytes_fwd + bytes_bwd, "achieved": (bytes_fwd + bytes_bwd) / (t_fwd + t_bwd) / 1e6,
+                        "peak": hbm_peak, "unit": "GB/s", "frac": (bytes_fwd + bytes_bwd) / (t_fwd + t_bwd) / 1e6 / hbm_peak,
+                        "fwd_frac": bytes_fwd / t_fwd / 1e6 / hbm_peak, "bwd_frac": bytes_bwd / t_bwd / 1e6 / hbm_peak},
+           "ours_reference_api_ms": timed(composed(our_fused_ssim))}
+    try:
+        from oracle import build_ref
+        ref = build_ref.load_fused_ssim()
+        if ref is not None:
+            class RefMap(torch.autograd.Function):      # FS/fused_ssim/__init__.py:8-31 over the reference extension
+                @staticmethod
+                def forward(ctx, a, b):
+                    m, d0, d1, d2 = ref.fusedssim(0.01 ** 2, 0.03 ** 2, a, b, True)
+                    ctx.save_for_backward(a.detach(), b, d0, d1, d2)
+                    return m
+
+                @staticmethod
+                def backward(ctx, g):
+                    a, b, d0, d1, d2 = ctx.saved_tensors
+                    return ref.fusedssim_backward(0.01 ** 2, 0.03 ** 2, a, b, g.contiguous(), d0, d1, d2), None
+            rep["reference_cuda_same_box_ms"] = timed(composed(lambda a, b: RefMap.apply(a, b).mean()))
+    except Exception as exc:  # informational leg only
+        rep["reference_cuda_same_box_error"] = str(exc)[:200]
+    return rep
+
+
+def loss_cpu_baseline(H, W):
+    """The loss stage's CPU oracle (port of the reference algorithm) on one full view, all host threads."""
+    from oracle import ssim_oracle as so
+    rng = np.random.default_rng(3)
+    img = rng.random((3, H, W), dtype=np.float32)
+    gt = np.clip(img + 0.05 * rng.standard_normal((3, H, W)).astype(np.float32), 0, 1)
+    so.l1_ssim_loss(img[:, :64, :64], gt[:, :64, :64], 0.2)
+    t0 = time.perf_counter()
+    so.l1_ssim_loss(img, gt, 0.2)
+    return {"ms": (time.perf_counter() - t0) * 1e3, "cores": so.num_threads(), "kind": "port",
+            "sample": "one full [3,%d,%d] view, loss forward + backward" % (H, W)}
+
+
 def run_reference(args):
     """--impl reference: the reference algorithm's CPU implementation (oracle port), all host threads."""
     rank = int(os.environ.get("RANK", "0"))
@@ -311,6 +397,7 @@ def main():
     rs_kw = dict(image_height=H, image_width=W, bg=bg, scale_modifier=1.0,
                  sh_degree=3, prefiltered=False, debug=False, antialiasing=w["aa"])
     from diff_gaussian_rasterization import grad_sink
+    from fused_ssim import l1_ssim_loss
     rng9 = np.random.default_rng(9)
     target_host = [torch.from_numpy(rng9.random((3, H, W), dtype=np.float32)).pin_memory() for _ in range(min(V, 2))]
     cam_host = [torch.from_numpy(np.concatenate([c.world_view_transform.ravel(), c.full_proj_transform.ravel(),
@@ -330,7 +417,7 @@ def main():
 
     def api_step():
         """One training-step's worth of rendering through the public API: for each of this rank's V views the camera
-        and the target image come from pinned host memory, GaussianRasterizer renders, an L1 loss is taken and
+        and the target image come from pinned host memory, GaussianRasterizer renders, the training loss (0.8 L1 + 0.2 D-SSIM, fused) is taken and
         backpropagated; parameter gradients of the V views add up in the flat bucket (grad_sink), which is
         all-reduced over ranks; the step's loss is read back to the host."""
         loss_dev.zero_()
@@ -354,7 +441,7 @@ def main():
             means2D = torch.zeros_like(params["xyz"], requires_grad=True)
             color, radii, invd = GaussianRasterizer(rs)(means3D=params["xyz"], means2D=means2D, opacities=params["opacity"],
                                                         shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
-            loss = (color - td).abs().mean()
+            loss = l1_ssim_loss(color, td, 0.2)               # train.py:118-126, two fused launches
             with grad_sink(*sink, accumulate=(v > 0)):
                 loss.backward()
             loss_dev.add_(loss.detach())
@@ -472,10 +559,14 @@ def main():
             "clocks": clocks,
             "e2e": {"value": e2e_val, "unit": "renders/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms / args.steps,
-                    "what": "per view: camera + target image from pinned host memory (copy stream, double-buffered, overlapping the previous view's kernels), GaussianRasterizer autograd fwd+bwd + L1 loss; per step: gradients of the rank's views summed in the bucket (grad_sink), all-reduce when N>1, loss read back"},
+                    "what": "per view: camera + target image from pinned host memory (copy stream, double-buffered, overlapping the previous view's kernels), GaussianRasterizer autograd fwd+bwd + the fused training loss 0.8*L1 + 0.2*(1-SSIM) (fused_ssim.l1_ssim_loss); per step: gradients of the rank's views summed in the bucket (grad_sink), all-reduce when N>1, loss read back"},
             "gpu_launches": launches_per_step * V * args.steps,
             "stage_ms": stage_ms, "roofline": roof, "roofline_stages": stages, "cpu_baseline": cpu,
         }
+        if world == 1:
+            out["loss_stage"] = loss_stage_report(dev, H, W, hbm_peak)
+            if not args.no_cpu_baseline:
+                out["loss_stage"]["cpu_baseline"] = loss_cpu_baseline(H, W)
         # same-box bar: the unmodified reference CUDA kernels (oracle/_ref), informational
         if not args.no_ref_cuda and world == 1:
             try:

@@ -20,7 +20,7 @@ LIB = os.path.join(HERE, "gsr_b200", "libgsr_b200.so")
 PKG = os.path.join(HERE, "diff_gaussian_rasterization")
 
 CU_SOURCES = ["gsr_api.cu", "preprocess_fwd.cu", "binning.cu", "radix_sort.cu", "render_fwd.cu",
-              "render_bwd.cu", "preprocess_bwd.cu"]
+              "render_bwd.cu", "preprocess_bwd.cu", "ssim.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
 
@@ -38,7 +38,8 @@ def ext_path():
 
 def build_lib(force=False, verbose=False):
     os.makedirs(OBJ, exist_ok=True)
-    headers = [os.path.join(CSRC, "gsr_common.cuh"), os.path.join(ROOT, "include", "gsr.h")]
+    headers = [os.path.join(CSRC, "gsr_common.cuh"), os.path.join(ROOT, "include", "gsr.h"),
+               os.path.join(ROOT, "include", "gsr_loss.h")]
     objs, jobs = [], []
     for src in CU_SOURCES:
         s = os.path.join(CSRC, src)
@@ -66,26 +67,44 @@ def build_lib(force=False, verbose=False):
     return LIB
 
 
-def build_ext(force=False):
+def ssim_ext_path():
+    return os.path.join(HERE, "fused_ssim_cuda" + sysconfig.get_config_var("EXT_SUFFIX"))
+
+
+def _compile_ext(name, sources, out, defines=()):
     import torch
     from torch.utils import cpp_extension as ce
-    src = os.path.join(CSRC, "torch_binding.cpp")
-    out = ext_path()
-    if not force and _newer(out, [src, os.path.join(ROOT, "include", "gsr.h"), LIB]):
-        return out
     inc = []
     for p in ce.include_paths("cuda") if "device_type" in ce.include_paths.__code__.co_varnames else ce.include_paths(cuda=True):
         inc += ["-I", p]
     inc += ["-I", sysconfig.get_paths()["include"], "-I", os.path.join(ROOT, "include"), "-I", "/usr/local/cuda/include"]
     tlib = os.path.join(os.path.dirname(torch.__file__), "lib")
     abi = int(torch._C._GLIBCXX_USE_CXX11_ABI)
-    cmd = ["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-DTORCH_EXTENSION_NAME=_C", "-DTORCH_API_INCLUDE_EXTENSION_H",
-           "-D_GLIBCXX_USE_CXX11_ABI=%d" % abi, *inc, src, "-o", out + ".tmp",
+    rel = os.path.relpath(os.path.dirname(LIB), os.path.dirname(out))
+    cmd = ["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-DTORCH_EXTENSION_NAME=" + name, "-DTORCH_API_INCLUDE_EXTENSION_H",
+           "-D_GLIBCXX_USE_CXX11_ABI=%d" % abi, *defines, *inc, *sources, "-o", out + ".tmp",
            "-L", tlib, "-lc10", "-lc10_cuda", "-ltorch_cpu", "-ltorch_cuda", "-ltorch", "-ltorch_python",
            "-L", os.path.dirname(LIB), "-lgsr_b200", "-L", "/usr/local/cuda/lib64", "-lcudart",
-           "-Wl,-rpath,$ORIGIN/../gsr_b200", "-Wl,-rpath," + tlib]
+           "-Wl,-rpath,$ORIGIN/" + rel, "-Wl,-rpath," + tlib]
     subprocess.check_call(cmd)
     os.replace(out + ".tmp", out)
+    return out
+
+
+def build_ext(force=False):
+    """_C (rasterizer + loss stage) and the top-level fused_ssim_cuda module (the reference's name)."""
+    hdrs = [os.path.join(ROOT, "include", "gsr.h"), os.path.join(ROOT, "include", "gsr_loss.h"), LIB]
+    main_src = os.path.join(CSRC, "torch_binding.cpp")
+    ssim_src = os.path.join(CSRC, "ssim_binding.cpp")
+    jobs = []
+    out = ext_path()
+    if force or not _newer(out, [main_src, ssim_src] + hdrs):
+        jobs.append(("_C", [main_src, ssim_src], out, ()))
+    out2 = ssim_ext_path()
+    if force or not _newer(out2, [ssim_src] + hdrs):
+        jobs.append(("fused_ssim_cuda", [ssim_src], out2, ("-DGSR_SSIM_STANDALONE",)))
+    with ThreadPoolExecutor(max_workers=2) as ex:
+        list(ex.map(lambda j: _compile_ext(*j), jobs))
     return out
 
 

@@ -34,6 +34,8 @@ static int fail(int code, const char* fmt, ...) {
 static inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 extern "C" const char* gsr_last_error(void) { return tl_error; }
+// error channel for the other translation units (ssim.cu, adam.cu): same thread-local message
+int gsr_set_error(int code, const char* msg) { return fail(code, "%s", msg); }
 extern "C" const char* gsr_version(void) { return "gsr_b200 0.1 (sm_100a)"; }
 extern "C" void gsr_set_profiling(int enabled) { tl_profiling = enabled; }
 extern "C" float gsr_last_stage_ms(int stage) { return (stage >= 0 && stage < 12) ? tl_stage_ms[stage] : -1.0f; }

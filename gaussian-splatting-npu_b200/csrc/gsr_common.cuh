@@ -202,6 +202,9 @@ struct BinningView {
     char* sort_temp;
 };
 
+// records `msg` as the calling thread's gsr_last_error() and returns `code` (defined in gsr_api.cu)
+int gsr_set_error(int code, const char* msg);
+
 // ---- kernel launchers (one per stage), all asynchronous on `stream` ----------------------------
 struct FwdParams {
     int P, D, M, W, H, gx, gy;

@@ -235,6 +235,8 @@ torch::Tensor markVisible(torch::Tensor& means3D, torch::Tensor& viewmatrix, tor
     return present;
 }
 
+void bind_ssim(pybind11::module_& m, bool rasterizer_module);   // ssim_binding.cpp
+
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.def("rasterize_gaussians", &RasterizeGaussiansCUDA);
     m.def("rasterize_gaussians_backward", &RasterizeGaussiansBackwardCUDA);
@@ -243,5 +245,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     // the fork's spellings (DGR/ext.cpp:16, rasterize_points.h:18,41)
     m.def("rasterize_gaussians_npu", &RasterizeGaussiansCUDA);
     m.def("rasterize_gaussians_backward_npu", &RasterizeGaussiansBackwardCUDA);
+    // loss stage (utils/loss_utils.py:16-19 imports fusedssim / fusedssim_backward from this module)
+    bind_ssim(m, true);
     m.attr("backend") = "gsr_b200 sm_100a";
 }

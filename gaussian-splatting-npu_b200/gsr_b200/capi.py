@@ -63,7 +63,10 @@ EXPORTS = ["gsr_forward", "gsr_backward", "gsr_mark_visible", "gsr_geometry_byte
            "gsr_binning_bytes", "gsr_sort_temp_bytes", "gsr_sort_pairs", "gsr_get_geometry_layout",
            "gsr_get_binning_layout", "gsr_get_image_layout", "gsr_materialize_keys", "gsr_set_profiling",
            "gsr_last_stage_ms",
-           "gsr_last_error", "gsr_version"]
+           "gsr_last_error", "gsr_version",
+           # include/gsr_loss.h
+           "gsr_ssim_forward", "gsr_ssim_backward", "gsr_l1_ssim_partials_bytes", "gsr_l1_ssim_loss_forward",
+           "gsr_l1_ssim_loss_backward"]
 
 _lib = None
 
@@ -103,6 +106,17 @@ def lib():
         L.gsr_last_stage_ms.argtypes = [c_int]
         L.gsr_last_error.restype = c_char_p
         L.gsr_version.restype = c_char_p
+        # loss stage (include/gsr_loss.h)
+        L.gsr_ssim_forward.restype = c_int
+        L.gsr_ssim_forward.argtypes = [c_int, c_int, c_int, c_float, c_float] + [c_void_p] * 7
+        L.gsr_ssim_backward.restype = c_int
+        L.gsr_ssim_backward.argtypes = [c_int, c_int, c_int] + [c_void_p] * 8
+        L.gsr_l1_ssim_partials_bytes.restype = c_size_t
+        L.gsr_l1_ssim_partials_bytes.argtypes = [c_int, c_int, c_int]
+        L.gsr_l1_ssim_loss_forward.restype = c_int
+        L.gsr_l1_ssim_loss_forward.argtypes = [c_int, c_int, c_int, c_float, c_float, c_float] + [c_void_p] * 8
+        L.gsr_l1_ssim_loss_backward.restype = c_int
+        L.gsr_l1_ssim_loss_backward.argtypes = [c_int, c_int, c_int, c_float] + [c_void_p] * 8
         _lib = L
     return _lib
 
@@ -276,3 +290,60 @@ def sort_pairs(keys, values, end_bit):
     _check(L.gsr_sort_pairs(_ptr(keys) if n else None, _ptr(values) if n else None, c_void_p(ko.data_ptr()) if n else None,
                             c_void_p(vo.data_ptr()) if n else None, n, end_bit, c_void_p(temp.data_ptr()), _stream()))
     return ko, vo
+
+
+# ---- loss stage (include/gsr_loss.h) ------------------------------------------------------------------
+SSIM_C1 = 0.01 ** 2
+SSIM_C2 = 0.03 ** 2
+
+
+def _planes(img):
+    H, W = img.shape[-2:]
+    return (img.numel() // (H * W) if H * W else 0), H, W
+
+
+def ssim_forward(img1, img2, train=True, C1=SSIM_C1, C2=SSIM_C2):
+    """gsr_ssim_forward: (ssim_map, dm_dmu1, dm_dsigma1_sq, dm_dsigma12); the last three are None if not train."""
+    planes, H, W = _planes(img1)
+    m = torch.empty_like(img1)
+    d = [torch.empty_like(img1) for _ in range(3)] if train else [None] * 3
+    _check(lib().gsr_ssim_forward(planes, H, W, C1, C2, _ptr(img1), _ptr(img2), _ptr(m), *[_ptr(x) for x in d], _stream()))
+    return m, d[0], d[1], d[2]
+
+
+def ssim_backward(img1, img2, dL_dmap, dm_dmu1, dm_dsigma1_sq, dm_dsigma12):
+    planes, H, W = _planes(img1)
+    g = torch.empty_like(img1)
+    _check(lib().gsr_ssim_backward(planes, H, W, _ptr(img1), _ptr(img2), _ptr(dL_dmap), _ptr(dm_dmu1), _ptr(dm_dsigma1_sq),
+                                   _ptr(dm_dsigma12), _ptr(g), _stream()))
+    return g
+
+
+class LossScratch:
+    """Preallocated buffers of the fused L1 + D-SSIM loss for one image shape (no allocation per step)."""
+
+    def __init__(self, shape, device):
+        e = lambda: torch.empty(shape, dtype=torch.float32, device=device)
+        self.dm = [e(), e(), e()]
+        self.dL_dimage = e()
+        self.loss = torch.empty(3, dtype=torch.float32, device=device)
+        H, W = shape[-2:]
+        planes = int(torch.Size(shape).numel() // (H * W))
+        self.partials = torch.empty(int(lib().gsr_l1_ssim_partials_bytes(planes, H, W)) // 8, dtype=torch.float64, device=device)
+
+
+def l1_ssim_loss_forward(image, gt, lambda_dssim, scratch, train=True, C1=SSIM_C1, C2=SSIM_C2):
+    """gsr_l1_ssim_loss_forward: fills scratch.loss = (loss, mean L1, mean ssim) and the derivative maps."""
+    planes, H, W = _planes(image)
+    d = scratch.dm if train else [None] * 3
+    _check(lib().gsr_l1_ssim_loss_forward(planes, H, W, C1, C2, lambda_dssim, _ptr(image), _ptr(gt), _ptr(scratch.loss),
+                                          *[_ptr(x) for x in d], _ptr(scratch.partials), _stream()))
+    return scratch.loss
+
+
+def l1_ssim_loss_backward(image, gt, lambda_dssim, scratch, upstream=None):
+    """gsr_l1_ssim_loss_backward into scratch.dL_dimage (upstream: device scalar tensor or None = 1)."""
+    planes, H, W = _planes(image)
+    _check(lib().gsr_l1_ssim_loss_backward(planes, H, W, lambda_dssim, _ptr(image), _ptr(gt), *[_ptr(x) for x in scratch.dm],
+                                           _ptr(upstream), _ptr(scratch.dL_dimage), _stream()))
+    return scratch.dL_dimage

@@ -42,5 +42,57 @@ def build(force=False):
     return OUT
 
 
+# ---- the reference's fused-ssim extension (loss stage) --------------------------
+FS = "/root/reference/submodules/fused-ssim"
+FS_OUT = os.path.join(OUT_DIR, "fused_ssim_cuda_ref.so")
+
+
+def fused_ssim_available():
+    return os.path.exists(os.path.join(FS, "ssim.cu"))
+
+
+def build_fused_ssim(force=False):
+    """UNMODIFIED FS/ssim.cu + FS/ext.cpp compiled for sm_100a as the torch extension module
+    `fused_ssim_cuda_ref` (the module name is the only change: -DTORCH_EXTENSION_NAME, so that it can be
+    imported next to the product's fused_ssim_cuda).  FS/setup.py is not run.  nvcc needs ~6 minutes
+    for the torch headers."""
+    if not fused_ssim_available():
+        return FS_OUT if os.path.exists(FS_OUT) else None
+    srcs = [os.path.join(FS, "ssim.cu"), os.path.join(FS, "ext.cpp")]
+    if not force and os.path.exists(FS_OUT) and all(os.path.getmtime(s) <= os.path.getmtime(FS_OUT) for s in srcs):
+        return FS_OUT
+    import sysconfig
+    import torch
+    from torch.utils import cpp_extension as ce
+    os.makedirs(OUT_DIR, exist_ok=True)
+    inc = []
+    for p in ce.include_paths("cuda"):
+        inc += ["-I", p]
+    inc += ["-I", sysconfig.get_paths()["include"]]
+    tlib = os.path.join(os.path.dirname(torch.__file__), "lib")
+    abi = int(torch._C._GLIBCXX_USE_CXX11_ABI)
+    cmd = ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-shared", "-Xcompiler", "-fPIC",
+           "-std=c++17", "-DTORCH_EXTENSION_NAME=fused_ssim_cuda_ref", "-DTORCH_API_INCLUDE_EXTENSION_H",
+           "-D_GLIBCXX_USE_CXX11_ABI=%d" % abi, "-w", *inc, *srcs, "-o", FS_OUT + ".tmp",
+           "-L", tlib, "-lc10", "-lc10_cuda", "-ltorch_cpu", "-ltorch_cuda", "-ltorch", "-ltorch_python",
+           "-Xlinker", "-rpath," + tlib]
+    subprocess.check_call(cmd)
+    os.replace(FS_OUT + ".tmp", FS_OUT)
+    return FS_OUT
+
+
+def load_fused_ssim():
+    """Imports oracle/_ref/fused_ssim_cuda_ref.so (GPU box: the prebuilt file).  None if it does not exist."""
+    if not os.path.exists(FS_OUT):
+        return None
+    import importlib.util
+    import torch  # noqa: F401  (libtorch must be loaded first)
+    spec = importlib.util.spec_from_file_location("fused_ssim_cuda_ref", FS_OUT)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv))
+    print(build_fused_ssim(force="--force" in sys.argv))

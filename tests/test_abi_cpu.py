@@ -1,4 +1,4 @@
-"""The C-ABI library loads without a GPU, exports every symbol include/gsr.h declares, and its
+"""The C-ABI library loads without a GPU, exports every symbol include/*.h declares, and its
 argument validation / layout functions work (no compute calls)."""
 import ctypes
 import os
@@ -13,7 +13,10 @@ ROOT = cases.ROOT
 
 
 def _declared_functions():
-    src = open(os.path.join(ROOT, "include", "gsr.h")).read()
+    src = ""
+    for h in sorted(os.listdir(os.path.join(ROOT, "include"))):
+        if h.endswith(".h"):
+            src += open(os.path.join(ROOT, "include", h)).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     return sorted(set(re.findall(r"\b(gsr_[a-z_0-9]+)\s*\(", src)) - {"gsr_alloc_fn"})
 
@@ -86,3 +89,28 @@ def test_python_api_has_no_cpu_fallback():
     assert list(GaussianRasterizationSettings._fields) == [
         "image_height", "image_width", "tanfovx", "tanfovy", "bg", "scale_modifier", "viewmatrix", "projmatrix",
         "sh_degree", "campos", "prefiltered", "debug", "antialiasing"]
+
+
+def test_loss_stage_argument_validation_without_gpu():
+    L = capi.lib()
+    assert L.gsr_l1_ssim_partials_bytes(3, 1080, 1920) == 60 * 34 * 3 * 16 + 256
+    # empty problems are no-ops, NULL images are rejected before any launch
+    assert L.gsr_ssim_forward(0, 16, 16, 1e-4, 9e-4, None, None, None, None, None, None, None) == 0
+    assert L.gsr_ssim_forward(1, 16, 16, 1e-4, 9e-4, None, None, None, None, None, None, None) == -1
+    assert "NULL" in capi.last_error()
+    assert L.gsr_ssim_backward(1, 16, 16, None, None, None, None, None, None, None, None) == -1
+    assert L.gsr_ssim_forward(70000, 16, 16, 1e-4, 9e-4, None, None, None, None, None, None, None) == -1
+    assert "65535" in capi.last_error()
+
+
+def test_fused_ssim_package_has_no_cpu_fallback():
+    import torch
+    from fused_ssim import fused_ssim, l1_ssim_loss, allowed_padding
+    assert allowed_padding == ["same", "valid"]
+    a = torch.rand(1, 3, 16, 16)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        fused_ssim(a, a)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        l1_ssim_loss(a[0], a[0])
+    with pytest.raises(AssertionError):
+        fused_ssim(a, a, padding="reflect")

@@ -1,0 +1,177 @@
+"""GPU parity of the loss stage (csrc/ssim.cu) through the C ABI (gsr_b200.capi -> libgsr_b200.so) and the
+reference-facing Python packages (fused_ssim, diff_gaussian_rasterization._C), against
+  (i) the CPU oracle (oracle/ssim_oracle.c), (ii) the golden vectors of the reference CUDA kernel,
+  (iii) the live reference CUDA build (oracle/_ref/fused_ssim_cuda_ref.so) on the same inputs.
+Tolerances (fp32): ssim_map max-abs <= 2e-5; derivative maps and gradients <= 2e-4 of the array's largest
+magnitude (the kernels use one reciprocal where the reference divides seven times)."""
+import os
+
+import numpy as np
+import pytest
+
+import ssim_cases
+from oracle import ssim_oracle as so
+from test_ssim_golden import DERIV_RTOL, GOLD, MAP_ATOL
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(got, want):
+    return np.abs(got - want).max() / (np.abs(want).max() + 1e-30)
+
+
+def _t(cuda, *arrs):
+    import torch
+    return [torch.from_numpy(np.ascontiguousarray(a)).to(cuda) for a in arrs]
+
+
+@pytest.mark.parametrize("name", list(ssim_cases.CASES))
+def test_c_abi_vs_oracle(cuda, name):
+    from gsr_b200 import capi
+    a, b, dl = ssim_cases.make(name)
+    ta, tb, tdl = _t(cuda, a, b, dl)
+    m, d0, d1, d2 = capi.ssim_forward(ta, tb, True)
+    om, od0, od1, od2 = so.fusedssim(so.C1, so.C2, a, b, True)
+    assert np.abs(m.cpu().numpy() - om).max() <= MAP_ATOL
+    for got, want in ((d0, od0), (d1, od1), (d2, od2)):
+        assert _rel(got.cpu().numpy(), want) <= DERIV_RTOL
+    g = capi.ssim_backward(ta, tb, tdl, d0, d1, d2)
+    og = so.fusedssim_backward(so.C1, so.C2, a, b, dl, od0, od1, od2)
+    assert _rel(g.cpu().numpy(), og) <= DERIV_RTOL
+    # inference form: map only, same values
+    m2, *_ = capi.ssim_forward(ta, tb, False)
+    assert np.array_equal(m2.cpu().numpy(), m.cpu().numpy())
+
+
+@pytest.mark.parametrize("name", ssim_cases.GOLDEN)
+def test_c_abi_vs_golden(cuda, name):
+    from gsr_b200 import capi
+    path = os.path.join(GOLD, "ssim_" + name + ".npz")
+    if not os.path.exists(path):
+        pytest.skip("golden vector not generated yet")
+    gold = np.load(path)
+    a, b, dl = ssim_cases.make(name)
+    ta, tb, tdl = _t(cuda, a, b, dl)
+    m, d0, d1, d2 = capi.ssim_forward(ta, tb, True)
+    assert np.abs(m.cpu().numpy() - gold["ssim_map"]).max() <= MAP_ATOL
+    assert _rel(d0.cpu().numpy(), gold["dm_dmu1"]) <= DERIV_RTOL
+    assert _rel(d1.cpu().numpy(), gold["dm_dsigma1_sq"]) <= DERIV_RTOL
+    assert _rel(d2.cpu().numpy(), gold["dm_dsigma12"]) <= DERIV_RTOL
+    g = capi.ssim_backward(ta, tb, tdl, d0, d1, d2)
+    assert _rel(g.cpu().numpy(), gold["dL_dimg1"]) <= DERIV_RTOL
+
+
+@pytest.mark.parametrize("shape", [(1, 3, 64, 64), (1, 3, 545, 980), (2, 3, 1080, 1920)])
+def test_vs_live_reference_cuda(cuda, shape):
+    """Same inputs through the unmodified reference kernels and ours, on this GPU (full 1080p included)."""
+    import torch
+    from oracle import build_ref
+    ref = build_ref.load_fused_ssim()
+    if ref is None:
+        pytest.skip("oracle/_ref/fused_ssim_cuda_ref.so not built")
+    import fused_ssim_cuda as ours
+    torch.manual_seed(shape[-1])
+    a = torch.rand(shape, device=cuda)
+    b = (a + 0.1 * torch.randn(shape, device=cuda)).clamp(0, 1)
+    dl = torch.randn(shape, device=cuda)
+    rm, r0, r1, r2 = ref.fusedssim(so.C1, so.C2, a, b, True)
+    m, d0, d1, d2 = ours.fusedssim(so.C1, so.C2, a, b, True)
+    assert (m - rm).abs().max().item() <= MAP_ATOL
+    for got, want in ((d0, r0), (d1, r1), (d2, r2)):
+        assert ((got - want).abs().max() / want.abs().max()).item() <= DERIV_RTOL
+    rg = ref.fusedssim_backward(so.C1, so.C2, a, b, dl, r0, r1, r2)
+    g = ours.fusedssim_backward(so.C1, so.C2, a, b, dl, r0, r1, r2)      # same derivative maps: isolates the backward
+    assert ((g - rg).abs().max() / rg.abs().max()).item() <= 1e-5
+    g2 = ours.fusedssim_backward(so.C1, so.C2, a, b, dl, d0, d1, d2)
+    assert ((g2 - rg).abs().max() / rg.abs().max()).item() <= DERIV_RTOL
+
+
+@pytest.mark.parametrize("padding", ["same", "valid"])
+def test_fused_ssim_package_matches_reference_test_recipe(cuda, padding):
+    """FS/tests/test.py:66-91: value and gradient against the torch conv2d SSIM, torch.isclose."""
+    import torch
+    from fused_ssim import fused_ssim
+    from test_ssim_oracle_cpu import torch_ssim_map
+    torch.manual_seed(0)
+    img1 = torch.nn.Parameter(torch.rand([2, 3, 270, 480], device=cuda))
+    img2 = torch.rand([2, 3, 270, 480], device=cuda)
+    img1_og = torch.nn.Parameter(img1.detach().clone().double())
+    ref_map = torch_ssim_map(img1_og, img2.double())
+    ref_val = (ref_map[:, :, 5:-5, 5:-5] if padding == "valid" else ref_map).mean()
+    val = fused_ssim(img1, img2, padding)
+    assert torch.isclose(ref_val.float(), val)
+    ref_val.backward()
+    val.backward()
+    gr = img1_og.grad.float()
+    assert ((img1.grad - gr).abs().max() / gr.abs().max()).item() <= DERIV_RTOL
+    # inference path (train=False) returns the same value and keeps no derivative maps
+    with torch.no_grad():
+        assert torch.equal(fused_ssim(img1, img2, padding, train=False), val.detach())
+
+
+def test_loss_utils_entry_points(cuda):
+    """utils/loss_utils.py:16-37 imports fusedssim / fusedssim_backward from diff_gaussian_rasterization._C."""
+    import torch
+    from diff_gaussian_rasterization._C import fusedssim, fusedssim_backward
+    a, b, dl = ssim_cases.make("rand_1x3x64x64")
+    ta, tb, tdl = _t(cuda, a, b, dl)
+    m = fusedssim(so.C1, so.C2, ta, tb)
+    om, od0, od1, od2 = so.fusedssim(so.C1, so.C2, a, b, True)
+    assert np.abs(m.cpu().numpy() - om).max() <= MAP_ATOL
+    g = fusedssim_backward(so.C1, so.C2, ta, tb, tdl)
+    og = so.fusedssim_backward(so.C1, so.C2, a, b, dl, od0, od1, od2)
+    assert _rel(g.cpu().numpy(), og) <= DERIV_RTOL
+
+
+@pytest.mark.parametrize("shape,lam", [((3, 64, 64), 0.2), ((3, 101, 167), 0.2), ((1, 3, 40, 56), 0.5), ((3, 546, 979), 0.2)])
+def test_l1_ssim_loss_vs_oracle(cuda, shape, lam):
+    """The fused training loss (train.py:118-126) through the autograd entry, upstream gradient 3.0."""
+    import torch
+    from fused_ssim import l1_ssim_loss
+    rng = np.random.default_rng(shape[-1])
+    img = rng.random(shape, dtype=np.float32)
+    gt = np.clip(img + 0.1 * rng.standard_normal(shape).astype(np.float32), 0, 1).astype(np.float32)
+    gt.reshape(-1)[::97] = img.reshape(-1)[::97]          # exact ties: sign(0) = 0 in the L1 term
+    o = so.l1_ssim_loss(img, gt, lam, upstream=3.0)
+    ti = torch.from_numpy(img).to(cuda).requires_grad_(True)
+    tg = torch.from_numpy(gt).to(cuda)
+    loss = l1_ssim_loss(ti, tg, lam)
+    (loss * 3.0).backward()
+    assert abs(loss.item() - o["loss"]) <= 2e-6
+    assert _rel(ti.grad.cpu().numpy(), o["dL_dimg"]) <= DERIV_RTOL
+    # deterministic: a second evaluation gives the same bits
+    ti2 = torch.from_numpy(img).to(cuda).requires_grad_(True)
+    loss2 = l1_ssim_loss(ti2, tg, lam)
+    loss2.backward(torch.tensor(3.0, device=cuda))
+    assert loss2.item() == loss.item() and torch.equal(ti2.grad, ti.grad)
+
+
+def test_l1_ssim_loss_matches_torch_composition_1080p(cuda):
+    """Full-size property check: fused loss == (1-l)*l1_loss + l*(1-fused_ssim) built from torch ops + our SSIM."""
+    import torch
+    from fused_ssim import fused_ssim, l1_ssim_loss
+    torch.manual_seed(5)
+    img = torch.rand(3, 1080, 1920, device=cuda)
+    gt = (img + 0.05 * torch.randn_like(img)).clamp(0, 1)
+    a = img.clone().requires_grad_(True)
+    b = img.clone().requires_grad_(True)
+    l_ref = 0.8 * torch.abs(a - gt).mean() + 0.2 * (1.0 - fused_ssim(a.unsqueeze(0), gt.unsqueeze(0)))
+    l_ref.backward()
+    l_fused = l1_ssim_loss(b, gt, 0.2)
+    l_fused.backward()
+    assert abs(l_ref.item() - l_fused.item()) <= 2e-6
+    assert ((a.grad - b.grad).abs().max() / a.grad.abs().max()).item() <= 1e-4
+
+
+def test_error_paths(cuda):
+    import torch
+    import fused_ssim_cuda as ours
+    a = torch.rand(1, 3, 16, 16)
+    with pytest.raises(RuntimeError, match="CUDA tensor"):
+        ours.fusedssim(so.C1, so.C2, a, a, True)
+    with pytest.raises(RuntimeError, match="same shape"):
+        ours.fusedssim(so.C1, so.C2, a.to(cuda), torch.rand(1, 3, 16, 17, device=cuda), True)
+    # empty batch: no launch, empty outputs
+    e = torch.empty(0, 3, 16, 16, device=cuda)
+    m, *_ = ours.fusedssim(so.C1, so.C2, e, e, True)
+    assert m.numel() == 0
