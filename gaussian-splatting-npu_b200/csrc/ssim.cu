@@ -16,22 +16,58 @@
 //           of the pass-1 result (conflict-free LDS, consecutive lanes = consecutive x) and finishes
 //           the SSIM algebra in registers; stores are 128-byte coalesced rows.
 // Three CTA barriers in total.  Tap order is the reference's (k = 0..10, one FFMA per tap) in both
-// passes, so the five window values are bit-identical to the reference's; the closing rational
-// expressions use ONE reciprocal of A*B instead of the reference's seven IEEE divisions (tolerance in
-// tests/test_gpu_ssim.py).
+// passes, so the five window values are bit-identical to the reference's; the API kernels (gsr_ssim_forward /
+// gsr_ssim_backward) close with the reference's own FFMA placement and IEEE divisions, which makes all their
+// outputs BIT-IDENTICAL to the reference CUDA kernel's; the fused-loss variant uses ONE reciprocal of A*B instead
+// of seven divisions (tolerance in tests/test_gpu_ssim.py).
 // Bound: HBM for the API kernels (fwd 8 B in + 16 B out, bwd 24 B in + 4 B out per pixel-channel),
 // FP32 issue for the arithmetic (~290 FFMA per pixel-channel forward).
 #include "../../include/gsr.h"
 #include "../../include/gsr_loss.h"
 #include "gsr_common.cuh"
+#include <cuda.h>                 // CUtensorMap (types only: the encoder is fetched through cudaGetDriverEntryPoint)
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <initializer_list>
 
 namespace {
 
 constexpr int TS = 32;            // tile side (pixels)
 constexpr int HS = TS + 10;       // staged side incl. the 5-pixel halo
-constexpr int PITCH = 44;         // staged row pitch in floats (16-byte multiple for LDS.128)
+constexpr int PITCH = 44;         // staged row pitch in floats (16-byte multiple: LDS.128, and the TMA box row = 176 B)
+constexpr int PLANE_FLOATS = 1856; // one staged plane: HS*PITCH = 1848 floats, padded so that every plane starts 128-byte aligned (TMA)
 constexpr int NTHREADS = 256;
+
+// ---- TMA staging ---------------------------------------------------------------------------------------
+// One elected thread issues one cp.async.bulk.tensor per input plane: a 44 x 42 x 1 box of the [planes,H,W] tensor at
+// (x0-5, y0-5, plane).  The TMA unit zero-fills everything outside the image (negative coordinates included), which is
+// exactly the reference's zero padding (ssim.cu:38-44), and lands the rows at the 176-byte pitch pass 1 reads --
+// no per-thread index arithmetic, bounds checks, LDG or STS.  Needs W % 4 == 0 and a 16-byte aligned base (row pitch
+// and base address of a tensor map are 16-byte quantities); other shapes take the manual staging path below.
+struct TmaMaps { CUtensorMap m[4]; };
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t phase) {
+    uint32_t ok;
+    do {
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(phase) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void tma_load_3d(float* dst, const CUtensorMap* map, int x, int y, int z, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 :: "r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar))
+                 : "memory");
+}
 
 // window weights as immediates (the loops below are fully unrolled, so G(k) folds into the FFMA)
 __device__ __forceinline__ constexpr float G(int k) {
@@ -54,44 +90,54 @@ __device__ __forceinline__ void stage_plane(float* s, const float* __restrict__ 
     }
 }
 
-// Same for the product of two planes (backward: dL_dmap * dm_*; reference multiply_shared_mem, ssim.cu:66-80).
-// `scalar` != nullptr replaces plane b by a constant (the fused loss: dL_dmap is uniform).
-__device__ __forceinline__ void stage_product(float* s, const float* __restrict__ a, const float* __restrict__ b,
-                                              float bconst, int H, int W, int x0, int y0) {
-    for (int i = threadIdx.x; i < HS * PITCH; i += NTHREADS) {
-        const int ly = i / PITCH, lx = i - ly * PITCH;
-        const int y = y0 + ly - 5, x = x0 + lx - 5;
-        float v = 0.0f;
-        if (lx < HS && x >= 0 && x < W && y >= 0 && y < H) {
-            const size_t o = (size_t)y * W + x;
-            v = __fmul_rn(__ldg(a + o), b ? __ldg(b + o) : bconst);
+// Stage NP planes (s + p*PLANE_FLOATS) and make them visible to the CTA.
+template <int NP, bool TMA>
+__device__ __forceinline__ void stage_all(float* s, const float* const (&planes)[NP], const TmaMaps& maps,
+                                          unsigned long long* bar, int H, int W, int x0, int y0) {
+    if (TMA) {
+        if (threadIdx.x == 0) mbar_init(bar, 1);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            mbar_expect_tx(bar, NP * HS * PITCH * 4);
+#pragma unroll
+            for (int p = 0; p < NP; ++p) tma_load_3d(s + p * PLANE_FLOATS, &maps.m[p], x0 - 5, y0 - 5, (int)blockIdx.z, bar);
         }
-        s[i] = v;
+        mbar_wait(bar, 0);
+    } else {
+        const size_t plane_off = (size_t)blockIdx.z * H * W;
+#pragma unroll
+        for (int p = 0; p < NP; ++p) stage_plane(s + p * PLANE_FLOATS, planes[p] + plane_off, H, W, x0, y0);
+        __syncthreads();
     }
 }
 
 // ---- pass 1: horizontal window, NQ quantities, 4 outputs per item ---------------------------------
 // FWD (NQ = 5): quantities a, a*a, b, b*b, a*b from the two staged images.
 // BWD (NQ = 3): the three staged product planes.
-template <bool FWD>
-__device__ __forceinline__ void pass1(const float* __restrict__ s0, const float* __restrict__ s1,
-                                      const float* __restrict__ s2, float* __restrict__ hz) {
+// DLP: the backward's dL_dmap is a staged plane (API) / a constant (fused loss: dL_dmap is uniform).
+template <bool FWD, bool DLP>
+__device__ __forceinline__ void pass1(const float* __restrict__ s, float dl_const, float* __restrict__ hz) {
     constexpr int NQ = FWD ? 5 : 3;
     for (int item = threadIdx.x; item < HS * 8; item += NTHREADS) {
         const int row = item >> 3, g = item & 7;
-        float va[16], vb[16], vc[16];
-        const float4* pa = reinterpret_cast<const float4*>(s0 + row * PITCH + 4 * g);
-        const float4* pb = reinterpret_cast<const float4*>(s1 + row * PITCH + 4 * g);
+        const int off = row * PITCH + 4 * g;
+        float va[16], vb[16], vc[16], vd[16];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            const float4 t = pa[q]; va[4 * q] = t.x; va[4 * q + 1] = t.y; va[4 * q + 2] = t.z; va[4 * q + 3] = t.w;
-            const float4 u = pb[q]; vb[4 * q] = u.x; vb[4 * q + 1] = u.y; vb[4 * q + 2] = u.z; vb[4 * q + 3] = u.w;
+            const float4 t = reinterpret_cast<const float4*>(s + off)[q];
+            va[4 * q] = t.x; va[4 * q + 1] = t.y; va[4 * q + 2] = t.z; va[4 * q + 3] = t.w;
+            const float4 u = reinterpret_cast<const float4*>(s + PLANE_FLOATS + off)[q];
+            vb[4 * q] = u.x; vb[4 * q + 1] = u.y; vb[4 * q + 2] = u.z; vb[4 * q + 3] = u.w;
         }
         if (!FWD) {
-            const float4* pc = reinterpret_cast<const float4*>(s2 + row * PITCH + 4 * g);
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                const float4 t = pc[q]; vc[4 * q] = t.x; vc[4 * q + 1] = t.y; vc[4 * q + 2] = t.z; vc[4 * q + 3] = t.w;
+                const float4 t = reinterpret_cast<const float4*>(s + 2 * PLANE_FLOATS + off)[q];
+                vc[4 * q] = t.x; vc[4 * q + 1] = t.y; vc[4 * q + 2] = t.z; vc[4 * q + 3] = t.w;
+                if (DLP) {
+                    const float4 u = reinterpret_cast<const float4*>(s + 3 * PLANE_FLOATS + off)[q];
+                    vd[4 * q] = u.x; vd[4 * q + 1] = u.y; vd[4 * q + 2] = u.z; vd[4 * q + 3] = u.w;
+                }
             }
         }
         float acc[NQ][4];
@@ -106,7 +152,9 @@ __device__ __forceinline__ void pass1(const float* __restrict__ s0, const float*
                 v[0] = va[j]; v[1] = __fmul_rn(va[j], va[j]); v[2] = vb[j]; v[3] = __fmul_rn(vb[j], vb[j]);
                 v[4] = __fmul_rn(va[j], vb[j]);
             } else {
-                v[0] = va[j]; v[1] = vb[j]; v[2] = vc[j];
+                // reference multiply_shared_mem (ssim.cu:66-80): the product is rounded before the window
+                const float d = DLP ? vd[j] : dl_const;
+                v[0] = __fmul_rn(va[j], d); v[1] = __fmul_rn(vb[j], d); v[2] = __fmul_rn(vc[j], d);
             }
 #pragma unroll
             for (int o = 0; o < 4; ++o) {
@@ -148,20 +196,21 @@ __device__ __forceinline__ void pass2(const float* __restrict__ hz, int x, int y
 
 // MODE 0: API forward (map and/or derivatives, whichever pointers are non-NULL)
 // MODE 1: fused loss forward: derivatives (if non-NULL) + per-CTA partial sums of |a-b| and of the map
-template <int MODE>
+template <int MODE, bool TMA>
 __global__ void __launch_bounds__(NTHREADS)
-ssim_fwd_kernel(int H, int W, float C1, float C2, const float* __restrict__ img1, const float* __restrict__ img2,
-                float* __restrict__ ssim_map, float* __restrict__ dm_dmu1, float* __restrict__ dm_dsigma1_sq,
-                float* __restrict__ dm_dsigma12, double* __restrict__ partials) {
-    __shared__ __align__(16) float sa[HS * PITCH];
-    __shared__ __align__(16) float sb[HS * PITCH];
+ssim_fwd_kernel(const __grid_constant__ TmaMaps maps, int H, int W, float C1, float C2, const float* __restrict__ img1,
+                const float* __restrict__ img2, float* __restrict__ ssim_map, float* __restrict__ dm_dmu1,
+                float* __restrict__ dm_dsigma1_sq, float* __restrict__ dm_dsigma12, double* __restrict__ partials) {
+    __shared__ __align__(128) float sin_[2 * PLANE_FLOATS];
     __shared__ __align__(16) float hz[5 * HS * TS];
+    __shared__ __align__(8) unsigned long long bar;
+    const float* sa = sin_;
+    const float* sb = sin_ + PLANE_FLOATS;
     const int x0 = blockIdx.x * TS, y0 = blockIdx.y * TS;
     const size_t plane_off = (size_t)blockIdx.z * H * W;
-    stage_plane(sa, img1 + plane_off, H, W, x0, y0);
-    stage_plane(sb, img2 + plane_off, H, W, x0, y0);
-    __syncthreads();
-    pass1<true>(sa, sb, nullptr, hz);
+    const float* const planes[2] = {img1, img2};
+    stage_all<2, TMA>(sin_, planes, maps, &bar, H, W, x0, y0);
+    pass1<true, false>(sin_, 0.0f, hz);
     __syncthreads();
     const int x = threadIdx.x & 31, yg = threadIdx.x >> 5;
     float w[5][4];
@@ -172,27 +221,51 @@ ssim_fwd_kernel(int H, int W, float C1, float C2, const float* __restrict__ img1
 #pragma unroll
     for (int o = 0; o < 4; ++o) {
         const int py = y0 + 4 * yg + o;
+        // FFMA placement of the reference's own sm_100a SASS (cuobjdump of the unmodified FS/ssim.cu build):
+        // mu1*mu2 and mu2*mu2 are rounded products that get reused, so sigma12 and sigma2_sq are FMUL + FADD;
+        // sigma1_sq and mu1^2 + mu2^2 are fused.  With the IEEE divisions of MODE 0 all four maps are
+        // bit-identical to the reference kernel's (tests/test_gpu_ssim.py asserts equality).
         const float mu1 = w[0][o], mu2 = w[2][o];
-        const float sigma1_sq = __fmaf_rn(-mu1, mu1, w[1][o]);   // ssim.cu:234
-        const float sigma2_sq = __fmaf_rn(-mu2, mu2, w[3][o]);   // ssim.cu:252
-        const float sigma12 = __fmaf_rn(-mu1, mu2, w[4][o]);     // ssim.cu:262
-        const float mu1_mu2 = mu1 * mu2;
-        const float C = 2.0f * mu1_mu2 + C1;
-        const float D = 2.0f * sigma12 + C2;
-        const float A = mu1 * mu1 + mu2 * mu2 + C1;
-        const float B = sigma1_sq + sigma2_sq + C2;
-        const float inv = __frcp_rn(A * B);
-        const float CDi = C * D * inv;                            // the map value, ssim.cu:273
-        if (px < W && py < H) {
-            const size_t idx = plane_off + (size_t)py * W + px;
-            if (MODE == 0 && ssim_map) ssim_map[idx] = CDi;
-            if (dm_dmu1) {
-                // ssim.cu:279-286 with 1/(A*A*B) = inv/A and 1/(A*B*B) = inv/B, 1/B - 1/A = (A-B)*inv
-                dm_dmu1[idx] = 2.0f * (mu2 * (D - C) * inv + mu1 * CDi * (A - B) * inv);
-                dm_dsigma1_sq[idx] = -CDi * (A * inv);
-                dm_dsigma12[idx] = 2.0f * C * inv;
+        const float mu1_mu2 = __fmul_rn(mu1, mu2);
+        const float mu2_sq = __fmul_rn(mu2, mu2);
+        const float sigma12 = __fsub_rn(w[4][o], mu1_mu2);        // ssim.cu:262
+        const float sigma1_sq = __fmaf_rn(-mu1, mu1, w[1][o]);    // ssim.cu:234
+        const float sigma2_sq = __fsub_rn(w[3][o], mu2_sq);       // ssim.cu:252
+        const float C = __fmaf_rn(mu1_mu2, 2.0f, C1);
+        const float D = __fmaf_rn(sigma12, 2.0f, C2);
+        const float A = __fadd_rn(__fmaf_rn(mu1, mu1, mu2_sq), C1);
+        const float B = __fadd_rn(__fadd_rn(sigma1_sq, sigma2_sq), C2);
+        const float AB = __fmul_rn(A, B);
+        const float CD = __fmul_rn(C, D);
+        const bool inside = px < W && py < H;
+        const size_t idx = plane_off + (size_t)py * W + px;
+        if (MODE == 0) {
+            if (ssim_map && inside) ssim_map[idx] = __fdiv_rn(CD, AB);                      // ssim.cu:273
+            if (dm_dmu1) {                                                                    // ssim.cu:279-288
+                const float two_mu2 = __fadd_rn(mu2, mu2), two_mu1 = __fadd_rn(mu1, mu1);
+                const float t1 = __fdiv_rn(__fmul_rn(D, two_mu2), AB);
+                const float t2 = __fdiv_rn(__fmul_rn(C, two_mu2), AB);
+                const float num = __fmul_rn(D, __fmul_rn(C, two_mu1));
+                const float t3 = __fdiv_rn(num, __fmul_rn(B, __fmul_rn(A, A)));
+                const float ABB = __fmul_rn(B, AB);
+                const float t4 = __fdiv_rn(num, ABB);
+                if (inside) {
+                    dm_dmu1[idx] = __fadd_rn(__fsub_rn(__fsub_rn(t1, t2), t3), t4);
+                    dm_dsigma1_sq[idx] = __fdiv_rn(__fmul_rn(C, -D), ABB);
+                    dm_dsigma12[idx] = __fdiv_rn(__fadd_rn(C, C), AB);
+                }
             }
-            if (MODE == 1) {
+        } else {
+            // fused loss: one reciprocal instead of seven divisions (these maps only feed our own backward):
+            // 1/(A*A*B) = inv/A, 1/(A*B*B) = inv/B, 1/B - 1/A = (A-B)*inv
+            const float inv = __frcp_rn(AB);
+            const float CDi = CD * inv;
+            if (inside) {
+                if (dm_dmu1) {
+                    dm_dmu1[idx] = 2.0f * (mu2 * (D - C) * inv + mu1 * CDi * (A - B) * inv);
+                    dm_dsigma1_sq[idx] = -CDi * (A * inv);
+                    dm_dsigma12[idx] = 2.0f * C * inv;
+                }
                 s_map += CDi;
                 s_l1 += fabsf(sa[(4 * yg + o + 5) * PITCH + x + 5] - sb[(4 * yg + o + 5) * PITCH + x + 5]);
             }
@@ -240,27 +313,29 @@ loss_reduce_kernel(const double* __restrict__ partials, size_t n_cta, double inv
 
 // MODE 0: API backward (dL_dmap is a plane)
 // MODE 1: fused loss backward (dL_dmap uniform = -upstream*lambda/n, plus the L1 term)
-template <int MODE>
+template <int MODE, bool TMA>
 __global__ void __launch_bounds__(NTHREADS)
-ssim_bwd_kernel(int H, int W, const float* __restrict__ img1, const float* __restrict__ img2,
-                const float* __restrict__ dL_dmap, const float* __restrict__ dm_dmu1,
+ssim_bwd_kernel(const __grid_constant__ TmaMaps maps, int H, int W, const float* __restrict__ img1,
+                const float* __restrict__ img2, const float* __restrict__ dL_dmap, const float* __restrict__ dm_dmu1,
                 const float* __restrict__ dm_dsigma1_sq, const float* __restrict__ dm_dsigma12,
                 const float* __restrict__ upstream, float c_ssim, float c_l1, float* __restrict__ dL_dimg1) {
-    __shared__ __align__(16) float s0[HS * PITCH];
-    __shared__ __align__(16) float s1[HS * PITCH];
-    __shared__ __align__(16) float s2[HS * PITCH];
+    constexpr int NP = MODE == 0 ? 4 : 3;
+    __shared__ __align__(128) float sin_[NP * PLANE_FLOATS];
     __shared__ __align__(16) float hz[3 * HS * TS];
+    __shared__ __align__(8) unsigned long long bar;
     const int x0 = blockIdx.x * TS, y0 = blockIdx.y * TS;
     const size_t plane_off = (size_t)blockIdx.z * H * W;
     float up = 1.0f;
     if (MODE == 1 && upstream) up = __ldg(upstream);
     const float dl_const = up * c_ssim;
-    const float* dl = MODE == 0 ? dL_dmap + plane_off : nullptr;
-    stage_product(s0, dm_dmu1 + plane_off, dl, dl_const, H, W, x0, y0);
-    stage_product(s1, dm_dsigma1_sq + plane_off, dl, dl_const, H, W, x0, y0);
-    stage_product(s2, dm_dsigma12 + plane_off, dl, dl_const, H, W, x0, y0);
-    __syncthreads();
-    pass1<false>(s0, s1, s2, hz);
+    if (MODE == 0) {
+        const float* const planes[4] = {dm_dmu1, dm_dsigma1_sq, dm_dsigma12, dL_dmap};
+        stage_all<4, TMA>(sin_, planes, maps, &bar, H, W, x0, y0);
+    } else {
+        const float* const planes[3] = {dm_dmu1, dm_dsigma1_sq, dm_dsigma12};
+        stage_all<3, TMA>(sin_, planes, maps, &bar, H, W, x0, y0);
+    }
+    pass1<false, MODE == 0>(sin_, dl_const, hz);
     __syncthreads();
     const int x = threadIdx.x & 31, yg = threadIdx.x >> 5;
     float w[3][4];
@@ -273,9 +348,9 @@ ssim_bwd_kernel(int H, int W, const float* __restrict__ img1, const float* __res
             if (py < H) {
                 const size_t idx = plane_off + (size_t)py * W + px;
                 const float p1 = __ldg(img1 + idx), p2 = __ldg(img2 + idx);
-                float g = w[0][o];                       // ssim.cu:336
-                g += p1 * 2.0f * w[1][o];                // ssim.cu:348-350
-                g += p2 * w[2][o];                       // ssim.cu:362-364
+                // ssim.cu:336,348-350,362-364 as the reference's SASS has it: FADD(0,w0) ; FFMA(w1, p1+p1, .) ; FFMA(w2, p2, .)
+                float g = __fmaf_rn(w[1][o], __fadd_rn(p1, p1), __fadd_rn(0.0f, w[0][o]));
+                g = __fmaf_rn(w[2][o], p2, g);
                 if (MODE == 1) {
                     const float d = p1 - p2;             // torch abs backward: sign(0) = 0
                     const float sgn = d > 0.0f ? 1.0f : (d < 0.0f ? -1.0f : 0.0f);
@@ -306,6 +381,75 @@ int launch_status(const char* what) {
     return GSR_OK;
 }
 
+// ---- tensor maps ------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+    // libcuda is not linked: the encoder comes from the driver the runtime already loaded (thread-safe static init)
+    static EncodeTiledFn fn = []() -> EncodeTiledFn {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            return nullptr;
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+
+// TMA staging is possible when every plane row starts 16-byte aligned.  GSR_SSIM_NO_TMA=1 forces the manual path
+// (tests run both).
+bool tma_eligible(int H, int W, std::initializer_list<const void*> ptrs) {
+    if (W % 4 != 0 || W < 64 || H < 64) return false;
+    for (const void* p : ptrs)
+        if (reinterpret_cast<uintptr_t>(p) & 15) return false;
+    const char* env = getenv("GSR_SSIM_NO_TMA");
+    if (env && env[0] == '1') return false;
+    return encode_fn() != nullptr;
+}
+
+// [planes,H,W] fp32 tensor, box 44 x 42 x 1, no swizzle, out-of-bounds elements read as zero
+bool make_map(CUtensorMap* m, const float* base, int planes, int H, int W) {
+    const cuuint64_t dims[3] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)planes};
+    const cuuint64_t strides[2] = {(cuuint64_t)W * 4, (cuuint64_t)W * H * 4};
+    const cuuint32_t box[3] = {PITCH, HS, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    return encode_fn()(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), dims, strides, box, estr,
+                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <int MODE>
+int launch_fwd(int planes, int H, int W, float C1, float C2, const float* img1, const float* img2, float* ssim_map,
+               float* d0, float* d1, float* d2, double* partials, cudaStream_t st) {
+    TmaMaps maps;
+    memset(&maps, 0, sizeof(maps));
+    const dim3 g = tile_grid(planes, H, W);
+    if (tma_eligible(H, W, {img1, img2}) && make_map(&maps.m[0], img1, planes, H, W) && make_map(&maps.m[1], img2, planes, H, W))
+        ssim_fwd_kernel<MODE, true><<<g, NTHREADS, 0, st>>>(maps, H, W, C1, C2, img1, img2, ssim_map, d0, d1, d2, partials);
+    else
+        ssim_fwd_kernel<MODE, false><<<g, NTHREADS, 0, st>>>(maps, H, W, C1, C2, img1, img2, ssim_map, d0, d1, d2, partials);
+    return launch_status(MODE == 0 ? "ssim_fwd" : "l1_ssim_fwd");
+}
+
+template <int MODE>
+int launch_bwd(int planes, int H, int W, const float* img1, const float* img2, const float* dl, const float* d0,
+               const float* d1, const float* d2, const float* upstream, float c_ssim, float c_l1, float* out, cudaStream_t st) {
+    TmaMaps maps;
+    memset(&maps, 0, sizeof(maps));
+    const dim3 g = tile_grid(planes, H, W);
+    bool tma = MODE == 0 ? tma_eligible(H, W, {d0, d1, d2, dl}) : tma_eligible(H, W, {d0, d1, d2});
+    tma = tma && make_map(&maps.m[0], d0, planes, H, W) && make_map(&maps.m[1], d1, planes, H, W) &&
+          make_map(&maps.m[2], d2, planes, H, W) && (MODE != 0 || make_map(&maps.m[3], dl, planes, H, W));
+    if (tma)
+        ssim_bwd_kernel<MODE, true><<<g, NTHREADS, 0, st>>>(maps, H, W, img1, img2, dl, d0, d1, d2, upstream, c_ssim, c_l1, out);
+    else
+        ssim_bwd_kernel<MODE, false><<<g, NTHREADS, 0, st>>>(maps, H, W, img1, img2, dl, d0, d1, d2, upstream, c_ssim, c_l1, out);
+    return launch_status(MODE == 0 ? "ssim_bwd" : "l1_ssim_bwd");
+}
+
 }  // namespace
 
 extern "C" int gsr_ssim_forward(int planes, int H, int W, float C1, float C2, const float* img1, const float* img2,
@@ -317,9 +461,8 @@ extern "C" int gsr_ssim_forward(int planes, int H, int W, float C1, float C2, co
     if (train && !(dm_dmu1 && dm_dsigma1_sq && dm_dsigma12))
         return gsr_set_error(GSR_ERR_INVALID, "ssim forward: the three derivative outputs go together");
     if (!ssim_map && !train) return gsr_set_error(GSR_ERR_INVALID, "ssim forward: no output requested");
-    ssim_fwd_kernel<0><<<tile_grid(planes, H, W), NTHREADS, 0, (cudaStream_t)stream>>>(
-        H, W, C1, C2, img1, img2, ssim_map, dm_dmu1, dm_dsigma1_sq, dm_dsigma12, nullptr);
-    return launch_status("ssim_fwd");
+    return launch_fwd<0>(planes, H, W, C1, C2, img1, img2, ssim_map, dm_dmu1, dm_dsigma1_sq, dm_dsigma12, nullptr,
+                         (cudaStream_t)stream);
 }
 
 extern "C" int gsr_ssim_backward(int planes, int H, int W, const float* img1, const float* img2, const float* dL_dmap,
@@ -329,9 +472,8 @@ extern "C" int gsr_ssim_backward(int planes, int H, int W, const float* img1, co
     if (planes == 0 || H == 0 || W == 0) return GSR_OK;
     if (!img1 || !img2 || !dL_dmap || !dm_dmu1 || !dm_dsigma1_sq || !dm_dsigma12 || !dL_dimg1)
         return gsr_set_error(GSR_ERR_INVALID, "ssim backward: NULL argument");
-    ssim_bwd_kernel<0><<<tile_grid(planes, H, W), NTHREADS, 0, (cudaStream_t)stream>>>(
-        H, W, img1, img2, dL_dmap, dm_dmu1, dm_dsigma1_sq, dm_dsigma12, nullptr, 0.0f, 0.0f, dL_dimg1);
-    return launch_status("ssim_bwd");
+    return launch_bwd<0>(planes, H, W, img1, img2, dL_dmap, dm_dmu1, dm_dsigma1_sq, dm_dsigma12, nullptr, 0.0f, 0.0f,
+                         dL_dimg1, (cudaStream_t)stream);
 }
 
 extern "C" size_t gsr_l1_ssim_partials_bytes(int planes, int H, int W) {
@@ -351,9 +493,9 @@ extern "C" int gsr_l1_ssim_loss_forward(int planes, int H, int W, float C1, floa
         return gsr_set_error(GSR_ERR_INVALID, "l1_ssim loss forward: the three derivative outputs go together");
     if (((uintptr_t)partials & 7) != 0) return gsr_set_error(GSR_ERR_INVALID, "l1_ssim loss forward: partials must be 8-byte aligned");
     const dim3 g = tile_grid(planes, H, W);
-    ssim_fwd_kernel<1><<<g, NTHREADS, 0, (cudaStream_t)stream>>>(H, W, C1, C2, image, gt, nullptr, dm_dmu1, dm_dsigma1_sq,
-                                                                dm_dsigma12, reinterpret_cast<double*>(partials));
-    if (int rc = launch_status("l1_ssim_fwd")) return rc;
+    if (int rc = launch_fwd<1>(planes, H, W, C1, C2, image, gt, nullptr, dm_dmu1, dm_dsigma1_sq, dm_dsigma12,
+                               reinterpret_cast<double*>(partials), (cudaStream_t)stream))
+        return rc;
     const double n = (double)planes * (double)H * (double)W;
     loss_reduce_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(reinterpret_cast<const double*>(partials),
                                                              (size_t)g.x * g.y * g.z, 1.0 / n, lambda_dssim, loss_out);
@@ -368,8 +510,6 @@ extern "C" int gsr_l1_ssim_loss_backward(int planes, int H, int W, float lambda_
     if (!image || !gt || !dm_dmu1 || !dm_dsigma1_sq || !dm_dsigma12 || !dL_dimage)
         return gsr_set_error(GSR_ERR_INVALID, "l1_ssim loss backward: NULL argument");
     const float n = (float)((double)planes * (double)H * (double)W);
-    ssim_bwd_kernel<1><<<tile_grid(planes, H, W), NTHREADS, 0, (cudaStream_t)stream>>>(
-        H, W, image, gt, nullptr, dm_dmu1, dm_dsigma1_sq, dm_dsigma12, upstream, -lambda_dssim / n,
-        (1.0f - lambda_dssim) / n, dL_dimage);
-    return launch_status("l1_ssim_bwd");
+    return launch_bwd<1>(planes, H, W, image, gt, nullptr, dm_dmu1, dm_dsigma1_sq, dm_dsigma12, upstream, -lambda_dssim / n,
+                         (1.0f - lambda_dssim) / n, dL_dimage, (cudaStream_t)stream);
 }

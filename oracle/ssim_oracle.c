@@ -23,9 +23,10 @@
  * `val += G_k * p` of its two passes is one FFMA in tap order k = 0..10, and `x - mu*mu` is one FFMA.
  * This file spells those as fmaf() and is compiled with -ffp-contract=off.  The squared / product
  * inputs (do_sq, multiply_shared_mem, FS/ssim.cu:66-86) are rounded to fp32 before the window is
- * applied, as in the reference.  The closing rational expressions are written as the reference
- * writes them; how nvcc fuses those is not reproduced, so the maps are compared with a tolerance
- * (tests state it), not bit for bit.  Sums over pixels (the mean) are accumulated in double.
+ * applied, as in the reference.  The closing rational expressions follow the FFMA placement of the
+ * reference's own sm_100a SASS (see sso_ssim_forward) with IEEE divisions, so on a CPU with a correctly
+ * rounded fmaf the four maps and dL_dimg1 are BIT-IDENTICAL to the reference CUDA kernel's
+ * (tests/test_ssim_golden.py asserts equality).  Sums over pixels (the mean) are accumulated in double.
  *
  * Parity pin: (1) the reference's own test recipe (FS/tests/test.py:14-55: torch conv2d SSIM, checked
  * with torch.isclose) is run against this file by tests/test_ssim_oracle_cpu.py; (2) golden vectors
@@ -109,21 +110,32 @@ void sso_ssim_forward(int planes, int H, int W, float C1, float C2, const float*
         window_plane(b, NULL, H, W, 1, tmp, w[3]); /* conv(img2^2)    */
         window_plane(a, b, H, W, 2, tmp, w[4]);    /* conv(img1*img2) */
         for (size_t i = 0; i < n; ++i) {
+            /* FFMA placement read from the reference's own sm_100a SASS (nvcc 12.9.86 on FS/ssim.cu,
+             * cuobjdump of oracle/_ref/fused_ssim_cuda_ref.so): mu1*mu2 and mu2*mu2 are rounded products that are
+             * reused, so sigma12 and sigma2_sq are FMUL + FADD; sigma1_sq and mu1_sq + mu2_sq are fused. */
             float mu1 = w[0][i], mu2 = w[2][i];
+            float mu1_mu2 = mu1 * mu2;
+            float mu2_sq = mu2 * mu2;
+            float sigma12 = w[4][i] - mu1_mu2;
             float sigma1_sq = fmaf(-mu1, mu1, w[1][i]);
-            float sigma2_sq = fmaf(-mu2, mu2, w[3][i]);
-            float sigma12 = fmaf(-mu1, mu2, w[4][i]);
-            float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu1_mu2 = mu1 * mu2;
-            float C = 2.0f * mu1_mu2 + C1;
-            float D = 2.0f * sigma12 + C2;
-            float A = mu1_sq + mu2_sq + C1;
-            float B = sigma1_sq + sigma2_sq + C2;
-            ssim_map[pl * n + i] = (C * D) / (A * B);
+            float sigma2_sq = w[3][i] - mu2_sq;
+            float C = fmaf(mu1_mu2, 2.0f, C1);
+            float D = fmaf(sigma12, 2.0f, C2);
+            float A = fmaf(mu1, mu1, mu2_sq) + C1;
+            float B = (sigma1_sq + sigma2_sq) + C2;
+            float AB = A * B;
+            ssim_map[pl * n + i] = (C * D) / AB;
             if (dm_dmu1) {
-                dm_dmu1[pl * n + i] = (mu2 * 2.0f * D) / (A * B) - (mu2 * 2.0f * C) / (A * B)
-                                      - (mu1 * 2.0f * C * D) / (A * A * B) + (mu1 * 2.0f * C * D) / (A * B * B);
-                dm_dsigma1_sq[pl * n + i] = (-C * D) / (A * B * B);
-                dm_dsigma12[pl * n + i] = (2 * C) / (A * B);
+                float two_mu2 = mu2 + mu2, two_mu1 = mu1 + mu1;
+                float t1 = (D * two_mu2) / AB;
+                float t2 = (C * two_mu2) / AB;
+                float num = D * (C * two_mu1);
+                float t3 = num / (B * (A * A));
+                float ABB = B * AB;
+                float t4 = num / ABB;
+                dm_dmu1[pl * n + i] = ((t1 - t2) - t3) + t4;
+                dm_dsigma1_sq[pl * n + i] = (C * -D) / ABB;
+                dm_dsigma12[pl * n + i] = (C + C) / AB;
             }
         }
         for (int i = 0; i < 5; ++i) free(w[i]);
@@ -145,11 +157,10 @@ void sso_ssim_backward(int planes, int H, int W, const float* img1, const float*
         window_plane(dm_dsigma1_sq + pl * n, dl, H, W, 2, tmp, w[1]);
         window_plane(dm_dsigma12 + pl * n, dl, H, W, 2, tmp, w[2]);
         for (size_t i = 0; i < n; ++i) {
-            float g = 0.0f;
-            g += w[0][i];
-            g += img1[pl * n + i] * 2.0f * w[1][i];
-            g += img2[pl * n + i] * w[2][i];
-            dL_dimg1[pl * n + i] = g;
+            /* reference SASS: FADD(0, w0) ; FFMA(w1, p1+p1, .) ; FFMA(w2, p2, .) */
+            float p1 = img1[pl * n + i];
+            float g = fmaf(w[1][i], p1 + p1, 0.0f + w[0][i]);
+            dL_dimg1[pl * n + i] = fmaf(w[2][i], img2[pl * n + i], g);
         }
         for (int i = 0; i < 3; ++i) free(w[i]);
         free(tmp);

@@ -2,8 +2,9 @@
 reference-facing Python packages (fused_ssim, diff_gaussian_rasterization._C), against
   (i) the CPU oracle (oracle/ssim_oracle.c), (ii) the golden vectors of the reference CUDA kernel,
   (iii) the live reference CUDA build (oracle/_ref/fused_ssim_cuda_ref.so) on the same inputs.
-Tolerances (fp32): ssim_map max-abs <= 2e-5; derivative maps and gradients <= 2e-4 of the array's largest
-magnitude (the kernels use one reciprocal where the reference divides seven times)."""
+The SSIM API kernels (gsr_ssim_forward / gsr_ssim_backward) are compared BIT FOR BIT.  The fused-loss variant
+(one reciprocal where the reference divides seven times) is tolerance-checked: loss value <= 2e-6 abs, gradient
+<= 2e-4 of its largest magnitude."""
 import os
 
 import numpy as np
@@ -32,12 +33,12 @@ def test_c_abi_vs_oracle(cuda, name):
     ta, tb, tdl = _t(cuda, a, b, dl)
     m, d0, d1, d2 = capi.ssim_forward(ta, tb, True)
     om, od0, od1, od2 = so.fusedssim(so.C1, so.C2, a, b, True)
-    assert np.abs(m.cpu().numpy() - om).max() <= MAP_ATOL
+    assert np.array_equal(m.cpu().numpy(), om)                       # bit-exact
     for got, want in ((d0, od0), (d1, od1), (d2, od2)):
-        assert _rel(got.cpu().numpy(), want) <= DERIV_RTOL
+        assert np.array_equal(got.cpu().numpy(), want)
     g = capi.ssim_backward(ta, tb, tdl, d0, d1, d2)
     og = so.fusedssim_backward(so.C1, so.C2, a, b, dl, od0, od1, od2)
-    assert _rel(g.cpu().numpy(), og) <= DERIV_RTOL
+    assert np.array_equal(g.cpu().numpy(), og)
     # inference form: map only, same values
     m2, *_ = capi.ssim_forward(ta, tb, False)
     assert np.array_equal(m2.cpu().numpy(), m.cpu().numpy())
@@ -53,12 +54,12 @@ def test_c_abi_vs_golden(cuda, name):
     a, b, dl = ssim_cases.make(name)
     ta, tb, tdl = _t(cuda, a, b, dl)
     m, d0, d1, d2 = capi.ssim_forward(ta, tb, True)
-    assert np.abs(m.cpu().numpy() - gold["ssim_map"]).max() <= MAP_ATOL
-    assert _rel(d0.cpu().numpy(), gold["dm_dmu1"]) <= DERIV_RTOL
-    assert _rel(d1.cpu().numpy(), gold["dm_dsigma1_sq"]) <= DERIV_RTOL
-    assert _rel(d2.cpu().numpy(), gold["dm_dsigma12"]) <= DERIV_RTOL
+    assert np.array_equal(m.cpu().numpy(), gold["ssim_map"])         # bit-exact vs the reference CUDA kernel
+    assert np.array_equal(d0.cpu().numpy(), gold["dm_dmu1"])
+    assert np.array_equal(d1.cpu().numpy(), gold["dm_dsigma1_sq"])
+    assert np.array_equal(d2.cpu().numpy(), gold["dm_dsigma12"])
     g = capi.ssim_backward(ta, tb, tdl, d0, d1, d2)
-    assert _rel(g.cpu().numpy(), gold["dL_dimg1"]) <= DERIV_RTOL
+    assert np.array_equal(g.cpu().numpy(), gold["dL_dimg1"])
 
 
 @pytest.mark.parametrize("shape", [(1, 3, 64, 64), (1, 3, 545, 980), (2, 3, 1080, 1920)])
@@ -76,14 +77,12 @@ def test_vs_live_reference_cuda(cuda, shape):
     dl = torch.randn(shape, device=cuda)
     rm, r0, r1, r2 = ref.fusedssim(so.C1, so.C2, a, b, True)
     m, d0, d1, d2 = ours.fusedssim(so.C1, so.C2, a, b, True)
-    assert (m - rm).abs().max().item() <= MAP_ATOL
+    assert torch.equal(m, rm)                                        # bit-exact at every size
     for got, want in ((d0, r0), (d1, r1), (d2, r2)):
-        assert ((got - want).abs().max() / want.abs().max()).item() <= DERIV_RTOL
+        assert torch.equal(got, want)
     rg = ref.fusedssim_backward(so.C1, so.C2, a, b, dl, r0, r1, r2)
-    g = ours.fusedssim_backward(so.C1, so.C2, a, b, dl, r0, r1, r2)      # same derivative maps: isolates the backward
-    assert ((g - rg).abs().max() / rg.abs().max()).item() <= 1e-5
-    g2 = ours.fusedssim_backward(so.C1, so.C2, a, b, dl, d0, d1, d2)
-    assert ((g2 - rg).abs().max() / rg.abs().max()).item() <= DERIV_RTOL
+    g = ours.fusedssim_backward(so.C1, so.C2, a, b, dl, d0, d1, d2)
+    assert torch.equal(g, rg)
 
 
 @pytest.mark.parametrize("padding", ["same", "valid"])
@@ -117,10 +116,10 @@ def test_loss_utils_entry_points(cuda):
     ta, tb, tdl = _t(cuda, a, b, dl)
     m = fusedssim(so.C1, so.C2, ta, tb)
     om, od0, od1, od2 = so.fusedssim(so.C1, so.C2, a, b, True)
-    assert np.abs(m.cpu().numpy() - om).max() <= MAP_ATOL
+    assert np.array_equal(m.cpu().numpy(), om)
     g = fusedssim_backward(so.C1, so.C2, ta, tb, tdl)
     og = so.fusedssim_backward(so.C1, so.C2, a, b, dl, od0, od1, od2)
-    assert _rel(g.cpu().numpy(), og) <= DERIV_RTOL
+    assert np.array_equal(g.cpu().numpy(), og)
 
 
 @pytest.mark.parametrize("shape,lam", [((3, 64, 64), 0.2), ((3, 101, 167), 0.2), ((1, 3, 40, 56), 0.5), ((3, 546, 979), 0.2)])
@@ -175,3 +174,35 @@ def test_error_paths(cuda):
     e = torch.empty(0, 3, 16, 16, device=cuda)
     m, *_ = ours.fusedssim(so.C1, so.C2, e, e, True)
     assert m.numel() == 0
+
+
+@pytest.mark.parametrize("shape", [(1, 3, 64, 64), (2, 3, 100, 128), (1, 3, 1080, 1920)])
+def test_tma_and_manual_staging_agree(cuda, shape, monkeypatch):
+    """W % 4 == 0 shapes stage their tiles with TMA (cp.async.bulk.tensor, zero fill outside the image); the manual
+    path serves every other shape.  Both must give the same bits -- forward maps, backward, and the fused loss."""
+    import torch
+    from gsr_b200 import capi
+    torch.manual_seed(shape[-2])
+    a = torch.rand(shape, device=cuda)
+    b = (a + 0.1 * torch.randn(shape, device=cuda)).clamp(0, 1)
+    dl = torch.randn(shape, device=cuda)
+
+    def run():
+        m, d0, d1, d2 = capi.ssim_forward(a, b, True)
+        g = capi.ssim_backward(a, b, dl, d0, d1, d2)
+        sc = capi.LossScratch(shape, cuda)
+        loss = capi.l1_ssim_loss_forward(a, b, 0.2, sc).clone()
+        gl = capi.l1_ssim_loss_backward(a, b, 0.2, sc).clone()
+        torch.cuda.synchronize()
+        return m, d0, d1, d2, g, loss, gl
+
+    monkeypatch.delenv("GSR_SSIM_NO_TMA", raising=False)
+    with_tma = run()
+    monkeypatch.setenv("GSR_SSIM_NO_TMA", "1")
+    manual = run()
+    for x, y in zip(with_tma, manual):
+        assert torch.equal(x, y)
+    # and the manual path against the oracle on this W % 4 == 0 shape (the TMA path is covered by the other tests)
+    if shape[-1] <= 128:
+        om, *_ = so.fusedssim(so.C1, so.C2, a.cpu().numpy(), b.cpu().numpy(), True)
+        assert np.array_equal(manual[0].cpu().numpy(), om)

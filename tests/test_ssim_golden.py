@@ -10,8 +10,9 @@ import ssim_cases
 from oracle import ssim_oracle as so
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-# fp32 tolerances of the loss stage: maps are O(1) rational expressions of window sums
-MAP_ATOL = 2e-5          # ssim_map (values in [-1, 1])
+# The SSIM API kernels are compared BIT FOR BIT (np.array_equal).  Tolerances below are for the fused-loss variant
+# (one reciprocal instead of seven divisions) and for comparisons with float64 torch recipes:
+MAP_ATOL = 2e-5          # ssim_map (values in [-1, 1]); ill-conditioned where sigma^2 << C2 (smooth images)
 DERIV_RTOL = 2e-4        # derivative maps / gradients, relative to the largest magnitude of the array
 
 
@@ -27,11 +28,9 @@ def test_oracle_matches_reference_cuda(name):
     g = _load(name)
     a, b, dl = ssim_cases.make(name)
     m, d0, d1, d2 = so.fusedssim(so.C1, so.C2, a, b, True)
-    assert np.abs(m - g["ssim_map"]).max() <= MAP_ATOL
+    # the oracle spells the reference's FFMA placement (read from its sm_100a SASS): bit-identical
+    assert np.array_equal(m, g["ssim_map"])
     for got, key in ((d0, "dm_dmu1"), (d1, "dm_dsigma1_sq"), (d2, "dm_dsigma12")):
-        want = g[key]
-        assert np.abs(got - want).max() <= DERIV_RTOL * np.abs(want).max(), key
-    # backward from the REFERENCE's derivative maps (isolates the backward kernel)
-    gi = so.fusedssim_backward(so.C1, so.C2, a, b, dl, g["dm_dmu1"], g["dm_dsigma1_sq"], g["dm_dsigma12"])
-    want = g["dL_dimg1"]
-    assert np.abs(gi - want).max() <= DERIV_RTOL * np.abs(want).max()
+        assert np.array_equal(got, g[key]), key
+    gi = so.fusedssim_backward(so.C1, so.C2, a, b, dl, d0, d1, d2)
+    assert np.array_equal(gi, g["dL_dimg1"])

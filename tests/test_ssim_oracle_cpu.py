@@ -27,7 +27,7 @@ def _window(channel):
 def torch_ssim_map(img1, img2):
     """The map of /root/reference/utils/loss_utils.py:54-73 (before the mean)."""
     ch = img1.size(-3)
-    w = _window(ch).to(img1.dtype)
+    w = _window(ch).to(img1.dtype).to(img1.device)
     mu1 = F.conv2d(img1, w, padding=5, groups=ch)
     mu2 = F.conv2d(img2, w, padding=5, groups=ch)
     mu1_sq, mu2_sq, mu1_mu2 = mu1.pow(2), mu2.pow(2), mu1 * mu2
