@@ -10,7 +10,7 @@
 // owns a 32x32 tile of ONE plane (channel planes are independent: they go in the grid), stages the
 // 42x42 zero-padded inputs once, and runs the separable window as two register-blocked passes:
 //   pass 1 (horizontal): a thread produces 4 adjacent outputs of one row for ALL five windows
-//           (a, a^2, b, b^2, ab) from 16 staged values per image (4 LDS.128 each), sliding the 11 taps
+//           (a, a^2, b, b^2, ab) from 20 staged values per image (5 aligned LDS.128 each), sliding the 11 taps
 //           through registers;  42 rows x 8 groups = 336 items;
 //   pass 2 (vertical):   a thread produces 4 outputs of one column for all five windows from 14 rows
 //           of the pass-1 result (conflict-free LDS, consecutive lanes = consecutive x) and finishes
@@ -35,14 +35,17 @@ namespace {
 
 constexpr int TS = 32;            // tile side (pixels)
 constexpr int HS = TS + 10;       // staged side incl. the 5-pixel halo
-constexpr int PITCH = 44;         // staged row pitch in floats (16-byte multiple: LDS.128, and the TMA box row = 176 B)
-constexpr int PLANE_FLOATS = 1856; // one staged plane: HS*PITCH = 1848 floats, padded so that every plane starts 128-byte aligned (TMA)
+constexpr int XOFF = 8;           // staged columns start at x0 - 8: a TMA box must start on a 16-byte boundary of the row
+                                  // (x0 - 5 is not: cp.async.bulk.tensor then faults with "illegal instruction"), so three
+                                  // unused columns ride along on the left
+constexpr int PITCH = 48;         // staged row pitch in floats = TMA box width (192 B): columns x0-8 .. x0+39
+constexpr int PLANE_FLOATS = HS * PITCH; // 2016 floats = 8064 B = 63 x 128 B: every staged plane starts 128-byte aligned (TMA)
 constexpr int NTHREADS = 256;
 
 // ---- TMA staging ---------------------------------------------------------------------------------------
-// One elected thread issues one cp.async.bulk.tensor per input plane: a 44 x 42 x 1 box of the [planes,H,W] tensor at
-// (x0-5, y0-5, plane).  The TMA unit zero-fills everything outside the image (negative coordinates included), which is
-// exactly the reference's zero padding (ssim.cu:38-44), and lands the rows at the 176-byte pitch pass 1 reads --
+// One elected thread issues one cp.async.bulk.tensor per input plane: a 48 x 42 x 1 box of the [planes,H,W] tensor at
+// (x0-8, y0-5, plane).  The TMA unit zero-fills everything outside the image (negative coordinates included), which is
+// exactly the reference's zero padding (ssim.cu:38-44), and lands the rows at the 192-byte pitch pass 1 reads --
 // no per-thread index arithmetic, bounds checks, LDG or STS.  Needs W % 4 == 0 and a 16-byte aligned base (row pitch
 // and base address of a tensor map are 16-byte quantities); other shapes take the manual staging path below.
 struct TmaMaps { CUtensorMap m[4]; };
@@ -83,9 +86,9 @@ __device__ __forceinline__ constexpr float G(int k) {
 __device__ __forceinline__ void stage_plane(float* s, const float* __restrict__ plane, int H, int W, int x0, int y0) {
     for (int i = threadIdx.x; i < HS * PITCH; i += NTHREADS) {
         const int ly = i / PITCH, lx = i - ly * PITCH;
-        const int y = y0 + ly - 5, x = x0 + lx - 5;
+        const int y = y0 + ly - 5, x = x0 + lx - XOFF;
         float v = 0.0f;
-        if (lx < HS && x >= 0 && x < W && y >= 0 && y < H) v = __ldg(plane + (size_t)y * W + x);
+        if (x >= 0 && x < W && y >= 0 && y < H) v = __ldg(plane + (size_t)y * W + x);
         s[i] = v;
     }
 }
@@ -100,7 +103,7 @@ __device__ __forceinline__ void stage_all(float* s, const float* const (&planes)
         if (threadIdx.x == 0) {
             mbar_expect_tx(bar, NP * HS * PITCH * 4);
 #pragma unroll
-            for (int p = 0; p < NP; ++p) tma_load_3d(s + p * PLANE_FLOATS, &maps.m[p], x0 - 5, y0 - 5, (int)blockIdx.z, bar);
+            for (int p = 0; p < NP; ++p) tma_load_3d(s + p * PLANE_FLOATS, &maps.m[p], x0 - XOFF, y0 - 5, (int)blockIdx.z, bar);
         }
         mbar_wait(bar, 0);
     } else {
@@ -121,9 +124,12 @@ __device__ __forceinline__ void pass1(const float* __restrict__ s, float dl_cons
     for (int item = threadIdx.x; item < HS * 8; item += NTHREADS) {
         const int row = item >> 3, g = item & 7;
         const int off = row * PITCH + 4 * g;
-        float va[16], vb[16], vc[16], vd[16];
+        // staged column c holds pixel x0 - 8 + c; output 4g+o needs pixels x0+4g+o-5 .. +5 = columns 4g+o+3 .. 4g+o+13:
+        // five aligned LDS.128 (columns 4g .. 4g+19), of which elements 3..16 are used
+        constexpr int E0 = XOFF - 5;
+        float va[20], vb[20], vc[20], vd[20];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
+        for (int q = 0; q < 5; ++q) {
             const float4 t = reinterpret_cast<const float4*>(s + off)[q];
             va[4 * q] = t.x; va[4 * q + 1] = t.y; va[4 * q + 2] = t.z; va[4 * q + 3] = t.w;
             const float4 u = reinterpret_cast<const float4*>(s + PLANE_FLOATS + off)[q];
@@ -131,7 +137,7 @@ __device__ __forceinline__ void pass1(const float* __restrict__ s, float dl_cons
         }
         if (!FWD) {
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
+            for (int q = 0; q < 5; ++q) {
                 const float4 t = reinterpret_cast<const float4*>(s + 2 * PLANE_FLOATS + off)[q];
                 vc[4 * q] = t.x; vc[4 * q + 1] = t.y; vc[4 * q + 2] = t.z; vc[4 * q + 3] = t.w;
                 if (DLP) {
@@ -149,12 +155,12 @@ __device__ __forceinline__ void pass1(const float* __restrict__ s, float dl_cons
         for (int j = 0; j < 14; ++j) {
             float v[NQ];
             if (FWD) {
-                v[0] = va[j]; v[1] = __fmul_rn(va[j], va[j]); v[2] = vb[j]; v[3] = __fmul_rn(vb[j], vb[j]);
-                v[4] = __fmul_rn(va[j], vb[j]);
+                const float a = va[j + E0], b = vb[j + E0];
+                v[0] = a; v[1] = __fmul_rn(a, a); v[2] = b; v[3] = __fmul_rn(b, b); v[4] = __fmul_rn(a, b);
             } else {
                 // reference multiply_shared_mem (ssim.cu:66-80): the product is rounded before the window
-                const float d = DLP ? vd[j] : dl_const;
-                v[0] = __fmul_rn(va[j], d); v[1] = __fmul_rn(vb[j], d); v[2] = __fmul_rn(vc[j], d);
+                const float d = DLP ? vd[j + E0] : dl_const;
+                v[0] = __fmul_rn(va[j + E0], d); v[1] = __fmul_rn(vb[j + E0], d); v[2] = __fmul_rn(vc[j + E0], d);
             }
 #pragma unroll
             for (int o = 0; o < 4; ++o) {
@@ -267,7 +273,7 @@ ssim_fwd_kernel(const __grid_constant__ TmaMaps maps, int H, int W, float C1, fl
                     dm_dsigma12[idx] = 2.0f * C * inv;
                 }
                 s_map += CDi;
-                s_l1 += fabsf(sa[(4 * yg + o + 5) * PITCH + x + 5] - sb[(4 * yg + o + 5) * PITCH + x + 5]);
+                s_l1 += fabsf(sa[(4 * yg + o + 5) * PITCH + x + XOFF] - sb[(4 * yg + o + 5) * PITCH + x + XOFF]);
             }
         }
     }
@@ -338,16 +344,27 @@ ssim_bwd_kernel(const __grid_constant__ TmaMaps maps, int H, int W, const float*
     pass1<false, MODE == 0>(sin_, dl_const, hz);
     __syncthreads();
     const int x = threadIdx.x & 31, yg = threadIdx.x >> 5;
+    // the two image values of this thread's four pixels are requested BEFORE the vertical pass so that their
+    // DRAM latency hides under its 220 FFMA (they used to be the exposed tail of the CTA)
+    const int px = x0 + x;
+    float p1v[4], p2v[4];
+#pragma unroll
+    for (int o = 0; o < 4; ++o) {
+        const int py = y0 + 4 * yg + o;
+        const bool in = px < W && py < H;
+        const size_t idx = plane_off + (size_t)py * W + px;
+        p1v[o] = in ? __ldg(img1 + idx) : 0.0f;
+        p2v[o] = in ? __ldg(img2 + idx) : 0.0f;
+    }
     float w[3][4];
     pass2<3>(hz, x, yg, w);
-    const int px = x0 + x;
     if (px < W) {
 #pragma unroll
         for (int o = 0; o < 4; ++o) {
             const int py = y0 + 4 * yg + o;
             if (py < H) {
                 const size_t idx = plane_off + (size_t)py * W + px;
-                const float p1 = __ldg(img1 + idx), p2 = __ldg(img2 + idx);
+                const float p1 = p1v[o], p2 = p2v[o];
                 // ssim.cu:336,348-350,362-364 as the reference's SASS has it: FADD(0,w0) ; FFMA(w1, p1+p1, .) ; FFMA(w2, p2, .)
                 float g = __fmaf_rn(w[1][o], __fadd_rn(p1, p1), __fadd_rn(0.0f, w[0][o]));
                 g = __fmaf_rn(w[2][o], p2, g);
@@ -410,7 +427,7 @@ bool tma_eligible(int H, int W, std::initializer_list<const void*> ptrs) {
     return encode_fn() != nullptr;
 }
 
-// [planes,H,W] fp32 tensor, box 44 x 42 x 1, no swizzle, out-of-bounds elements read as zero
+// [planes,H,W] fp32 tensor, box 48 x 42 x 1, no swizzle, out-of-bounds elements read as zero
 bool make_map(CUtensorMap* m, const float* base, int planes, int H, int W) {
     const cuuint64_t dims[3] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)planes};
     const cuuint64_t strides[2] = {(cuuint64_t)W * 4, (cuuint64_t)W * H * 4};
