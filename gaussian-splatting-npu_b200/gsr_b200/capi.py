@@ -59,6 +59,12 @@ class ImageLayout(Structure):
     _fields_ = [(n, c_size_t) for n in ("final_T", "n_contrib", "ranges", "total")]
 
 
+class AdamSegment(ctypes.Structure):
+    """gsr_adam_segment (include/gsr_optim.h)."""
+    _fields_ = [("param", c_void_p), ("grad", c_void_p), ("exp_avg", c_void_p), ("exp_avg_sq", c_void_p),
+                ("rows", c_size_t), ("cols", c_int), ("split_col", c_int), ("lr_a", c_float), ("lr_b", c_float)]
+
+
 EXPORTS = ["gsr_forward", "gsr_backward", "gsr_mark_visible", "gsr_geometry_bytes", "gsr_image_bytes",
            "gsr_binning_bytes", "gsr_sort_temp_bytes", "gsr_sort_pairs", "gsr_get_geometry_layout",
            "gsr_get_binning_layout", "gsr_get_image_layout", "gsr_materialize_keys", "gsr_set_profiling",
@@ -66,7 +72,9 @@ EXPORTS = ["gsr_forward", "gsr_backward", "gsr_mark_visible", "gsr_geometry_byte
            "gsr_last_error", "gsr_version",
            # include/gsr_loss.h
            "gsr_ssim_forward", "gsr_ssim_backward", "gsr_l1_ssim_partials_bytes", "gsr_l1_ssim_loss_forward",
-           "gsr_l1_ssim_loss_backward"]
+           "gsr_l1_ssim_loss_backward",
+           # include/gsr_optim.h
+           "gsr_adam_step", "gsr_densification_stats"]
 
 _lib = None
 
@@ -117,6 +125,11 @@ def lib():
         L.gsr_l1_ssim_loss_forward.argtypes = [c_int, c_int, c_int, c_float, c_float, c_float] + [c_void_p] * 8
         L.gsr_l1_ssim_loss_backward.restype = c_int
         L.gsr_l1_ssim_loss_backward.argtypes = [c_int, c_int, c_int, c_float] + [c_void_p] * 8
+        # optimizer stage (include/gsr_optim.h)
+        L.gsr_adam_step.restype = c_int
+        L.gsr_adam_step.argtypes = [POINTER(AdamSegment), c_int, c_int, c_float, c_float, c_float, c_void_p, c_int, c_void_p]
+        L.gsr_densification_stats.restype = c_int
+        L.gsr_densification_stats.argtypes = [c_int] + [c_void_p] * 6
         _lib = L
     return _lib
 
@@ -347,3 +360,36 @@ def l1_ssim_loss_backward(image, gt, lambda_dssim, scratch, upstream=None):
     _check(lib().gsr_l1_ssim_loss_backward(planes, H, W, lambda_dssim, _ptr(image), _ptr(gt), *[_ptr(x) for x in scratch.dm],
                                            _ptr(upstream), _ptr(scratch.dL_dimage), _stream()))
     return scratch.dL_dimage
+
+
+# ---- optimizer stage (include/gsr_optim.h) --------------------------------------------------------------
+def adam_step(segments, step, beta1=0.9, beta2=0.999, eps=1e-15, visible=None, zero_grad=False):
+    """gsr_adam_step.  segments: list of dicts(param, grad, exp_avg, exp_avg_sq [rows, cols] contiguous CUDA fp32,
+    lr or (lr_a, lr_b, split_col)).  One launch for all of them."""
+    arr = (AdamSegment * len(segments))()
+    for i, sg in enumerate(segments):
+        p = sg["param"]
+        rows = p.shape[0]
+        cols = p.numel() // rows if rows else 1
+        if "lr" in sg:
+            lr_a = lr_b = float(sg["lr"])
+            split = cols
+        else:
+            lr_a, lr_b, split = float(sg["lr_a"]), float(sg["lr_b"]), int(sg["split_col"])
+        for k in ("param", "grad", "exp_avg", "exp_avg_sq"):
+            assert sg[k].is_cuda and sg[k].is_contiguous() and sg[k].dtype == torch.float32 and sg[k].numel() == p.numel()
+        arr[i] = AdamSegment(p.data_ptr(), sg["grad"].data_ptr(), sg["exp_avg"].data_ptr(), sg["exp_avg_sq"].data_ptr(),
+                             rows, cols, split, lr_a, lr_b)
+    vis = None
+    if visible is not None:
+        assert visible.is_cuda and visible.is_contiguous() and visible.dtype in (torch.bool, torch.uint8)
+        vis = c_void_p(visible.data_ptr())
+    _check(lib().gsr_adam_step(arr, len(segments), int(step), beta1, beta2, eps, vis, int(zero_grad), _stream()))
+
+
+def densification_stats(grad_means2D, radii, xyz_gradient_accum, denom, max_radii2D):
+    """gsr_densification_stats (train.py:166-167, gaussian_model.py:471-473), in place."""
+    P = radii.shape[0]
+    assert grad_means2D.shape == (P, 3) and grad_means2D.is_contiguous() and radii.dtype == torch.int32
+    _check(lib().gsr_densification_stats(P, _ptr(grad_means2D), _ptr(radii), _ptr(xyz_gradient_accum), _ptr(denom),
+                                         _ptr(max_radii2D), _stream()))

@@ -105,7 +105,12 @@ class DensificationStats:
         self._d_accum, self._d_denom, self._d_radii = z(P, 1), z(P, 1), z(P)
 
     def add_view(self, grad_means2D, radii):
-        vis = radii > 0
+        if grad_means2D.is_cuda:
+            # one fused launch (csrc/adam.cu: densification_stats_kernel) instead of three indexed updates
+            from . import capi
+            capi.densification_stats(grad_means2D.contiguous(), radii.contiguous(), self._d_accum, self._d_denom, self._d_radii)
+            return
+        vis = radii > 0      # host tensors (the gloo CPU tests of the reduction logic)
         self._d_accum[vis] += torch.norm(grad_means2D[vis, :2], dim=-1, keepdim=True)
         self._d_denom[vis] += 1
         self._d_radii[vis] = torch.max(self._d_radii[vis], radii[vis].float())

@@ -1,0 +1,49 @@
+"""The optimizer the reference attaches to the Gaussians, on the flat bucket of gsr_b200.dist.FlatGaussians.
+
+Mirrors GaussianModel.training_setup (/root/reference/scene/gaussian_model.py:178-201): Adam(lr=0, eps=1e-15) with the
+groups xyz / f_dc / f_rest / opacity / scaling / rotation and their learning rates
+(/root/reference/arguments/__init__.py OptimizationParams), stepped as /root/reference/train.py:176-186 does.
+One kernel launch updates all 59 floats of every Gaussian (csrc/adam.cu); `step(visible=...)` is the sparse form
+train.py:179-181 asks for (`optimizer.step(visible, N)`), `zero_grad=True` clears the consumed gradients in the same
+pass (optimizer.zero_grad()).  No CPU fallback.
+"""
+import torch
+
+from . import capi
+from .dist import SEGMENTS
+
+DEFAULT_LRS = dict(xyz=1.6e-4, f_dc=2.5e-3, f_rest=2.5e-3 / 20.0, opacity=0.025, scaling=0.005, rotation=0.001)
+
+
+class GaussianAdam:
+    def __init__(self, flat, lrs=None, spatial_lr_scale=1.0, betas=(0.9, 0.999), eps=1e-15):
+        self.flat, self.betas, self.eps, self.step_count = flat, betas, eps, 0
+        self.lrs = dict(DEFAULT_LRS)
+        self.lrs.update(lrs or {})
+        self.lrs["xyz"] = self.lrs["xyz"] * spatial_lr_scale
+        self.exp_avg = torch.zeros_like(flat.params)
+        self.exp_avg_sq = torch.zeros_like(flat.params)
+
+    def set_lr(self, name, lr):
+        """update_learning_rate (gaussian_model.py:203-209) sets the xyz group's rate every iteration."""
+        self.lrs[name] = float(lr)
+
+    def _segments(self):
+        f = self.flat
+        v = lambda buf, name: f._view(buf, name).reshape(f.P, -1)
+        lr_of = dict(xyz=("xyz", "xyz", 3), shs=("f_dc", "f_rest", 3), opacity=("opacity", "opacity", 1),
+                     scales=("scaling", "scaling", 3), rotations=("rotation", "rotation", 4))
+        segs = []
+        for name, _ in SEGMENTS:
+            a, b, split = lr_of[name]
+            segs.append(dict(param=v(f.params, name), grad=v(f.bucket, name), exp_avg=v(self.exp_avg, name),
+                             exp_avg_sq=v(self.exp_avg_sq, name), lr_a=self.lrs[a], lr_b=self.lrs[b], split_col=split))
+        return segs
+
+    def step(self, visible=None, zero_grad=False):
+        self.step_count += 1
+        capi.adam_step(self._segments(), self.step_count, self.betas[0], self.betas[1], self.eps, visible=visible,
+                       zero_grad=zero_grad)
+
+    def zero_grad(self):
+        self.flat.bucket.zero_()
