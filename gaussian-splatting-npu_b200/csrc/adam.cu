@@ -70,16 +70,32 @@ adam_kernel(const __grid_constant__ AdamTable t) {
         float4 p[ADAM_QUADS], g[ADAM_QUADS], m[ADAM_QUADS], v[ADAM_QUADS];
         bool live[ADAM_QUADS];
         uint32_t e0[ADAM_QUADS];
+        // (a) which quads are live: the visibility bytes of all four quads are requested together (one round trip)
+        uint32_t row0[ADAM_QUADS], col0[ADAM_QUADS];
+        unsigned char vb[ADAM_QUADS][4];
 #pragma unroll
         for (int k = 0; k < ADAM_QUADS; ++k) {
             e0[k] = base + (k * ADAM_THREADS + threadIdx.x) * 4;
             live[k] = e0[k] + 3 < sg.n;             // full quads only; the tail is done scalar below
-            if (live[k] && vis) {
-                const uint32_t r0 = e0[k] / sg.cols, r1 = (e0[k] + 3) / sg.cols;
-                bool any = false;
-                for (uint32_t r = r0; r <= r1; ++r) any |= vis[r] != 0;
-                live[k] = any;
+            row0[k] = e0[k] / sg.cols;
+            col0[k] = e0[k] - row0[k] * sg.cols;
+            if (vis) {
+                // rows of the quad's four elements (cols >= 4: at most two distinct rows; cols < 4: up to four)
+                uint32_t r = row0[k], c = col0[k];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    vb[k][j] = live[k] ? __ldg(vis + r) : 0;
+                    if (++c == sg.cols) { c = 0; ++r; }
+                }
             }
+        }
+        if (vis) {
+#pragma unroll
+            for (int k = 0; k < ADAM_QUADS; ++k) live[k] = live[k] && (vb[k][0] | vb[k][1] | vb[k][2] | vb[k][3]);
+        }
+        // (b) all loads of the live quads in flight before the first use
+#pragma unroll
+        for (int k = 0; k < ADAM_QUADS; ++k) {
             if (live[k]) {
                 p[k] = ld_cs_f4(sg.p + e0[k]);
                 g[k] = ld_cs_f4(sg.g + e0[k]);
@@ -90,15 +106,15 @@ adam_kernel(const __grid_constant__ AdamTable t) {
 #pragma unroll
         for (int k = 0; k < ADAM_QUADS; ++k) {
             if (!live[k]) continue;
-            uint32_t row = e0[k] / sg.cols, col = e0[k] - row * sg.cols;
+            uint32_t col = col0[k];
             float* pp = &p[k].x; float* gp = &g[k].x; float* mp = &m[k].x; float* vp = &v[k].x;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                if (!vis || vis[row]) {
+                if (!vis || vb[k][j]) {
                     adam_one(pp[j], gp[j], mp[j], vp[j], col < sg.split ? sg.step_a : sg.step_b, t);
                     gp[j] = 0.0f;
                 }
-                if (++col == sg.cols) { col = 0; ++row; }
+                if (++col == sg.cols) col = 0;
             }
             stg_stream_f4(reinterpret_cast<float4*>(sg.p + e0[k]), p[k]);
             stg_stream_f4(reinterpret_cast<float4*>(sg.m + e0[k]), m[k]);
@@ -151,8 +167,8 @@ densification_stats_kernel(int P, const float* __restrict__ grad2D, const int* _
 
 }  // namespace
 
-extern "C" int gsr_adam_step(const gsr_adam_segment* segments, int n_segments, int step, float beta1, float beta2,
-                             float eps, const unsigned char* visible, int zero_grad, void* stream) {
+extern "C" int gsr_adam_step(const gsr_adam_segment* segments, int n_segments, int step, double beta1, double beta2,
+                             double eps, const unsigned char* visible, int zero_grad, void* stream) {
     if (n_segments < 0 || n_segments > GSR_ADAM_MAX_SEGMENTS)
         return gsr_set_error(GSR_ERR_INVALID, "adam: between 0 and 8 segments per call");
     if (n_segments == 0) return GSR_OK;
@@ -161,13 +177,14 @@ extern "C" int gsr_adam_step(const gsr_adam_segment* segments, int n_segments, i
     AdamTable t;
     memset(&t, 0, sizeof(t));
     // bias corrections in double on the host, as torch computes them in Python floats (adam.py: _single_tensor_adam)
-    const double bc1 = 1.0 - std::pow((double)beta1, (double)step);
-    const double bc2 = 1.0 - std::pow((double)beta2, (double)step);
-    t.one_minus_b1 = 1.0f - beta1;
-    t.b2 = beta2;
-    t.one_minus_b2 = 1.0f - beta2;
+    // (torch rounds each scalar to fp32 once, from the double: 1-beta2 = 0.001 -> fp32, not 1.0f - 0.999f)
+    const double bc1 = 1.0 - std::pow(beta1, (double)step);
+    const double bc2 = 1.0 - std::pow(beta2, (double)step);
+    t.one_minus_b1 = (float)(1.0 - beta1);
+    t.b2 = (float)beta2;
+    t.one_minus_b2 = (float)(1.0 - beta2);
     t.bc2_sqrt = (float)std::sqrt(bc2);
-    t.eps = eps;
+    t.eps = (float)eps;
     t.visible = visible;
     t.zero_grad = zero_grad;
     bool vec = true;

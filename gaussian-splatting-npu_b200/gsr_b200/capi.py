@@ -8,7 +8,7 @@ No fallback: a missing library raises.
 """
 import ctypes
 import os
-from ctypes import (CFUNCTYPE, POINTER, Structure, c_char_p, c_float, c_int, c_size_t, c_ubyte,
+from ctypes import (CFUNCTYPE, POINTER, Structure, c_char_p, c_double, c_float, c_int, c_size_t, c_ubyte,
                     c_uint32, c_uint64, c_void_p)
 
 import torch
@@ -127,7 +127,7 @@ def lib():
         L.gsr_l1_ssim_loss_backward.argtypes = [c_int, c_int, c_int, c_float] + [c_void_p] * 8
         # optimizer stage (include/gsr_optim.h)
         L.gsr_adam_step.restype = c_int
-        L.gsr_adam_step.argtypes = [POINTER(AdamSegment), c_int, c_int, c_float, c_float, c_float, c_void_p, c_int, c_void_p]
+        L.gsr_adam_step.argtypes = [POINTER(AdamSegment), c_int, c_int, c_double, c_double, c_double, c_void_p, c_int, c_void_p]
         L.gsr_densification_stats.restype = c_int
         L.gsr_densification_stats.argtypes = [c_int] + [c_void_p] * 6
         _lib = L

@@ -46,7 +46,8 @@ typedef struct gsr_adam_segment {
  * One Adam step over all segments in ONE launch (torch.optim.Adam.step for the six groups: ~24 foreach kernels).
  *   m = m + (1-beta1) (g - m);  v = beta2 v + (1-beta2) g g;
  *   p = p - lr/(1-beta1^step) * m / (sqrt(v)/sqrt(1-beta2^step) + eps)
- * `step` is the 1-based step count AFTER the increment (torch increments first).
+ * `step` is the 1-based step count AFTER the increment (torch increments first).  beta1/beta2/eps are doubles, as
+ * in torch: 1-beta and the bias corrections are formed in double and rounded to fp32 once.
  * visible (u8[rows], may be NULL): when given, only rows with visible[row] != 0 are updated -- parameters AND
  * moments of the other rows are left untouched (the "sparse Adam" variant train.py:179-181 asks for through
  * optimizer.step(visible, N); NULL = the reference's dense torch.optim.Adam).  All segments must have the same row
@@ -54,7 +55,7 @@ typedef struct gsr_adam_segment {
  * zero_grad != 0 additionally clears the gradients that were consumed (optimizer.zero_grad(), train.py:186), so the
  * next step's first backward can run in accumulate mode; the gradient pointers must then be writable.
  */
-int gsr_adam_step(const gsr_adam_segment* segments, int n_segments, int step, float beta1, float beta2, float eps,
+int gsr_adam_step(const gsr_adam_segment* segments, int n_segments, int step, double beta1, double beta2, double eps,
                   const unsigned char* visible, int zero_grad, void* stream);
 
 /*

@@ -1,0 +1,138 @@
+"""GPU parity of the optimizer stage (csrc/adam.cu) through the C ABI (gsr_b200.capi -> libgsr_b200.so) against
+  (i) the numpy oracle (oracle/optim_oracle.py), (ii) torch.optim.Adam itself -- the optimizer the reference
+  constructs at /root/reference/scene/gaussian_model.py:178-201 -- on this GPU.
+Tolerances (fp32): moments <= 1e-6 of their input scale, parameters <= 1e-4 of one step (lr) + fp32 rounding."""
+import numpy as np
+import pytest
+
+from oracle import optim_oracle as oo
+from test_optim_oracle_cpu import GROUPS
+
+pytestmark = pytest.mark.gpu
+
+
+def _mk(P, seed):
+    rng = np.random.default_rng(seed)
+    params = {n: rng.standard_normal((P, c)).astype(np.float32) for n, c, _ in GROUPS}
+    return rng, params
+
+
+def _segs(t, cols=None):
+    return [dict(param=t["p"][n], grad=t["g"][n], exp_avg=t["m"][n], exp_avg_sq=t["v"][n], lr=lr) for n, _, lr in GROUPS]
+
+
+@pytest.mark.parametrize("P", [1, 257, 4099])
+def test_adam_vs_oracle_and_torch(cuda, P):
+    import torch
+    from gsr_b200 import capi
+    rng, params = _mk(P, P)
+    dev = {k: {n: torch.from_numpy(params[n].copy()).to(cuda) if k == "p" else torch.zeros(P, c, device=cuda)
+               for n, c, _ in GROUPS} for k in ("p", "g", "m", "v")}
+    tp = {n: torch.nn.Parameter(torch.from_numpy(params[n].copy()).to(cuda)) for n, _, _ in GROUPS}
+    opt = torch.optim.Adam([{"params": [tp[n]], "lr": lr, "name": n} for n, _, lr in GROUPS], lr=0.0, eps=1e-15)
+    m = {n: np.zeros_like(params[n]) for n, _, _ in GROUPS}
+    v = {n: np.zeros_like(params[n]) for n, _, _ in GROUPS}
+    for step in range(1, 6):
+        grads = {n: (rng.standard_normal((P, c)) * 10.0 ** rng.integers(-6, 1)).astype(np.float32) for n, c, _ in GROUPS}
+        for n, _, lr in GROUPS:
+            dev["g"][n].copy_(torch.from_numpy(grads[n]))
+            tp[n].grad = torch.from_numpy(grads[n].copy()).to(cuda)
+            oo.adam_step(params[n], grads[n], m[n], v[n], step, lr)
+        capi.adam_step(_segs(dev), step)
+        opt.step()
+        for n, _, lr in GROUPS:
+            gmax = np.abs(grads[n]).max()
+            for want_p, want_m, want_v in ((params[n], m[n], v[n]),
+                                           (tp[n].detach().cpu().numpy(), opt.state[tp[n]]["exp_avg"].cpu().numpy(),
+                                            opt.state[tp[n]]["exp_avg_sq"].cpu().numpy())):
+                assert np.abs(dev["m"][n].cpu().numpy() - want_m).max() <= 1e-6 * max(gmax, np.abs(want_m).max()), (n, step)
+                assert np.abs(dev["v"][n].cpu().numpy() - want_v).max() <= 1e-6 * max(gmax ** 2, np.abs(want_v).max()), (n, step)
+                assert np.abs(dev["p"][n].cpu().numpy() - want_p).max() <= 1e-4 * lr + 2e-7 * np.abs(want_p).max(), (n, step)
+
+
+def test_gaussian_adam_on_flat_bucket_matches_six_group_torch_adam(cuda):
+    """The host mirror (gsr_b200.optim.GaussianAdam over FlatGaussians): SH row = f_dc + f_rest with their own rates,
+    zero_grad fused, visible mask = sparse step."""
+    import torch
+    import cases
+    from gsr_b200.dist import FlatGaussians
+    from gsr_b200.optim import GaussianAdam, DEFAULT_LRS
+    scene, cam, opts = cases.get_case("tiny64")
+    G = FlatGaussians.from_numpy(scene, cuda)
+    P = G.P
+    opt = GaussianAdam(G, spatial_lr_scale=5.0)
+    ref = {"xyz": G.xyz.clone(), "f_dc": G.shs[:, :1].clone(), "f_rest": G.shs[:, 1:].clone(), "opacity": G.opacity.clone(),
+           "scaling": G.scales.clone(), "rotation": G.rotations.clone()}
+    tp = {k: torch.nn.Parameter(t.contiguous()) for k, t in ref.items()}
+    lrs = dict(DEFAULT_LRS)
+    lrs["xyz"] *= 5.0
+    topt = torch.optim.Adam([{"params": [tp[k]], "lr": lrs[k], "name": k} for k in tp], lr=0.0, eps=1e-15)
+    gen = torch.Generator(device="cuda").manual_seed(1)
+    for step in range(3):
+        G.bucket.normal_(generator=gen)
+        gv = G.grad_views()
+        tp["xyz"].grad = gv["dL_dmeans3D"].clone()
+        tp["f_dc"].grad = gv["dL_dsh"][:, :1].clone()
+        tp["f_rest"].grad = gv["dL_dsh"][:, 1:].clone()
+        tp["opacity"].grad = gv["dL_dopacity"].clone()
+        tp["scaling"].grad = gv["dL_dscales"].clone()
+        tp["rotation"].grad = gv["dL_drotations"].clone()
+        opt.step(zero_grad=True)
+        topt.step()
+        for gview in G.grad_views().values():               # optimizer.zero_grad() fused into the step
+            assert float(gview.abs().max()) == 0.0           # (the 64-float padding between segments is not a gradient)
+    got = {"xyz": G.xyz, "f_dc": G.shs[:, :1], "f_rest": G.shs[:, 1:], "opacity": G.opacity, "scaling": G.scales,
+           "rotation": G.rotations}
+    for k in tp:
+        d = (got[k] - tp[k].detach()).abs().max().item()
+        assert d <= 1e-4 * lrs[k] + 2e-7 * tp[k].abs().max().item(), (k, d)
+    # sparse step: rows outside the mask keep parameters and moments bit for bit
+    vis = torch.rand(P, device=cuda, generator=gen) < 0.3
+    before = (G.params.clone(), opt.exp_avg.clone(), opt.exp_avg_sq.clone())
+    G.bucket.normal_(generator=gen)
+    opt.step(visible=vis)
+    for name, n in (("xyz", 3), ("shs", 48), ("opacity", 1), ("scales", 3), ("rotations", 4)):
+        for now, was in zip((G.params, opt.exp_avg, opt.exp_avg_sq), before):
+            a, b = G._view(now, name).reshape(P, -1), G._view(was, name).reshape(P, -1)
+            assert torch.equal(a[~vis], b[~vis])
+            assert not torch.equal(a[vis], b[vis])
+
+
+def test_unaligned_segments_take_the_scalar_path(cuda):
+    import torch
+    from gsr_b200 import capi
+    rng = np.random.default_rng(4)
+    n = 1001
+    host = {k: rng.standard_normal(n + 1).astype(np.float32) for k in "pg"}
+    big = {k: torch.from_numpy(host[k]).to(cuda) if k in host else torch.zeros(n + 1, device=cuda) for k in "pgmv"}
+    t = {k: big[k][1:].view(n, 1) for k in big}             # 4-byte aligned only
+    p, m, v = host["p"][1:].reshape(n, 1).copy(), np.zeros((n, 1), np.float32), np.zeros((n, 1), np.float32)
+    oo.adam_step(p, host["g"][1:].reshape(n, 1), m, v, 1, 0.01)
+    capi.adam_step([dict(param=t["p"], grad=t["g"], exp_avg=t["m"], exp_avg_sq=t["v"], lr=0.01)], 1)
+    assert np.abs(t["p"].cpu().numpy() - p).max() <= 1e-6
+
+
+def test_densification_stats_vs_oracle_and_reference_expressions(cuda):
+    import torch
+    from gsr_b200 import capi
+    rng = np.random.default_rng(3)
+    P = 100_003
+    g2 = rng.standard_normal((P, 3)).astype(np.float32)
+    radii = rng.integers(0, 40, P).astype(np.int32)
+    radii[rng.random(P) < 0.5] = 0
+    accum = rng.random((P, 1)).astype(np.float32)
+    denom = rng.integers(0, 5, (P, 1)).astype(np.float32)
+    maxr = rng.integers(0, 30, P).astype(np.float32)
+    t = [torch.from_numpy(a.copy()).to(cuda) for a in (g2, radii, accum, denom, maxr)]
+    capi.densification_stats(*t)
+    oo.densification_stats(g2, radii, accum, denom, maxr)
+    assert np.allclose(t[2].cpu().numpy(), accum, rtol=1e-6, atol=0)
+    assert np.array_equal(t[3].cpu().numpy(), denom) and np.array_equal(t[4].cpu().numpy(), maxr)
+
+
+def test_error_paths(cuda):
+    import torch
+    from gsr_b200 import capi
+    z = torch.zeros(4, 3, device=cuda)
+    with pytest.raises(RuntimeError, match="step counts from 1"):
+        capi.adam_step([dict(param=z, grad=z, exp_avg=z, exp_avg_sq=z, lr=0.1)], 0)
