@@ -74,7 +74,9 @@ EXPORTS = ["gsr_forward", "gsr_backward", "gsr_mark_visible", "gsr_geometry_byte
            "gsr_ssim_forward", "gsr_ssim_backward", "gsr_l1_ssim_partials_bytes", "gsr_l1_ssim_loss_forward",
            "gsr_l1_ssim_loss_backward",
            # include/gsr_optim.h
-           "gsr_adam_step", "gsr_densification_stats"]
+           "gsr_adam_step", "gsr_densification_stats",
+           # include/gsr_ply.h (bound in gsr_b200/ply.py)
+           "gsr_ply_parse_header", "gsr_ply_write_header", "gsr_ply_unpack", "gsr_ply_pack"]
 
 _lib = None
 
