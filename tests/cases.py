@@ -22,7 +22,7 @@ from gsr_b200 import synth  # noqa: E402
 def _lego_cam(k, W=800, H=800):
     with open(os.path.join(ROOT, "tests", "golden", "lego_cams.json")) as f:
         t = json.load(f)
-    return synth.blender_camera(t["transform_matrix"][k], W, H, t["camera_angle_x"])
+    return synth.blender_camera(t["transform_matrix"][k % len(t["transform_matrix"])], W, H, t["camera_angle_x"])
 
 
 def _one_gaussian():

