@@ -330,6 +330,12 @@ def main():
     if args.impl == "reference":
         return run_reference(args)
 
+    # stdout carries exactly ONE JSON line: anything a library prints there (NCCL's "NCCL version ..." banner when
+    # NCCL_DEBUG is set, for one) is sent to stderr; the line itself goes to the saved descriptor at the end
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
     import torch
     import torch.distributed as dist
     from gsr_b200 import capi
@@ -646,7 +652,8 @@ def main():
                     R.close()
             except Exception as exc:  # informational leg only
                 out["reference_cuda_same_box"] = {"error": str(exc)[:200]}
-        print(json.dumps(out))
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(out) + "\n").encode())
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
