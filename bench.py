@@ -205,6 +205,24 @@ def loss_stage_report(dev, H, W, hbm_peak, reps=30):
                         "peak": hbm_peak, "unit": "GB/s", "frac": (bytes_fwd + bytes_bwd) / (t_fwd + t_bwd) / 1e6 / hbm_peak,
                         "fwd_frac": bytes_fwd / t_fwd / 1e6 / hbm_peak, "bwd_frac": bytes_bwd / t_bwd / 1e6 / hbm_peak},
            "ours_reference_api_ms": timed(composed(our_fused_ssim))}
+    # render epilogue (exposure affine + clamp, gaussian_renderer/__init__.py:112-119): ours vs the reference's torch lines
+    expo = (torch.eye(3, 4, device=dev) + 0.05 * torch.randn(3, 4, device=dev)).contiguous()
+    dL = torch.randn_like(img)
+    pre = img * 1.4 - 0.2
+
+    def ours_epilogue():
+        capi.exposure_clamp_forward(pre, expo)
+        capi.exposure_clamp_backward(pre, expo, dL)
+
+    def torch_epilogue():
+        a, e = pre.detach().requires_grad_(True), expo.detach().requires_grad_(True)
+        y = (torch.matmul(a.permute(1, 2, 0), e[:3, :3]).permute(2, 0, 1) + e[:3, 3, None, None]).clamp(0, 1)
+        y.backward(dL)
+
+    t_ep = timed(ours_epilogue)
+    rep["epilogue"] = {"workload": "exposure affine + clamp, forward + backward (image and exposure gradients)",
+                       "ours_ms": t_ep, "reference_torch_lines_ms": timed(torch_epilogue), "gpu_launches": 3,
+                       "algorithmic_bytes": 20 * n, "hbm_frac": 20 * n / t_ep / 1e6 / hbm_peak}
     try:
         from oracle import build_ref
         ref = build_ref.load_fused_ssim()

@@ -20,7 +20,7 @@ LIB = os.path.join(HERE, "gsr_b200", "libgsr_b200.so")
 PKG = os.path.join(HERE, "diff_gaussian_rasterization")
 
 CU_SOURCES = ["gsr_api.cu", "preprocess_fwd.cu", "binning.cu", "radix_sort.cu", "render_fwd.cu",
-              "render_bwd.cu", "preprocess_bwd.cu", "ssim.cu", "adam.cu", "ply_io.cu"]
+              "render_bwd.cu", "preprocess_bwd.cu", "ssim.cu", "adam.cu", "ply_io.cu", "epilogue.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
 

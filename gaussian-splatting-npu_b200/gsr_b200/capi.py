@@ -72,7 +72,8 @@ EXPORTS = ["gsr_forward", "gsr_backward", "gsr_mark_visible", "gsr_geometry_byte
            "gsr_last_error", "gsr_version",
            # include/gsr_loss.h
            "gsr_ssim_forward", "gsr_ssim_backward", "gsr_l1_ssim_partials_bytes", "gsr_l1_ssim_loss_forward",
-           "gsr_l1_ssim_loss_backward",
+           "gsr_l1_ssim_loss_backward", "gsr_exposure_clamp_forward", "gsr_exposure_partials_bytes",
+           "gsr_exposure_clamp_backward",
            # include/gsr_optim.h
            "gsr_adam_step", "gsr_densification_stats",
            # include/gsr_ply.h (bound in gsr_b200/ply.py)
@@ -127,6 +128,12 @@ def lib():
         L.gsr_l1_ssim_loss_forward.argtypes = [c_int, c_int, c_int, c_float, c_float, c_float] + [c_void_p] * 8
         L.gsr_l1_ssim_loss_backward.restype = c_int
         L.gsr_l1_ssim_loss_backward.argtypes = [c_int, c_int, c_int, c_float] + [c_void_p] * 8
+        L.gsr_exposure_clamp_forward.restype = c_int
+        L.gsr_exposure_clamp_forward.argtypes = [c_int, c_int] + [c_void_p] * 4
+        L.gsr_exposure_partials_bytes.restype = c_size_t
+        L.gsr_exposure_partials_bytes.argtypes = [c_int, c_int]
+        L.gsr_exposure_clamp_backward.restype = c_int
+        L.gsr_exposure_clamp_backward.argtypes = [c_int, c_int] + [c_void_p] * 7
         # optimizer stage (include/gsr_optim.h)
         L.gsr_adam_step.restype = c_int
         L.gsr_adam_step.argtypes = [POINTER(AdamSegment), c_int, c_int, c_double, c_double, c_double, c_void_p, c_int, c_void_p]
@@ -362,6 +369,30 @@ def l1_ssim_loss_backward(image, gt, lambda_dssim, scratch, upstream=None):
     _check(lib().gsr_l1_ssim_loss_backward(planes, H, W, lambda_dssim, _ptr(image), _ptr(gt), *[_ptr(x) for x in scratch.dm],
                                            _ptr(upstream), _ptr(scratch.dL_dimage), _stream()))
     return scratch.dL_dimage
+
+
+def exposure_clamp_forward(image, exposure=None):
+    """gsr_exposure_clamp_forward: clamp(exposure[:3,:3]^T . image + exposure[:3,3], 0, 1) of one [3,H,W] image
+    (gaussian_renderer/__init__.py:112-119); exposure None = clamp only."""
+    assert image.dim() == 3 and image.shape[0] == 3 and image.dtype == torch.float32
+    if exposure is not None:
+        assert exposure.dtype == torch.float32 and tuple(exposure.shape) == (3, 4)
+    out = torch.empty_like(image)
+    _check(lib().gsr_exposure_clamp_forward(image.shape[1], image.shape[2], _ptr(image), _ptr(exposure), _ptr(out), _stream()))
+    return out
+
+
+def exposure_clamp_backward(image, exposure, dL_dout, need_exposure_grad=True):
+    """gsr_exposure_clamp_backward: (dL_dimage [3,H,W], dL_dexposure [3,4] or None)."""
+    H, W = image.shape[1:]
+    dimg = torch.empty_like(image)
+    dexp = part = None
+    if exposure is not None and need_exposure_grad:
+        dexp = torch.zeros(3, 4, dtype=torch.float32, device=image.device)
+        part = torch.empty(int(lib().gsr_exposure_partials_bytes(H, W)) // 8, dtype=torch.float64, device=image.device)
+    _check(lib().gsr_exposure_clamp_backward(H, W, _ptr(image), _ptr(exposure), _ptr(dL_dout), _ptr(dimg), _ptr(dexp),
+                                             _ptr(part), _stream()))
+    return dimg, dexp
 
 
 # ---- optimizer stage (include/gsr_optim.h) --------------------------------------------------------------

@@ -61,6 +61,26 @@ int gsr_l1_ssim_loss_backward(int planes, int H, int W, float lambda_dssim, cons
                               const float* dm_dmu1, const float* dm_dsigma1_sq, const float* dm_dsigma12,
                               const float* upstream, float* dL_dimage, void* stream);
 
+/*
+ * Render epilogue of /root/reference/gaussian_renderer/__init__.py:112-119 (between the rasterizer and the loss):
+ *   if use_trained_exp:  y[c] = sum_k x[k] * exposure[k][c] + exposure[c][3]      (exposure: row-major [3,4])
+ *   y = clamp(y, 0, 1)
+ * on one [3,H,W] image, as ONE launch (the reference: permute, matmul, permute, add, clamp).  exposure == NULL skips
+ * the affine map (use_trained_exp false).  out is fully written.
+ */
+int gsr_exposure_clamp_forward(int H, int W, const float* image, const float* exposure, float* out, void* stream);
+
+/*
+ * Its backward: dL_dimage[k] = sum_c g[c] * exposure[k][c] with g[c] = dL_dout[c] where the unclamped value lies in
+ * [0, 1] (torch.clamp's gradient mask) and 0 elsewhere; dL_dexposure[k][c] = sum_pix x[k] g[c],
+ * dL_dexposure[c][3] = sum_pix g[c] (12 floats, row-major [3,4]; NULL when exposure is NULL or not trained).
+ * The pixel sums are reduced in a fixed order (per-CTA partials in `partials`, gsr_exposure_partials_bytes(H, W)
+ * bytes, then one CTA in double): deterministic.
+ */
+size_t gsr_exposure_partials_bytes(int H, int W);
+int gsr_exposure_clamp_backward(int H, int W, const float* image, const float* exposure, const float* dL_dout,
+                                float* dL_dimage, float* dL_dexposure, char* partials, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

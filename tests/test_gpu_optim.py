@@ -98,6 +98,41 @@ def test_gaussian_adam_on_flat_bucket_matches_six_group_torch_adam(cuda):
             assert not torch.equal(a[vis], b[vis])
 
 
+def test_untouched_and_decayed_rows(cuda):
+    """Zero and denormal moments are the common case (Gaussians no view has touched; moments decaying after a Gaussian
+    left every frustum).  The kernel's branch-free sqrt / division must agree with the oracle there and everywhere else:
+    compared elementwise on a state that mixes all the ranges."""
+    import torch
+    from gsr_b200 import capi
+    rng = np.random.default_rng(11)
+    n = 64 * 1024
+    p = rng.standard_normal((n, 1)).astype(np.float32)
+    g = (rng.standard_normal((n, 1)) * 10.0 ** rng.integers(-12, 3, (n, 1))).astype(np.float32)
+    m = (rng.standard_normal((n, 1)) * 10.0 ** rng.integers(-44, 1, (n, 1))).astype(np.float32)
+    v = (rng.random((n, 1)) * 10.0 ** rng.integers(-44, 4, (n, 1))).astype(np.float32)
+    kind = rng.integers(0, 4, (n, 1))
+    g[kind == 0] = 0.0                                      # not visible this step
+    m[kind == 1] = 0.0
+    v[kind == 1] = 0.0                                      # never touched
+    g[kind == 1] = 0.0
+    t = {k: torch.from_numpy(a.copy()).to(cuda) for k, a in dict(p=p, g=g, m=m, v=v).items()}
+    for step in (1, 2, 1000):
+        p0, m0, v0 = p.copy(), m.copy(), v.copy()
+        oo.adam_step(p, g, m, v, step, 0.01)
+        capi.adam_step([dict(param=t["p"], grad=t["g"], exp_avg=t["m"], exp_avg_sq=t["v"], lr=0.01)], step)
+        got = {k: t[k].cpu().numpy() for k in "pmv"}
+        assert all(np.isfinite(a).all() for a in got.values())
+        # elementwise: one fp32 rounding of the operands (the kernel fuses multiply-adds the oracle rounds twice)
+        g64 = g.astype(np.float64)
+        assert (np.abs(got["m"] - m) <= 1.2e-7 * (np.abs(m0) + np.abs(g)) + 2e-45).all(), step
+        assert (np.abs(got["v"] - v) <= 1.2e-7 * (v0 + g64 * g64) + 2e-45).all(), step
+        assert (np.abs(got["p"] - p) <= 2.4e-7 * np.abs(p0) + 1e-5 * np.abs(p - p0) + 1e-12).all(), step
+        untouched = (kind == 1)
+        assert np.array_equal(got["p"][untouched], p0[untouched])          # 0 / eps = 0: the parameter does not move
+        for k, a in (("p", p), ("m", m), ("v", v)):
+            t[k].copy_(torch.from_numpy(a))
+
+
 def test_unaligned_segments_take_the_scalar_path(cuda):
     import torch
     from gsr_b200 import capi

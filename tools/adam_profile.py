@@ -15,13 +15,26 @@ G = FlatGaussians(P, dev)
 G.params.normal_()
 G.bucket.normal_()
 opt = GaussianAdam(G)
+STATE = sys.argv[2] if len(sys.argv) > 2 else "random"   # random | zero (untouched rows: g = m = v = 0) | denormal (decayed m)
+if STATE == "zero":
+    G.bucket.zero_()
+elif STATE == "denormal":
+    G.bucket.zero_()
+    opt.exp_avg.fill_(1e-41)
+    opt.exp_avg_sq.fill_(1e-24)
+elif STATE == "half":                                      # 57 % of the rows never seen, the rest with gradients
+    opt.step(zero_grad=False)
+    rows = (torch.rand(P, device=dev) < 0.57).nonzero().squeeze(1)
+    for buf in (G.bucket, opt.exp_avg, opt.exp_avg_sq):
+        for name in ("xyz", "shs", "opacity", "scales", "rotations"):
+            G._view(buf, name)[rows] = 0
 vis = torch.rand(P, device=dev) < 0.43
 for mode in ("dense", "sparse"):
     ts = []
     for _ in range(6):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
-        opt.step(visible=vis if mode == "sparse" else None, zero_grad=True)
+        opt.step(visible=vis if mode == "sparse" else None, zero_grad=(STATE == "random"))
         b.record()
         torch.cuda.synchronize()
         ts.append(a.elapsed_time(b))
