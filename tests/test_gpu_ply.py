@@ -97,3 +97,40 @@ def test_fixture_renders_through_the_rasterizer(cuda):
     o = cases.run_oracle(scene, cam, dict(opts, mode="sh"), None)
     assert np.array_equal(st["radii"].cpu().numpy(), o["radii"])
     assert np.abs(st["out_color"].cpu().numpy() - o["out_color"])[:, ~o["borderline"]].max() <= 1e-5
+
+
+def test_real_scene_flow_ply_plus_colmap_camera(cuda, tmp_path):
+    """What a caller with a trained scene does: point_cloud.ply from disk (device unpack), cameras from the COLMAP
+    sparse model (gsr_b200/cameras.py), one render per camera through the C ABI, checked against the oracle rasterizer
+    fed by the oracle loader."""
+    import torch
+    import cases
+    from gsr_b200 import capi, ply, synth, cameras as cm
+    train, test, norm = cm.read_colmap_scene(os.path.join(GOLD, "colmap_tiny"), eval=True, llffhold=3)
+    infos = (train + test)[:3]
+    rng = np.random.default_rng(8)
+    sc = synth.trained_like_scene(3000, 8, s0=0.05)
+    path = str(tmp_path / "point_cloud.ply")
+    for k, info in enumerate(infos):
+        cam = cm.to_camera(info, resolution_scale=4.0)
+        assert (cam.image_width, cam.image_height) == (round(info.width / 4), round(info.height / 4))
+        # put the cloud 4 units in front of this camera: forward axis = third row of the w2c rotation
+        w2c = cam.world_view_transform.T
+        centre = cam.camera_center + 4.0 * w2c[2, :3]
+        xyz = (centre + 0.6 * rng.standard_normal((3000, 3))).astype(np.float32)
+        raw = {k2: torch.from_numpy(np.ascontiguousarray(v)) for k2, v in
+               dict(xyz=xyz, shs=sc["shs"], opacity=np.log(sc["opacities"] / (1 - sc["opacities"])).reshape(-1, 1),
+                    scaling=np.log(sc["scales"]), rotation=sc["rotations"]).items()}
+        ply.save_ply(path, *[raw[n].to(cuda) for n in ("xyz", "shs", "opacity", "scaling", "rotation")])
+        a = ply.load_ply_for_render(path, cuda)
+        w = po.activate(po.load_ply(open(path, "rb").read()))
+        t = lambda x: torch.from_numpy(np.ascontiguousarray(x)).to(cuda)
+        st = capi.forward(means3D=a["xyz"], opacities=a["opacity"], shs=a["shs"], scales=a["scales"], rotations=a["rotations"],
+                          viewmatrix=t(cam.world_view_transform), projmatrix=t(cam.full_proj_transform), cam_pos=t(cam.camera_center),
+                          background=t(np.zeros(3, np.float32)), width=cam.image_width, height=cam.image_height,
+                          tan_fovx=cam.tanfovx, tan_fovy=cam.tanfovy, sh_degree=3)
+        scene = dict(means3D=w["xyz"], shs=w["shs"], opacities=w["opacity"], scales=w["scales"], rotations=w["rotations"], sh_degree=3)
+        o = cases.run_oracle(scene, cam, dict(bg=(0.0, 0.0, 0.0), antialiasing=False, mode="sh"), None)
+        assert int((o["radii"] > 0).sum()) > 1000, "camera %d does not see the cloud" % k
+        assert np.array_equal(st["radii"].cpu().numpy(), o["radii"])
+        assert np.abs(st["out_color"].cpu().numpy() - o["out_color"])[:, ~o["borderline"]].max() <= 1e-5
