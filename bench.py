@@ -244,6 +244,39 @@ def loss_stage_report(dev, H, W, hbm_peak, reps=30):
     return rep
 
 
+def frame_stage_report(dev, H, W, hbm_peak, reps=30):
+    """Frame output after a forward-only render: [3,H,W] fp32 -> [H,W,3] u8, ours (one launch)
+    vs the reference's torch expressions (train.py:81 viewer bytes; torchvision save_image's quantisation, render.py:44)."""
+    import torch
+    from gsr_b200 import frames
+    img = torch.rand(3, H, W, device=dev) * 1.2 - 0.1
+    out8 = torch.empty(H, W, 3, dtype=torch.uint8, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def timed(fn):
+        for _ in range(3):
+            fn()
+        ts = []
+        for _ in range(reps):
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b))
+        return float(np.median(ts))
+
+    t_ours = timed(lambda: frames.to_rgb8(img, frames.TRUNCATE, out=out8))
+    t_gui = timed(lambda: (torch.clamp(img, min=0, max=1.0) * 255).byte().permute(1, 2, 0).contiguous())
+    t_png = timed(lambda: img.mul(255).add_(0.5).clamp_(0, 255).permute(1, 2, 0).to(torch.uint8).contiguous())
+    nbytes = 15 * H * W
+    return {"workload": "one [3,%d,%d] fp32 render -> [H,W,3] u8 frame" % (H, W), "ours_ms": t_ours, "gpu_launches": 1,
+            "reference_torch_viewer_bytes_ms": t_gui, "reference_torch_save_image_quantise_ms": t_png,
+            "roofline": {"bound": "hbm", "algorithmic_bytes": nbytes, "achieved": nbytes / t_ours / 1e6, "peak": hbm_peak,
+                         "unit": "GB/s", "frac": nbytes / t_ours / 1e6 / hbm_peak}}
+
+
 def optimizer_stage_report(G, radii, hbm_peak, reps=10):
     """Optimizer step after the backward: Adam over the 59 floats of every Gaussian.
     Rows: ours dense (one launch, gradient cleared in the same pass), ours sparse (rows of view 0's visible
@@ -641,6 +674,10 @@ def main():
             out["loss_stage"] = loss_stage_report(dev, H, W, hbm_peak)
             if not args.no_cpu_baseline:
                 out["loss_stage"]["cpu_baseline"] = loss_cpu_baseline(H, W)
+            try:
+                out["frame_stage"] = frame_stage_report(dev, H, W, hbm_peak)
+            except Exception as exc:  # informational leg only
+                out["frame_stage"] = {"error": str(exc)[:300]}
             try:
                 out["optimizer_stage"] = optimizer_stage_report(G, st["radii"], hbm_peak)
             except Exception as exc:  # informational leg only

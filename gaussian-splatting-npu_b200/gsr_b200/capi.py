@@ -77,7 +77,9 @@ EXPORTS = ["gsr_forward", "gsr_backward", "gsr_mark_visible", "gsr_geometry_byte
            # include/gsr_optim.h
            "gsr_adam_step", "gsr_densification_stats",
            # include/gsr_ply.h (bound in gsr_b200/ply.py)
-           "gsr_ply_parse_header", "gsr_ply_write_header", "gsr_ply_unpack", "gsr_ply_pack"]
+           "gsr_ply_parse_header", "gsr_ply_write_header", "gsr_ply_unpack", "gsr_ply_pack",
+           # include/gsr_frame.h (bound in gsr_b200/frames.py)
+           "gsr_frame_to_rgb8"]
 
 _lib = None
 
