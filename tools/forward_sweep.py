@@ -33,8 +33,8 @@ for k, m in enumerate(float(x) for x in args.sizes.split(",")):
     def fwd(c):
         return capi.forward(width=W, height=H, viewmatrix=c[0], projmatrix=c[1], cam_pos=c[2], tan_fovx=c[3], tan_fovy=c[4],
                             background=bg, sh_degree=3, want_invdepth=False, **g)
-    for c in cam_t[:5]:
-        fwd(c)
+    for c in cam_t[:400]:                  # >= 0.3 s of work: SM clocks ramp over the first few hundred ms
+        fwd(c)                             # (tools/forward_gap.py: 1.50 ms/view cold vs 0.67 warm at 1M)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     n_sum = 0
