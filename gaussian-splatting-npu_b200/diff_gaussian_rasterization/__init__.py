@@ -141,7 +141,14 @@ class GaussianRasterizer(nn.Module):
             return _C.mark_visible(positions, rs.viewmatrix, rs.projmatrix)
 
     def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None,
-                rotations=None, cov3D_precomp=None):
+                rotations=None, cov3D_precomp=None, dc=None):
+        # `dc` is what gaussian_renderer/__init__.py:90-100 passes on its separate_sh path (only taken when
+        # SparseGaussianAdam is importable from this package, i.e. under GSR_EXPORT_SPARSE_ADAM=1): the degree-0
+        # coefficients [P,1,3] apart from the rest [P,M-1,3]; the kernels read one [P,M,3] tensor
+        if dc is not None and shs is not None:
+            shs = torch.cat([dc, shs], dim=1)
+        elif dc is not None:
+            shs = dc
         have_sh, have_col = shs is not None, colors_precomp is not None
         if have_sh == have_col:
             raise Exception('Please provide excatly one of either SHs or precomputed colors!')
@@ -156,3 +163,12 @@ class GaussianRasterizer(nn.Module):
         return rasterize_gaussians(means3D, means2D, or_empty(shs), or_empty(colors_precomp),
                                    opacities, or_empty(scales), or_empty(rotations),
                                    or_empty(cov3D_precomp), self.raster_settings)
+
+
+# The reference's own rasterizer package does not export SparseGaussianAdam, which keeps train.py:37-41 on its
+# torch.optim.Adam / single-SH-tensor path.  Opt in to the sparse optimizer + separate_sh path:
+import os as _os
+
+if _os.environ.get("GSR_EXPORT_SPARSE_ADAM") == "1":
+    from gsr_b200.optim import SparseGaussianAdam  # noqa: E402,F401
+    __all__.append("SparseGaussianAdam")

@@ -47,3 +47,43 @@ class GaussianAdam:
 
     def zero_grad(self):
         self.flat.bucket.zero_()
+
+
+class SparseGaussianAdam(torch.optim.Adam):
+    """The optimizer interface the reference's training loop already knows:
+        self.optimizer = SparseGaussianAdam(l, lr=0.0, eps=1e-15)        /root/reference/scene/gaussian_model.py:194-198
+        gaussians.optimizer.step(visible, radii.shape[0])                /root/reference/train.py:179-181
+    A torch.optim.Adam subclass (so the densification code that edits `optimizer.state[param]["exp_avg"/"exp_avg_sq"]`
+    and `param_groups`, gaussian_model.py:316-392, works unchanged) whose step updates ONLY the rows of visible
+    Gaussians, all parameter groups in one launch (gsr_adam_step).  The update is torch.optim.Adam's (bias-corrected,
+    the reference's default optimizer) restricted to those rows; rows outside the mask keep parameter and moments bit
+    for bit.  Not exported from diff_gaussian_rasterization by default, exactly like the reference's own rasterizer
+    package (exporting it switches train.py to its separate_sh path); GSR_EXPORT_SPARSE_ADAM=1 opts in.  No CPU path."""
+
+    def __init__(self, params, lr, eps):
+        super().__init__(params=params, lr=lr, eps=eps)
+
+    @torch.no_grad()
+    def step(self, visibility, N):
+        by_step = {}
+        for group in self.param_groups:
+            assert len(group["params"]) == 1, "more than one tensor in group"
+            param = group["params"][0]
+            if param.grad is None:
+                continue
+            if not param.is_cuda:
+                raise RuntimeError("SparseGaussianAdam needs CUDA parameters: there is no CPU path")
+            state = self.state[param]
+            if "exp_avg" not in state:                       # lazy init, as torch.optim.Adam does
+                state["exp_avg"] = torch.zeros_like(param, memory_format=torch.preserve_format)
+                state["exp_avg_sq"] = torch.zeros_like(param, memory_format=torch.preserve_format)
+            step = int(state["step"]) + 1 if "step" in state else 1
+            state["step"] = torch.tensor(float(step))
+            assert param.shape[0] == N and param.is_contiguous() and param.grad.is_contiguous()
+            v2 = lambda t: t.view(N, -1)
+            seg = dict(param=v2(param.data), grad=v2(param.grad), exp_avg=v2(state["exp_avg"]),
+                       exp_avg_sq=v2(state["exp_avg_sq"]), lr=group["lr"])
+            by_step.setdefault((step, tuple(group["betas"]), group["eps"]), []).append(seg)
+        vis = visibility if visibility is None or visibility.dtype in (torch.bool, torch.uint8) else visibility != 0
+        for (step, betas, eps), segs in by_step.items():     # one launch unless groups have diverged step counts
+            capi.adam_step(segs, step, betas[0], betas[1], eps, visible=None if vis is None else vis.contiguous())

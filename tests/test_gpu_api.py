@@ -166,3 +166,30 @@ def test_accumulate_mode_sums_views(cuda, name):
         first = sep[0][0][k].cpu().numpy().reshape(P, -1)
         # atomic-order noise only enters through rows view 1 touched
         assert np.abs(got[~vis1] - first[~vis1]).max() / scale <= 1e-4, k
+
+
+def test_separate_sh_arguments_dc_plus_rest(cuda):
+    """gaussian_renderer/__init__.py:90-100 (separate_sh): rasterizer(dc=[P,1,3], shs=[P,15,3]) renders the same bits as
+    one [P,16,3] tensor and autograd splits dL_dsh between the two leaves."""
+    import torch
+    from diff_gaussian_rasterization import GaussianRasterizer
+    scene, cam, opts = cases.get_case("tiny64")
+    g0, g1 = cases.grads_for(cam)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(cuda).requires_grad_(True)
+    R = GaussianRasterizer(_settings(cam, opts, scene, cuda))
+    res = {}
+    for split in (False, True):
+        means3D, opac, sc, rot = t(scene["means3D"]), t(scene["opacities"]), t(scene["scales"]), t(scene["rotations"])
+        means2D = torch.zeros_like(means3D, requires_grad=True)
+        if split:
+            dc, rest = t(scene["shs"][:, :1]), t(scene["shs"][:, 1:])
+            color, radii, invd = R(means3D=means3D, means2D=means2D, dc=dc, shs=rest, colors_precomp=None, opacities=opac,
+                                   scales=sc, rotations=rot, cov3D_precomp=None)
+        else:
+            shs = t(scene["shs"])
+            color, radii, invd = R(means3D=means3D, means2D=means2D, shs=shs, opacities=opac, scales=sc, rotations=rot)
+        (color * torch.from_numpy(g0).to(cuda)).sum().backward()
+        res[split] = (color.detach(), radii, torch.cat([dc.grad, rest.grad], 1) if split else shs.grad, means3D.grad)
+    assert torch.equal(res[False][0], res[True][0]) and torch.equal(res[False][1], res[True][1])
+    for a, b in zip(res[False][2:], res[True][2:]):           # gradients: fp32 RED order differs from run to run
+        assert (a - b).abs().max().item() <= 1e-4 * a.abs().max().item()

@@ -133,6 +133,57 @@ def test_untouched_and_decayed_rows(cuda):
             t[k].copy_(torch.from_numpy(a))
 
 
+def test_sparse_gaussian_adam_interface(cuda):
+    """SparseGaussianAdam(l, lr=0.0, eps=1e-15).step(visible, N) as gaussian_model.py:194-198 / train.py:179-181 use it,
+    against torch.optim.Adam with the rows outside the mask restored after every step."""
+    import torch
+    from gsr_b200.optim import SparseGaussianAdam
+    N = 5003
+    gen = torch.Generator(device="cuda").manual_seed(5)
+    shapes = dict(xyz=(N, 3), f_dc=(N, 1, 3), f_rest=(N, 15, 3), opacity=(N, 1), scaling=(N, 3), rotation=(N, 4))
+    lrs = dict(xyz=1.6e-4, f_dc=2.5e-3, f_rest=1.25e-4, opacity=0.025, scaling=0.005, rotation=0.001)
+    ours = {k: torch.nn.Parameter(torch.randn(s, device=cuda, generator=gen)) for k, s in shapes.items()}
+    ref = {k: torch.nn.Parameter(v.detach().clone()) for k, v in ours.items()}
+    opt = SparseGaussianAdam([{"params": [ours[k]], "lr": lrs[k], "name": k} for k in ours], lr=0.0, eps=1e-15)
+    topt = torch.optim.Adam([{"params": [ref[k]], "lr": lrs[k], "name": k} for k in ref], lr=0.0, eps=1e-15)
+    assert isinstance(opt, torch.optim.Adam)
+    for step in range(4):
+        vis = torch.rand(N, device=cuda, generator=gen) < 0.4
+        for k in ours:
+            g = torch.randn(shapes[k], device=cuda, generator=gen)
+            ours[k].grad, ref[k].grad = g.clone(), g.clone()
+        before = {k: (ref[k].detach().clone(), topt.state[ref[k]].get("exp_avg", torch.zeros_like(ref[k])).clone(),
+                      topt.state[ref[k]].get("exp_avg_sq", torch.zeros_like(ref[k])).clone()) for k in ref}
+        mine = {k: (ours[k].detach().clone(), opt.state[ours[k]].get("exp_avg", torch.zeros_like(ours[k])).clone()) for k in ours}
+        opt.step(vis, N)
+        topt.step()
+        for k in ref:                                          # rows outside the mask: as if the step had not happened
+            st = topt.state[ref[k]]
+            ref[k].data[~vis] = before[k][0][~vis]
+            st["exp_avg"][~vis] = before[k][1][~vis]
+            st["exp_avg_sq"][~vis] = before[k][2][~vis]
+        for k in ours:
+            assert torch.equal(ours[k].detach()[~vis], mine[k][0][~vis]), (k, step)       # untouched bit for bit
+            assert torch.equal(opt.state[ours[k]]["exp_avg"][~vis], mine[k][1][~vis]), (k, step)
+            assert (ours[k].detach() - ref[k].detach()).abs().max().item() <= 1e-4 * lrs[k] + 2e-7 * ref[k].abs().max().item(), (k, step)
+            assert (opt.state[ours[k]]["exp_avg"] - topt.state[ref[k]]["exp_avg"]).abs().max().item() <= 1e-6 * 5, (k, step)
+            assert int(opt.state[ours[k]]["step"]) == step + 1
+    # the densification code replaces state tensors and parameters in place (gaussian_model.py:316-392): keep working
+    k = "opacity"
+    st = opt.state.pop(ours[k])
+    grown = torch.nn.Parameter(torch.cat([ours[k].detach(), torch.zeros(7, 1, device=cuda)]))
+    st["exp_avg"] = torch.cat([st["exp_avg"], torch.zeros(7, 1, device=cuda)])
+    st["exp_avg_sq"] = torch.cat([st["exp_avg_sq"], torch.zeros(7, 1, device=cuda)])
+    opt.param_groups[3]["params"][0] = grown
+    opt.state[grown] = st
+    grown.grad = torch.ones_like(grown)
+    for kk in ours:
+        if kk != k:
+            ours[kk].grad = None
+    opt.step(torch.ones(N + 7, dtype=torch.bool, device=cuda), N + 7)
+    assert int(opt.state[grown]["step"]) == 5 and bool((grown.detach()[-7:] < 0).all())
+
+
 def test_unaligned_segments_take_the_scalar_path(cuda):
     import torch
     from gsr_b200 import capi

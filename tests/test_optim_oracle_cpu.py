@@ -86,3 +86,15 @@ def test_densification_stats_match_reference_expressions():
     oo.densification_stats(g2, radii, accum, denom, maxr)
     assert np.allclose(accum, t_acc.numpy(), rtol=1e-6, atol=0)
     assert np.array_equal(denom, t_den.numpy()) and np.array_equal(maxr, t_max.numpy())
+
+
+def test_sparse_gaussian_adam_has_no_cpu_path():
+    import pytest
+    import torch
+    from gsr_b200.optim import SparseGaussianAdam
+    p = torch.nn.Parameter(torch.zeros(4, 3))
+    opt = SparseGaussianAdam([{"params": [p], "lr": 0.1, "name": "xyz"}], lr=0.0, eps=1e-15)
+    assert isinstance(opt, torch.optim.Adam)
+    p.grad = torch.ones_like(p)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        opt.step(torch.ones(4, dtype=torch.bool), 4)
