@@ -375,6 +375,8 @@ def main():
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true")
+    ap.add_argument("--streams", type=int, default=3,
+                    help="CUDA streams the views of a step are spread over (gsr_b200.dist.ViewStreams)")
     ap.add_argument("--views-per-rank", type=int, default=8,
                     help="views every rank renders per step (gradients accumulate in the bucket; one all-reduce per step)")
     args = ap.parse_args()
@@ -421,12 +423,14 @@ def main():
 
     grad_views = G.grad_views()     # the backward kernels write straight into the all-reduce bucket
 
+    from gsr_b200.dist import ViewStreams
+    view_streams = ViewStreams(dev, args.streams)
+
     def abi_step():
         # one step = this rank's V views: the first backward overwrites the bucket, the others add into it
-        for v in range(V):
-            st = capi.forward(width=W, height=H, **per_view[v])
-            g = capi.backward(st, dL_dcolor=dcol, dL_dinvdepth=ddep, out=grad_views, accumulate=(v > 0), **per_view[v])
-        return st, g
+        return view_streams.run(
+            V, lambda v: capi.forward(width=W, height=H, **per_view[v]),
+            lambda v, st, acc: capi.backward(st, dL_dcolor=dcol, dL_dinvdepth=ddep, out=grad_views, accumulate=acc, **per_view[v]))
 
     def barrier():
         if world > 1:
@@ -509,14 +513,16 @@ def main():
     target_host = [torch.from_numpy(rng9.random((3, H, W), dtype=np.float32)).pin_memory() for _ in range(min(V, 2))]
     cam_host = [torch.from_numpy(np.concatenate([c.world_view_transform.ravel(), c.full_proj_transform.ravel(),
                                                  c.camera_center.ravel()]).astype(np.float32)).pin_memory() for c in cams]
-    target_dev = [torch.empty(3, H, W, device=dev) for _ in range(2)]       # double-buffered: the copy of view v+1
-    cam_dev = [torch.empty(35, device=dev) for _ in range(2)]               # may run under view v's kernels
+    NB = max(2, args.streams)                                                # one input buffer per view in flight
+    target_dev = [torch.empty(3, H, W, device=dev) for _ in range(NB)]       # double-buffered: the copy of view v+1
+    cam_dev = [torch.empty(35, device=dev) for _ in range(NB)]              # may run under view v's kernels
     params = G.as_leaf_params()
     loss_host = torch.empty(1).pin_memory()
     loss_dev = torch.zeros(1, device=dev)
+    loss_slots = torch.zeros(V, 1, device=dev)              # one slot per view: views on different streams never share a word
     copy_stream = torch.cuda.Stream(device=dev)
-    uploaded = [torch.cuda.Event() for _ in range(2)]
-    buf_free = [torch.cuda.Event() for _ in range(2)]
+    uploaded = [torch.cuda.Event() for _ in range(NB)]
+    buf_free = [torch.cuda.Event() for _ in range(NB)]
     for e_ in buf_free:
         e_.record(torch.cuda.current_stream())
     sink = (grad_views["dL_dmeans3D"], grad_views["dL_dsh"], grad_views["dL_dopacity"], grad_views["dL_dscales"],
@@ -527,32 +533,50 @@ def main():
         and the target image come from pinned host memory, GaussianRasterizer renders, the training loss (0.8 L1 + 0.2 D-SSIM, fused) is taken and
         backpropagated; parameter gradients of the V views add up in the flat bucket (grad_sink), which is
         all-reduced over ranks; the step's loss is read back to the host."""
-        loss_dev.zero_()
         main = torch.cuda.current_stream()
 
-        def upload(v):      # H2D of view v's camera + target on the copy stream, into buffer v & 1
-            copy_stream.wait_event(buf_free[v & 1])          # the view that last used this buffer is done with it
+        def upload(v):      # H2D of view v's camera + target on the copy stream, into buffer v % NB
+            copy_stream.wait_event(buf_free[v % NB])          # the view that last used this buffer is done with it
             with torch.cuda.stream(copy_stream):
-                cam_dev[v & 1].copy_(cam_host[v], non_blocking=True)
-                target_dev[v & 1].copy_(target_host[v % len(target_host)], non_blocking=True)
-                uploaded[v & 1].record(copy_stream)
+                cam_dev[v % NB].copy_(cam_host[v], non_blocking=True)
+                target_dev[v % NB].copy_(target_host[v % len(target_host)], non_blocking=True)
+                uploaded[v % NB].record(copy_stream)
 
         upload(0)
+        streams = [main] + view_streams.side                 # view v runs on stream v % S (gsr_b200.dist.ViewStreams)
+        if len(streams) > 1:
+            start = torch.cuda.Event()
+            start.record(main)
+            for s_ in streams[1:]:
+                s_.wait_event(start)
+        first_done = None
         for v in range(V):
-            cd, td = cam_dev[v & 1], target_dev[v & 1]
-            main.wait_event(uploaded[v & 1])
+            cd, td = cam_dev[v % NB], target_dev[v % NB]
+            sv = streams[v % len(streams)]
+            sv.wait_event(uploaded[v % NB])
             if v + 1 < V:
                 upload(v + 1)                                 # travels while this view renders
-            rs = GaussianRasterizationSettings(viewmatrix=cd[0:16].view(4, 4), projmatrix=cd[16:32].view(4, 4),
-                                               campos=cd[32:35], tanfovx=cams[v].tanfovx, tanfovy=cams[v].tanfovy, **rs_kw)
-            means2D = torch.zeros_like(params["xyz"], requires_grad=True)
-            color, radii, invd = GaussianRasterizer(rs)(means3D=params["xyz"], means2D=means2D, opacities=params["opacity"],
-                                                        shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
-            loss = l1_ssim_loss(color, td, 0.2)               # train.py:118-126, two fused launches
-            with grad_sink(*sink, accumulate=(v > 0)):
-                loss.backward()
-            loss_dev.add_(loss.detach())
-            buf_free[v & 1].record(main)
+            with torch.cuda.stream(sv):
+                rs = GaussianRasterizationSettings(viewmatrix=cd[0:16].view(4, 4), projmatrix=cd[16:32].view(4, 4),
+                                                   campos=cd[32:35], tanfovx=cams[v].tanfovx, tanfovy=cams[v].tanfovy, **rs_kw)
+                means2D = torch.zeros_like(params["xyz"], requires_grad=True)
+                color, radii, invd = GaussianRasterizer(rs)(means3D=params["xyz"], means2D=means2D, opacities=params["opacity"],
+                                                            shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
+                loss = l1_ssim_loss(color, td, 0.2)           # train.py:118-126, two fused launches
+                if v > 0 and sv is not main and first_done is not None:
+                    sv.wait_event(first_done)                 # view 0's backward overwrites the bucket: add only after it
+                with grad_sink(*sink, accumulate=(v > 0)):
+                    loss.backward()
+                if v == 0 and len(streams) > 1:
+                    first_done = torch.cuda.Event()
+                    first_done.record(sv)
+                loss_slots[v].copy_(loss.detach().reshape(1))
+                buf_free[v % NB].record(sv)
+        for s_ in streams[1:]:
+            done = torch.cuda.Event()
+            done.record(s_)
+            main.wait_event(done)
+        loss_dev.copy_(loss_slots.sum().reshape(1))
         if world > 1:
             dist.all_reduce(G.bucket, op=dist.ReduceOp.SUM)
         loss_host.copy_(loss_dev, non_blocking=True)
@@ -564,8 +588,9 @@ def main():
     barrier()
     t0 = time.perf_counter()
     e0.record()
+    step_loss = None
     for _ in range(args.steps):
-        api_step()
+        step_loss = api_step()
     e1.record()
     barrier()
     wall = time.perf_counter() - t0
@@ -657,15 +682,16 @@ def main():
             "config": {"workload": args.workload + ": " + w["desc"], "P": P, "P_visible": P_vis, "num_rendered": N,
                        "width": W, "height": H, "pairs_evaluated_fwd": pairs_eval, "pairs_blended": pairs_blend,
                        "pairs_evaluated_bwd": pairs_bwd_eval, "l2": "inputs (708 MB of Gaussians + scratch) exceed the 126 MB L2",
-                       "views_per_rank_per_step": V, "global_views_per_step": V * world,
-                       "step": "each rank renders its %d views (fwd+bwd, parameter gradients accumulated in one flat bucket)%s" % (
-                           V, ", then ONE NCCL all-reduce of the 59 fp32/Gaussian bucket" if world > 1 else ""),
-                       "roofline_view": "stage times / roofline figures are of view 0 (single-view fwd+bwd, write mode)",
+                       "views_per_rank_per_step": V, "global_views_per_step": V * world, "streams": args.streams,
+                       "step": "each rank renders its %d views (fwd+bwd, parameter gradients accumulated in one flat bucket), view v on CUDA stream v %% %d%s" % (
+                           V, max(1, args.streams), ", then ONE NCCL all-reduce of the 59 fp32/Gaussian bucket" if world > 1 else ""),
+                       "roofline_view": "stage times / roofline figures are of view 0 alone on one stream (single-view fwd+bwd, write mode)",
                        "parallelism": "view-parallel dp%d, replicated Gaussians, NCCL all-reduce of 59 fp32/Gaussian" % world
                        if world > 1 else "single GPU", "peak_source": peak_src},
             "clocks": clocks,
             "e2e": {"value": e2e_val, "unit": "renders/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": e2e_ms / args.steps,
+                    "ms_per_step": e2e_ms / args.steps, "step_loss": step_loss,
+                    "bucket_checksum": float(G.bucket.double().abs().sum().item()),
                     "what": "per view: camera + target image from pinned host memory (copy stream, double-buffered, overlapping the previous view's kernels), GaussianRasterizer autograd fwd+bwd + the fused training loss 0.8*L1 + 0.2*(1-SSIM) (fused_ssim.l1_ssim_loss); per step: gradients of the rank's views summed in the bucket (grad_sink), all-reduce when N>1, loss read back"},
             "gpu_launches": launches_per_step * V * args.steps,
             "stage_ms": stage_ms, "roofline": roof, "roofline_stages": stages, "cpu_baseline": cpu,

@@ -91,6 +91,48 @@ class FlatGaussians:
                 params[name].grad.copy_(self._view(self.bucket, name).view(params[name].grad.shape))
 
 
+class ViewStreams:
+    """Renders the views of one step (forward + backward, gradients accumulated in one bucket) on several CUDA streams.
+
+    The views of a step are independent until their gradients meet in the bucket, so view v runs on stream v % S: the
+    short latency-bound stages of one view (scans, the sorts of ~1 M keys, the mid-forward count readback the host waits
+    for) execute under the blend kernels of its neighbour.  One host thread drives all streams; ordering is by events:
+      * side streams start after everything already queued on the caller's stream (previous step's all-reduce / Adam);
+      * view 0's backward OVERWRITES the bucket (no separate zero fill), so no other backward may start before it ends;
+        later backwards only add (RED), in any order;
+      * the caller's stream continues after the last kernel of every side stream.
+    """
+
+    def __init__(self, device, n_streams):
+        self.side = [torch.cuda.Stream(device=device) for _ in range(max(1, n_streams) - 1)]
+
+    def run(self, n_views, forward, backward):
+        """forward(v) -> state and backward(v, state, accumulate) -> grads are called under the view's stream."""
+        main = torch.cuda.current_stream()
+        streams = [main] + self.side
+        if self.side:
+            start = torch.cuda.Event()
+            start.record(main)
+            for s in self.side:
+                s.wait_event(start)
+        first_done, out = None, None
+        for v in range(n_views):
+            s = streams[v % len(streams)]
+            with torch.cuda.stream(s):
+                st = forward(v)
+                if v > 0 and s is not main and first_done is not None:
+                    s.wait_event(first_done)
+                out = (st, backward(v, st, v > 0))
+                if v == 0 and self.side:
+                    first_done = torch.cuda.Event()
+                    first_done.record(s)
+        for s in self.side:
+            done = torch.cuda.Event()
+            done.record(s)
+            main.wait_event(done)
+        return out
+
+
 class DensificationStats:
     """Densification statistics (scene/gaussian_model.py:471-473, train.py:166) for view-parallel
     steps.  Each rank accumulates this step's views into step-local deltas; `allreduce()` reduces the

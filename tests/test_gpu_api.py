@@ -193,3 +193,35 @@ def test_separate_sh_arguments_dc_plus_rest(cuda):
     assert torch.equal(res[False][0], res[True][0]) and torch.equal(res[False][1], res[True][1])
     for a, b in zip(res[False][2:], res[True][2:]):           # gradients: fp32 RED order differs from run to run
         assert (a - b).abs().max().item() <= 1e-4 * a.abs().max().item()
+
+
+@pytest.mark.parametrize("n_streams", [2, 3])
+def test_view_streams_match_single_stream(cuda, n_streams):
+    """gsr_b200.dist.ViewStreams: the views of a step spread over several CUDA streams give the same bucket as the
+    sequential loop (view 0 overwrites, the others add; only the order of the fp32 adds differs)."""
+    import torch
+    from gsr_b200 import capi
+    from gsr_b200.dist import ViewStreams
+    scene, cam, opts = cases.get_case("odd167x101")
+    grads = cases.grads_for(cam)
+    dcol = torch.from_numpy(grads[0]).cuda(); ddep = torch.from_numpy(grads[1]).cuda()
+    views = []
+    for k in range(5):
+        sc = dict(scene); sc["means3D"] = scene["means3D"] + np.array([0.2 * k - 0.4, 0.05 * k, 0.0], np.float32)
+        views.append(cases._to_dev(cases.inputs_of(sc, cam, opts)))
+    P, M = scene["means3D"].shape[0], scene["shs"].shape[1]
+    W, H = cam.image_width, cam.image_height
+
+    def run(S):
+        bucket = dict(dL_dmeans3D=torch.full((P, 3), 7.0, device=cuda), dL_dsh=torch.full((P, M, 3), 7.0, device=cuda),
+                      dL_dopacity=torch.full((P, 1), 7.0, device=cuda), dL_dscales=torch.full((P, 3), 7.0, device=cuda),
+                      dL_drotations=torch.full((P, 4), 7.0, device=cuda))
+        vs = ViewStreams(cuda, S)
+        for _ in range(3):                                   # repeated steps reuse the streams
+            vs.run(len(views), lambda v: capi.forward(width=W, height=H, **views[v]),
+                   lambda v, st, acc: capi.backward(st, dL_dcolor=dcol, dL_dinvdepth=ddep, out=bucket, accumulate=acc, **views[v]))
+        torch.cuda.synchronize()
+        return {k: b.double().cpu().numpy() for k, b in bucket.items()}
+    want, got = run(1), run(n_streams)
+    for k in want:
+        assert np.abs(got[k] - want[k]).max() <= 1e-4 * (np.abs(want[k]).max() + 1e-30), k
