@@ -178,6 +178,31 @@ class _Buf:
         self.cb = ALLOC_FN(cb)
 
 
+class _GrowBuf(_Buf):
+    """A scratch tensor that only grows (25 % headroom): a request that fits is served without touching the allocator."""
+
+    def __init__(self, device):
+        super().__init__(device)
+
+        def cb(nbytes, _user):
+            if self.t.numel() < nbytes:
+                self.t = torch.empty(0, dtype=torch.uint8, device=self.device)     # release before growing
+                self.t = torch.empty(int(nbytes) + int(nbytes) // 4, dtype=torch.uint8, device=self.device)
+            return self.t.data_ptr()
+        self.cb = ALLOC_FN(cb)
+
+
+class Workspace:
+    """Reusable scratch of gsr_forward (geometry / binning / image buffers) for callers that keep ONE forward state alive
+    at a time per workspace (a forward-only render loop, or forward immediately followed by its backward).  The binning
+    buffer's size follows the number of (Gaussian, tile) pairs of the view; sizing it per call makes the caching
+    allocator split, merge and occasionally cudaMalloc -- a growth-only buffer takes that out of the loop.  The state
+    returned by forward(workspace=ws) aliases these tensors: it is valid until the next forward with the same ws."""
+
+    def __init__(self, device):
+        self.geom, self.binning, self.img = _GrowBuf(device), _GrowBuf(device), _GrowBuf(device)
+
+
 STAGES = ["preprocess", "scan", "duplicate", "sort", "ranges", "render_fwd", "render_bwd",
           "preprocess_bwd", "host_sync", "depth_sort"]
 
@@ -194,8 +219,9 @@ def set_profiling(on):
 def forward(*, means3D, opacities, viewmatrix, projmatrix, cam_pos, background, width, height,
             tan_fovx, tan_fovy, shs=None, colors_precomp=None, scales=None, rotations=None,
             cov3D_precomp=None, sh_degree=3, scale_modifier=1.0, prefiltered=False,
-            antialiasing=False, debug=False, want_invdepth=True):
-    """gsr_forward on torch CUDA tensors.  Returns a state dict holding outputs + scratch buffers."""
+            antialiasing=False, debug=False, want_invdepth=True, workspace=None):
+    """gsr_forward on torch CUDA tensors.  Returns a state dict holding outputs + scratch buffers (fresh per call, or
+    the caller's `workspace`)."""
     L = lib()
     dev = means3D.device
     P = means3D.shape[0]
@@ -207,7 +233,10 @@ def forward(*, means3D, opacities, viewmatrix, projmatrix, cam_pos, background, 
                     _ptr(colors_precomp), _ptr(opacities), _ptr(scales), scale_modifier, _ptr(rotations),
                     _ptr(cov3D_precomp), _ptr(viewmatrix), _ptr(projmatrix), _ptr(cam_pos), tan_fovx, tan_fovy,
                     int(prefiltered), int(antialiasing), int(debug), _ptr(out_color), _ptr(out_invdepth), _ptr(radii))
-    geom, binning, img = _Buf(dev), _Buf(dev), _Buf(dev)
+    if workspace is not None:
+        geom, binning, img = workspace.geom, workspace.binning, workspace.img
+    else:
+        geom, binning, img = _Buf(dev), _Buf(dev), _Buf(dev)
     n = c_int(0)
     with torch.cuda.device(dev):
         _check(L.gsr_forward(ctypes.byref(a), geom.cb, None, binning.cb, None, img.cb, None, _stream(), ctypes.byref(n)))

@@ -225,3 +225,26 @@ def test_view_streams_match_single_stream(cuda, n_streams):
     want, got = run(1), run(n_streams)
     for k in want:
         assert np.abs(got[k] - want[k]).max() <= 1e-4 * (np.abs(want[k]).max() + 1e-30), k
+
+
+def test_workspace_reuse_gives_the_same_render(cuda):
+    """capi.Workspace: growth-only scratch reused across forwards (big view, then a small one, then the big one again)
+    renders the same bits as per-call scratch, and backward works from the aliased state."""
+    import torch
+    from gsr_b200 import capi
+    ws = capi.Workspace(cuda)
+    grads = None
+    for name in ("odd167x101", "tiny64", "odd167x101"):
+        scene, cam, opts = cases.get_case(name)
+        kw = cases._to_dev(cases.inputs_of(scene, cam, opts))
+        a = capi.forward(width=cam.image_width, height=cam.image_height, **kw)
+        b = capi.forward(width=cam.image_width, height=cam.image_height, workspace=ws, **kw)
+        assert a["num_rendered"] == b["num_rendered"]
+        assert torch.equal(a["out_color"], b["out_color"]) and torch.equal(a["radii"], b["radii"])
+        g = cases.grads_for(cam)
+        dcol, ddep = torch.from_numpy(g[0]).cuda(), torch.from_numpy(g[1]).cuda()
+        ga = capi.backward(a, dL_dcolor=dcol, dL_dinvdepth=ddep, **kw)
+        gb = capi.backward(b, dL_dcolor=dcol, dL_dinvdepth=ddep, **kw)
+        for k in ("dL_dmeans3D", "dL_dsh", "dL_dopacity"):
+            assert (ga[k] - gb[k]).abs().max().item() <= 1e-4 * (ga[k].abs().max().item() + 1e-30), (name, k)
+    assert ws.binning.t.numel() > 0
