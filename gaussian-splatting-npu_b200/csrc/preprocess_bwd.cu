@@ -108,6 +108,25 @@ preprocess_bwd_kernel(BwdParams p, GeomView g) {
     const bool in = i < p.P;
     const bool vis = in && p.radii[i] > 0;
 
+    // The SH rows of the warp's visible Gaussians start travelling NOW (cp.async straight into the swizzled staging
+    // rows, no registers held): the kernel is latency-bound, and this fetch used to start only after the covariance
+    // math below, as a third dependent round trip to HBM (radii -> per-Gaussian inputs -> SH rows).
+    unsigned vmask = 0;
+    if (SH16 && p.shs) {
+        vmask = __ballot_sync(0xffffffffu, vis);
+        if (vmask && p.D > 0) {                   // degree 0 needs no coefficients
+            const float4* src = reinterpret_cast<const float4*>(p.shs) + ((size_t)blockIdx.x * PB_THREADS + (size_t)warp * 32) * 12;
+            const uint32_t st0 = smem_addr(stage + warp * 384);
+#pragma unroll
+            for (int it = 0; it < 12; it++) {
+                const int f = it * 32 + lane;
+                const int row = f / 12, j = f - row * 12;
+                if ((vmask >> row) & 1u) cp_async16(st0 + 16u * (uint32_t)(row * 12 + (j ^ ((row >> 1) & 3))), src + f);
+            }
+        }
+        cp_async_commit();
+    }
+
     float dmx = 0, dmy = 0, dmz = 0;
     float dcov[6] = { 0, 0, 0, 0, 0, 0 };
     float mx = 0, my = 0, mz = 0, dop_out = 0;
@@ -214,23 +233,14 @@ preprocess_bwd_kernel(BwdParams p, GeomView g) {
     // ---------------- SH backward (backward.cu:23-142) ----------------
     if (p.shs) {
         if (SH16) {
-            const unsigned vmask = __ballot_sync(0xffffffffu, vis);
             float4* st = stage + warp * 384;
             const size_t warp_first = (size_t)blockIdx.x * PB_THREADS + (size_t)warp * 32;
             float w[16], d[3] = { 0.0f, 0.0f, 0.0f };
 #pragma unroll
             for (int k = 0; k < 16; k++) w[k] = 0.0f;
+            cp_async_wait_all();                  // the rows requested at the top of the kernel
+            __syncwarp();
             if (vmask) {
-                const float4* src = reinterpret_cast<const float4*>(p.shs) + warp_first * 12;
-                if (p.D > 0) {                    // degree 0 needs no coefficients
-#pragma unroll
-                    for (int it = 0; it < 12; it++) {
-                        const int f = it * 32 + lane;
-                        const int row = f / 12, j = f - row * 12;
-                        if ((vmask >> row) & 1u) st[row * 12 + (j ^ ((row >> 1) & 3))] = ldg_stream_f4(src + f);
-                    }
-                    __syncwarp();
-                }
                 if (vis) {
                     const StageRow E = { reinterpret_cast<const float*>(st + lane * 12), (lane >> 1) & 3 };
                     const float dr = p.dL_dcolor[3 * (size_t)i], dg = p.dL_dcolor[3 * (size_t)i + 1], db = p.dL_dcolor[3 * (size_t)i + 2];
