@@ -484,6 +484,19 @@ def main():
     value = world * V * args.steps / (ms / 1000.0)
     N = st["num_rendered"]
 
+    # ---------------- single-view latency: view 0 alone, one stream, write mode (BASELINE configs[1]) ----------------
+    sv_ms = []
+    for _ in range(12):
+        a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        a_.record()
+        st = capi.forward(width=W, height=H, **per_view[0])
+        capi.backward(st, dL_dcolor=dcol, dL_dinvdepth=ddep, out=grad_views, **per_view[0])
+        b_.record()
+        torch.cuda.synchronize()
+        sv_ms.append(a_.elapsed_time(b_))
+    single_view_ms = float(np.median(sv_ms[2:]))
+
     # ---------------- per-stage device times (profiling mode, separate pass) ----------------
     capi.set_profiling(True)
     stage = {}
@@ -694,6 +707,8 @@ def main():
                     "bucket_checksum": float(G.bucket.double().abs().sum().item()),
                     "what": "per view: camera + target image from pinned host memory (copy stream, double-buffered, overlapping the previous view's kernels), GaussianRasterizer autograd fwd+bwd + the fused training loss 0.8*L1 + 0.2*(1-SSIM) (fused_ssim.l1_ssim_loss); per step: gradients of the rank's views summed in the bucket (grad_sink), all-reduce when N>1, loss read back"},
             "gpu_launches": launches_per_step * V * args.steps,
+            "single_view": {"fwd_bwd_ms": single_view_ms, "renders_per_s": 1000.0 / single_view_ms,
+                            "what": "one view alone on one stream, forward + backward through the C ABI, inputs resident (latency; `value` is the throughput of the 8-view step)"},
             "stage_ms": stage_ms, "roofline": roof, "roofline_stages": stages, "cpu_baseline": cpu,
         }
         if world == 1:
