@@ -425,11 +425,15 @@ def main():
 
     from gsr_b200.dist import ViewStreams
     view_streams = ViewStreams(dev, args.streams)
+    # one growth-only scratch set per stream (a view's backward follows its forward on the same stream, so one live
+    # state per stream): the binning buffer's size changes with every view, and per-call sizing lets the caching
+    # allocator split / merge / occasionally cudaMalloc inside the timed region
+    spaces = [capi.Workspace(dev) for _ in range(max(1, args.streams))]
 
     def abi_step():
         # one step = this rank's V views: the first backward overwrites the bucket, the others add into it
         return view_streams.run(
-            V, lambda v: capi.forward(width=W, height=H, **per_view[v]),
+            V, lambda v: capi.forward(width=W, height=H, workspace=spaces[v % len(spaces)], **per_view[v]),
             lambda v, st, acc: capi.backward(st, dL_dcolor=dcol, dL_dinvdepth=ddep, out=grad_views, accumulate=acc, **per_view[v]))
 
     def barrier():
