@@ -240,3 +240,68 @@ def to_camera(info, trans=(0.0, 0.0, 0.0), scale=1.0, resolution_scale=1.0):
     divides the image size as loadCam does (utils/camera_utils.py: round(orig / scale))."""
     W, H = round(info.width / resolution_scale), round(info.height / resolution_scale)
     return Camera(world_to_view(info.R, info.T, np.asarray(trans), scale), W, H, info.FovX, info.FovY)
+
+
+# ---- COLMAP points3D and the initial point cloud (scene/colmap_loader.py:83-154, dataset_readers.py:120-143) ----
+def read_points3D_binary(path):
+    """-> (xyz [N,3] f64, rgb [N,3] f64, error [N,1] f64); the 2D tracks are skipped by their byte count."""
+    buf = open(path, "rb").read()
+    (n,), off = struct.unpack_from("<Q", buf, 0), 8
+    xyz, rgb, err = np.empty((n, 3)), np.empty((n, 3)), np.empty((n, 1))
+    for k in range(n):
+        rec = struct.unpack_from("<QdddBBBdQ", buf, off)
+        xyz[k], rgb[k], err[k] = rec[1:4], rec[4:7], rec[7]
+        off += 51 + 8 * rec[8]
+    if off > len(buf):
+        raise ValueError("%s: truncated" % path)
+    return xyz, rgb, err
+
+
+def read_points3D_text(path):
+    rows = [line.split() for line in _data_lines(path) if line]
+    xyz = np.array([[float(v) for v in e[1:4]] for e in rows]).reshape(-1, 3)
+    rgb = np.array([[int(v) for v in e[4:7]] for e in rows], dtype=np.float64).reshape(-1, 3)
+    err = np.array([[float(e[7])] for e in rows]).reshape(-1, 1)
+    return xyz, rgb, err
+
+
+_PCD_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4"), ("nx", "<f4"), ("ny", "<f4"), ("nz", "<f4"),
+                       ("red", "u1"), ("green", "u1"), ("blue", "u1")])
+
+
+def store_ply(path, xyz, rgb):
+    """storePly (dataset_readers.py:128-143): points3D.ply with float xyz + zero normals + uchar colours."""
+    el = np.zeros(len(xyz), _PCD_DTYPE)
+    for k, name in enumerate("xyz"):
+        el[name] = np.asarray(xyz)[:, k]
+    for k, name in enumerate(("red", "green", "blue")):
+        el[name] = np.asarray(rgb)[:, k]
+    head = "ply\nformat binary_little_endian 1.0\nelement vertex %d\n" % len(el)
+    head += "".join("property %s %s\n" % ("float" if _PCD_DTYPE[n].kind == "f" else "uchar", n) for n in _PCD_DTYPE.names)
+    with open(path, "wb") as f:
+        f.write((head + "end_header\n").encode("ascii") + el.tobytes())
+
+
+def fetch_ply(path):
+    """fetchPly (dataset_readers.py:120-126): (points [N,3] f32, colors [N,3] in 0..1, normals [N,3] f32).  Properties
+    are looked up by name; float / uchar / double / int properties of any order are accepted."""
+    buf = open(path, "rb").read()
+    end = buf.index(b"end_header\n") + len(b"end_header\n")
+    lines = buf[:end].decode("ascii").split("\n")
+    if lines[0].strip() != "ply" or not any(l.startswith("format binary_little_endian") for l in lines):
+        raise ValueError("%s: not a binary little-endian PLY" % path)
+    np_of = dict(float="<f4", float32="<f4", double="<f8", float64="<f8", uchar="u1", uint8="u1", char="i1", int8="i1",
+                 short="<i2", int16="<i2", ushort="<u2", uint16="<u2", int="<i4", int32="<i4", uint="<u4", uint32="<u4")
+    n, fields, in_vertex = 0, [], False
+    for l in lines:
+        t = l.split()
+        if t[:1] == ["element"]:
+            in_vertex = t[1] == "vertex"
+            n = int(t[2]) if in_vertex else n
+        elif t[:1] == ["property"] and in_vertex:
+            if t[1] == "list":
+                raise ValueError("%s: list property inside the vertex element" % path)
+            fields.append((t[2], np_of[t[1]]))
+    v = np.frombuffer(buf, np.dtype(fields), count=n, offset=end)
+    cols = lambda names: np.vstack([v[k] for k in names]).T
+    return cols("xyz"), cols(("red", "green", "blue")) / 255.0, cols(("nx", "ny", "nz"))

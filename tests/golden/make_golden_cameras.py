@@ -79,6 +79,30 @@ def write_colmap(d, cams, images, text):
                 f.write(struct.pack("<ddq", x, y, p))
 
 
+def write_points3d(d, pts, text):
+    if text:
+        with open(os.path.join(d, "points3D.txt"), "w") as f:
+            f.write("# 3D point list with one line of data per point:\n#   POINT3D_ID, X, Y, Z, R, G, B, ERROR, TRACK[] as (IMAGE_ID, POINT2D_IDX)\n")
+            for pid, (xyz, rgb, err, track) in pts.items():
+                f.write("%d %s %d %d %d %r %s\n" % (pid, " ".join(repr(float(v)) for v in xyz), *rgb, float(err),
+                                                    " ".join("%d %d" % t for t in track)))
+        return
+    with open(os.path.join(d, "points3D.bin"), "wb") as f:
+        f.write(struct.pack("<Q", len(pts)))
+        for pid, (xyz, rgb, err, track) in pts.items():
+            f.write(struct.pack("<QdddBBBdQ", pid, *xyz, *rgb, err, len(track)))
+            for t in track:
+                f.write(struct.pack("<ii", *t))
+
+
+def tiny_points(rng):
+    pts = {}
+    for pid in (3, 1, 20, 7, 8):
+        track = [(int(rng.integers(1, 13)), int(rng.integers(0, 5))) for _ in range(int(rng.integers(0, 4)))]
+        pts[pid] = (rng.standard_normal(3) * 2, tuple(int(v) for v in rng.integers(0, 256, 3)), float(rng.random()), track)
+    return pts
+
+
 def tiny_model(rng, models):
     cams = {}
     for k, model in enumerate(models):
@@ -121,6 +145,9 @@ if __name__ == "__main__":
         cams, images = tiny_model(rng, models)
         d = os.path.join(HERE, sub, "sparse/0")
         write_colmap(d, cams, images, text)
+        write_points3d(d, tiny_points(np.random.default_rng(77)), text)
+        pr = cl.read_points3D_text(os.path.join(d, "points3D.txt")) if text else cl.read_points3D_binary(os.path.join(d, "points3D.bin"))
+        out[sub + "_p3d_xyz"], out[sub + "_p3d_rgb"], out[sub + "_p3d_err"] = pr
         if text:
             extr, intr = cl.read_extrinsics_text(os.path.join(d, "images.txt")), cl.read_intrinsics_text(os.path.join(d, "cameras.txt"))
         else:

@@ -103,3 +103,42 @@ def test_image_size_from_png_header(tmp_path):
     (tmp_path / "bad.png").write_bytes(b"not a png at all, really not")
     with pytest.raises(ValueError, match="not a PNG"):
         cm.png_size(str(tmp_path / "bad.png"))
+
+
+@pytest.mark.parametrize("sub", ["colmap_tiny", "colmap_tiny_txt"])
+def test_points3d_vs_reference(gold, sub):
+    d = os.path.join(GOLD, sub, "sparse/0")
+    xyz, rgb, err = cm.read_points3D_text(os.path.join(d, "points3D.txt")) if sub.endswith("txt") else \
+        cm.read_points3D_binary(os.path.join(d, "points3D.bin"))
+    assert np.array_equal(xyz, gold[sub + "_p3d_xyz"]) and np.array_equal(rgb, gold[sub + "_p3d_rgb"])
+    assert np.array_equal(err, gold[sub + "_p3d_err"])
+
+
+def test_point_cloud_ply_round_trip_and_foreign_layout(tmp_path):
+    rng = np.random.default_rng(6)
+    xyz, rgb = rng.standard_normal((11, 3)), rng.integers(0, 256, (11, 3))
+    p = str(tmp_path / "points3D.ply")
+    cm.store_ply(p, xyz, rgb)
+    raw = open(p, "rb").read()
+    head = raw[:raw.index(b"end_header\n")].decode()
+    # the header storePly's structured dtype produces (dataset_readers.py:130-132): 6 floats then 3 uchars, 27 B/record
+    assert head.split("\n")[:3] == ["ply", "format binary_little_endian 1.0", "element vertex 11"]
+    assert [l.split()[1:] for l in head.split("\n")[3:] if l] == [["float", n] for n in ("x", "y", "z", "nx", "ny", "nz")] + \
+        [["uchar", n] for n in ("red", "green", "blue")]
+    assert len(raw) == len(head) + len("end_header\n") + 11 * 27
+    pts, col, nrm = cm.fetch_ply(p)
+    assert np.array_equal(pts, xyz.astype(np.float32)) and np.array_equal(col, rgb / 255.0) and not nrm.any()
+    # another tool's layout: colours first, doubles for the position, an extra property
+    dt = np.dtype([("red", "u1"), ("green", "u1"), ("blue", "u1"), ("x", "<f8"), ("y", "<f8"), ("z", "<f8"),
+                   ("nx", "<f4"), ("ny", "<f4"), ("nz", "<f4"), ("confidence", "<i4")])
+    el = np.zeros(4, dt)
+    el["x"], el["green"], el["nz"] = [1, 2, 3, 4], [10, 20, 30, 40], 1.0
+    hdr = "ply\nformat binary_little_endian 1.0\nelement vertex 4\n" + "".join(
+        "property %s %s\n" % ({"u1": "uchar", "<f8": "double", "<f4": "float", "<i4": "int"}[dt[n].str.replace("|", "")], n) for n in dt.names)
+    q = str(tmp_path / "other.ply")
+    open(q, "wb").write((hdr + "element face 0\nproperty list uchar int vertex_indices\nend_header\n").encode() + el.tobytes())
+    pts, col, nrm = cm.fetch_ply(q)
+    assert np.array_equal(pts[:, 0], [1, 2, 3, 4]) and np.allclose(col[:, 1], np.array([10, 20, 30, 40]) / 255.0) and (nrm[:, 2] == 1).all()
+    open(q, "wb").write(b"ply\nformat ascii 1.0\nend_header\n")
+    with pytest.raises(ValueError, match="binary little-endian"):
+        cm.fetch_ply(q)
