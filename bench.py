@@ -42,6 +42,8 @@ WORKLOADS = {
                desc="Mip-NeRF360-shape: 3M SH3 Gaussians, single view 1920x1080"),
     "c3": dict(P=1_800_000, W=979, H=546, seed=3003, s0=0.006, kind="trained", aa=False, extent=1.5,
                desc="T&T-shape: 1.8M SH3 Gaussians, 979x546"),
+    "c5": dict(P=10_000_000, W=1920, H=1080, seed=5009, s0=0.004, kind="trained", aa=False,
+               desc="forward sweep, largest size: 10M SH3 Gaussians, 1920x1080"),
     "c4": dict(P=6_000_000, W=3840, H=2160, seed=4004, s0=0.004, kind="trained", aa=True,
                desc="6M SH3 Gaussians at 3840x2160, antialiasing + inverse depth"),
 }

@@ -283,7 +283,9 @@ preprocess_bwd_kernel(BwdParams p, GeomView g) {
 #pragma unroll
                 for (int k = 0; k < 16; k++)
                     if (k < p.M) {
-                        if (ACC) { drow[3 * k] += w[k] * d[0]; drow[3 * k + 1] += w[k] * d[1]; drow[3 * k + 2] += w[k] * d[2]; }
+                        // atomic like every other accumulated output: the views of a step may run their
+                        // accumulate-mode backwards concurrently on different streams (dist.ViewStreams)
+                        if (ACC) { atomicAdd(drow + 3 * k, w[k] * d[0]); atomicAdd(drow + 3 * k + 1, w[k] * d[1]); atomicAdd(drow + 3 * k + 2, w[k] * d[2]); }
                         else { drow[3 * k] = w[k] * d[0]; drow[3 * k + 1] = w[k] * d[1]; drow[3 * k + 2] = w[k] * d[2]; }
                     }
             } else if (!ACC) {

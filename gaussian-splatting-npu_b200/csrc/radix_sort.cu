@@ -268,11 +268,8 @@ void sort_pairs_pingpong_t(KeyT* keys_a, uint32_t* vals_a, KeyT* keys_b, uint32_
     int hist_blocks = (int)min((size_t)148 * 8, (n_max + (size_t)HIST_THREADS * HIST_KPT - 1) / ((size_t)HIST_THREADS * HIST_KPT));
     sort_hist_kernel<KeyT><<<hist_blocks, HIST_THREADS, 0, s>>>(keys_a, n_max, n_dev, passes, end_bit, ghist);
 
-    static bool attr_set = false;      // per instantiation
-    if (!attr_set) {
-        cudaFuncSetAttribute(onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(OnesweepSmem<KeyT>));
-        attr_set = true;
-    }
+    // the attribute is per device / context (several devices may be driven from one process): set it on every call
+    cudaFuncSetAttribute(onesweep_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(OnesweepSmem<KeyT>));
     KeyT* kin = keys_a; uint32_t* vin = vals_a; KeyT* kout = keys_b; uint32_t* vout = vals_b;
     for (int p = 0; p < passes; p++) {
         const int shift = p * RADIX_BITS;

@@ -1,7 +1,7 @@
 """fused_ssim -- drop-in for the reference's fused-ssim package, on the sm_100a kernels of libgsr_b200.so.
 
-Mirrors /root/reference/submodules/fused-ssim/fused_ssim/__init__.py:1-41 (same names, arguments,
-padding modes and autograd structure): `fused_ssim(img1, img2, padding="same", train=True)`,
+Same public surface as /root/reference/submodules/fused-ssim/fused_ssim/__init__.py:1-41 (names, arguments,
+padding modes, autograd slots -- the API a caller binds to), bodies restated: `fused_ssim(img1, img2, padding="same", train=True)`,
 `FusedSSIMMap`, `allowed_padding`; the extension module keeps the reference's name `fused_ssim_cuda`
 (`fusedssim`, `fusedssim_backward`).  train.py:24-28,121-122 uses it unchanged.
 
@@ -20,43 +20,42 @@ except ImportError as e:  # pragma: no cover
                       "`python gaussian-splatting-npu_b200/build.py`; there is no fallback path") from e
 
 allowed_padding = ["same", "valid"]
+_BORDER = 5          # half of the 11-tap window: what padding="valid" crops on every side
+_SSIM_C1, _SSIM_C2 = 0.01 ** 2, 0.03 ** 2
+
+
+def _crop(t):
+    return t[:, :, _BORDER:-_BORDER, _BORDER:-_BORDER]
 
 
 class FusedSSIMMap(torch.autograd.Function):
+    """Autograd node over the two extension entry points.  Its signature -- apply(C1, C2, img1, img2, padding, train)
+    returning the SSIM map, six backward slots with the gradient in the third -- is the reference's
+    (fused_ssim/__init__.py:8-31) because callers may use the class directly; the body is restated here."""
+
     @staticmethod
     def forward(ctx, C1, C2, img1, img2, padding="same", train=True):
-        ssim_map, dm_dmu1, dm_dsigma1_sq, dm_dsigma12 = fusedssim(C1, C2, img1, img2, train)
-
-        if padding == "valid":
-            ssim_map = ssim_map[:, :, 5:-5, 5:-5]
-
-        ctx.save_for_backward(img1.detach(), img2, dm_dmu1, dm_dsigma1_sq, dm_dsigma12)
-        ctx.C1 = C1
-        ctx.C2 = C2
-        ctx.padding = padding
-
-        return ssim_map
+        full_map, d_mu1, d_sigma1_sq, d_sigma12 = fusedssim(C1, C2, img1, img2, train)
+        ctx.consts = (C1, C2, padding)
+        ctx.save_for_backward(img1.detach(), img2, d_mu1, d_sigma1_sq, d_sigma12)
+        return _crop(full_map) if padding == "valid" else full_map
 
     @staticmethod
-    def backward(ctx, opt_grad):
-        img1, img2, dm_dmu1, dm_dsigma1_sq, dm_dsigma12 = ctx.saved_tensors
-        C1, C2, padding = ctx.C1, ctx.C2, ctx.padding
-        dL_dmap = opt_grad
-        if padding == "valid":
-            dL_dmap = torch.zeros_like(img1)
-            dL_dmap[:, :, 5:-5, 5:-5] = opt_grad
-        grad = fusedssim_backward(C1, C2, img1, img2, dL_dmap, dm_dmu1, dm_dsigma1_sq, dm_dsigma12)
-        return None, None, grad, None, None, None
+    def backward(ctx, grad_map):
+        C1, C2, padding = ctx.consts
+        img1, img2, d_mu1, d_sigma1_sq, d_sigma12 = ctx.saved_tensors
+        if padding == "valid":          # the kernel wants a full-size upstream map: zero outside the cropped window
+            full = torch.zeros_like(img1)
+            _crop(full).copy_(grad_map)
+            grad_map = full
+        d_img1 = fusedssim_backward(C1, C2, img1, img2, grad_map, d_mu1, d_sigma1_sq, d_sigma12)
+        return (None, None, d_img1, None, None, None)
 
 
 def fused_ssim(img1, img2, padding="same", train=True):
-    C1 = 0.01 ** 2
-    C2 = 0.03 ** 2
-
+    """Mean SSIM of two [B,CH,H,W] images (reference signature, fused_ssim/__init__.py:33-41)."""
     assert padding in allowed_padding
-
-    map = FusedSSIMMap.apply(C1, C2, img1, img2, padding, train)
-    return map.mean()
+    return FusedSSIMMap.apply(_SSIM_C1, _SSIM_C2, img1, img2, padding, train).mean()
 
 
 class _L1SSIMLoss(torch.autograd.Function):

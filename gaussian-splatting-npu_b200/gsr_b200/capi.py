@@ -280,7 +280,8 @@ def backward(state, *, dL_dcolor, dL_dinvdepth=None, means3D, opacities, viewmat
 def mark_visible(means3D, viewmatrix, projmatrix):
     P = means3D.shape[0]
     out = torch.zeros(P, dtype=torch.bool, device=means3D.device)
-    _check(lib().gsr_mark_visible(P, _ptr(means3D), _ptr(viewmatrix), _ptr(projmatrix), c_void_p(out.data_ptr()), _stream()))
+    with torch.cuda.device(means3D.device):
+        _check(lib().gsr_mark_visible(P, _ptr(means3D), _ptr(viewmatrix), _ptr(projmatrix), c_void_p(out.data_ptr()), _stream()))
     return out
 
 
@@ -321,8 +322,9 @@ def introspect(state):
         o["point_list"] = _view(state["binning"], bl.point_list, N, torch.int32)
         # the reference's 64-bit sorted keys, rebuilt on demand (the hot path never materialises them)
         keys = torch.empty(N, dtype=torch.int64, device=state["geom"].device)
-        _check(L.gsr_materialize_keys(P, N, W, H, c_void_p(state["geom"].data_ptr()), c_void_p(state["binning"].data_ptr()),
-                                      c_void_p(keys.data_ptr()), _stream()))
+        with torch.cuda.device(keys.device):
+            _check(L.gsr_materialize_keys(P, N, W, H, c_void_p(state["geom"].data_ptr()), c_void_p(state["binning"].data_ptr()),
+                                          c_void_p(keys.data_ptr()), _stream()))
         o["keys"] = keys
     else:
         o["tile_keys"] = torch.empty(0, dtype=torch.int32, device=state["geom"].device)
@@ -340,8 +342,9 @@ def sort_pairs(keys, values, end_bit):
     n = keys.numel()
     ko, vo = torch.empty_like(keys), torch.empty_like(values)
     temp = torch.empty(int(L.gsr_sort_temp_bytes(n)), dtype=torch.uint8, device=keys.device)
-    _check(L.gsr_sort_pairs(_ptr(keys) if n else None, _ptr(values) if n else None, c_void_p(ko.data_ptr()) if n else None,
-                            c_void_p(vo.data_ptr()) if n else None, n, end_bit, c_void_p(temp.data_ptr()), _stream()))
+    with torch.cuda.device(keys.device):
+        _check(L.gsr_sort_pairs(_ptr(keys) if n else None, _ptr(values) if n else None, c_void_p(ko.data_ptr()) if n else None,
+                                c_void_p(vo.data_ptr()) if n else None, n, end_bit, c_void_p(temp.data_ptr()), _stream()))
     return ko, vo
 
 
@@ -360,15 +363,17 @@ def ssim_forward(img1, img2, train=True, C1=SSIM_C1, C2=SSIM_C2):
     planes, H, W = _planes(img1)
     m = torch.empty_like(img1)
     d = [torch.empty_like(img1) for _ in range(3)] if train else [None] * 3
-    _check(lib().gsr_ssim_forward(planes, H, W, C1, C2, _ptr(img1), _ptr(img2), _ptr(m), *[_ptr(x) for x in d], _stream()))
+    with torch.cuda.device(img1.device):
+        _check(lib().gsr_ssim_forward(planes, H, W, C1, C2, _ptr(img1), _ptr(img2), _ptr(m), *[_ptr(x) for x in d], _stream()))
     return m, d[0], d[1], d[2]
 
 
 def ssim_backward(img1, img2, dL_dmap, dm_dmu1, dm_dsigma1_sq, dm_dsigma12):
     planes, H, W = _planes(img1)
     g = torch.empty_like(img1)
-    _check(lib().gsr_ssim_backward(planes, H, W, _ptr(img1), _ptr(img2), _ptr(dL_dmap), _ptr(dm_dmu1), _ptr(dm_dsigma1_sq),
-                                   _ptr(dm_dsigma12), _ptr(g), _stream()))
+    with torch.cuda.device(img1.device):
+        _check(lib().gsr_ssim_backward(planes, H, W, _ptr(img1), _ptr(img2), _ptr(dL_dmap), _ptr(dm_dmu1), _ptr(dm_dsigma1_sq),
+                                       _ptr(dm_dsigma12), _ptr(g), _stream()))
     return g
 
 
@@ -389,16 +394,18 @@ def l1_ssim_loss_forward(image, gt, lambda_dssim, scratch, train=True, C1=SSIM_C
     """gsr_l1_ssim_loss_forward: fills scratch.loss = (loss, mean L1, mean ssim) and the derivative maps."""
     planes, H, W = _planes(image)
     d = scratch.dm if train else [None] * 3
-    _check(lib().gsr_l1_ssim_loss_forward(planes, H, W, C1, C2, lambda_dssim, _ptr(image), _ptr(gt), _ptr(scratch.loss),
-                                          *[_ptr(x) for x in d], _ptr(scratch.partials), _stream()))
+    with torch.cuda.device(image.device):
+        _check(lib().gsr_l1_ssim_loss_forward(planes, H, W, C1, C2, lambda_dssim, _ptr(image), _ptr(gt), _ptr(scratch.loss),
+                                              *[_ptr(x) for x in d], _ptr(scratch.partials), _stream()))
     return scratch.loss
 
 
 def l1_ssim_loss_backward(image, gt, lambda_dssim, scratch, upstream=None):
     """gsr_l1_ssim_loss_backward into scratch.dL_dimage (upstream: device scalar tensor or None = 1)."""
     planes, H, W = _planes(image)
-    _check(lib().gsr_l1_ssim_loss_backward(planes, H, W, lambda_dssim, _ptr(image), _ptr(gt), *[_ptr(x) for x in scratch.dm],
-                                           _ptr(upstream), _ptr(scratch.dL_dimage), _stream()))
+    with torch.cuda.device(image.device):
+        _check(lib().gsr_l1_ssim_loss_backward(planes, H, W, lambda_dssim, _ptr(image), _ptr(gt), *[_ptr(x) for x in scratch.dm],
+                                               _ptr(upstream), _ptr(scratch.dL_dimage), _stream()))
     return scratch.dL_dimage
 
 
@@ -409,7 +416,8 @@ def exposure_clamp_forward(image, exposure=None):
     if exposure is not None:
         assert exposure.dtype == torch.float32 and tuple(exposure.shape) == (3, 4)
     out = torch.empty_like(image)
-    _check(lib().gsr_exposure_clamp_forward(image.shape[1], image.shape[2], _ptr(image), _ptr(exposure), _ptr(out), _stream()))
+    with torch.cuda.device(image.device):
+        _check(lib().gsr_exposure_clamp_forward(image.shape[1], image.shape[2], _ptr(image), _ptr(exposure), _ptr(out), _stream()))
     return out
 
 
@@ -421,8 +429,9 @@ def exposure_clamp_backward(image, exposure, dL_dout, need_exposure_grad=True):
     if exposure is not None and need_exposure_grad:
         dexp = torch.zeros(3, 4, dtype=torch.float32, device=image.device)
         part = torch.empty(int(lib().gsr_exposure_partials_bytes(H, W)) // 8, dtype=torch.float64, device=image.device)
-    _check(lib().gsr_exposure_clamp_backward(H, W, _ptr(image), _ptr(exposure), _ptr(dL_dout), _ptr(dimg), _ptr(dexp),
-                                             _ptr(part), _stream()))
+    with torch.cuda.device(image.device):
+        _check(lib().gsr_exposure_clamp_backward(H, W, _ptr(image), _ptr(exposure), _ptr(dL_dout), _ptr(dimg), _ptr(dexp),
+                                                 _ptr(part), _stream()))
     return dimg, dexp
 
 
@@ -448,12 +457,14 @@ def adam_step(segments, step, beta1=0.9, beta2=0.999, eps=1e-15, visible=None, z
     if visible is not None:
         assert visible.is_cuda and visible.is_contiguous() and visible.dtype in (torch.bool, torch.uint8)
         vis = c_void_p(visible.data_ptr())
-    _check(lib().gsr_adam_step(arr, len(segments), int(step), beta1, beta2, eps, vis, int(zero_grad), _stream()))
+    with torch.cuda.device(segments[0]["param"].device):
+        _check(lib().gsr_adam_step(arr, len(segments), int(step), beta1, beta2, eps, vis, int(zero_grad), _stream()))
 
 
 def densification_stats(grad_means2D, radii, xyz_gradient_accum, denom, max_radii2D):
     """gsr_densification_stats (train.py:166-167, gaussian_model.py:471-473), in place."""
     P = radii.shape[0]
     assert grad_means2D.shape == (P, 3) and grad_means2D.is_contiguous() and radii.dtype == torch.int32
-    _check(lib().gsr_densification_stats(P, _ptr(grad_means2D), _ptr(radii), _ptr(xyz_gradient_accum), _ptr(denom),
-                                         _ptr(max_radii2D), _stream()))
+    with torch.cuda.device(radii.device):
+        _check(lib().gsr_densification_stats(P, _ptr(grad_means2D), _ptr(radii), _ptr(xyz_gradient_accum), _ptr(denom),
+                                             _ptr(max_radii2D), _stream()))

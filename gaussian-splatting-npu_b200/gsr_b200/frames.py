@@ -43,7 +43,8 @@ def to_rgb8(image, mode=TRUNCATE, x_begin=0, x_end=None, out=None):
         out = torch.empty(H, max(x_end - x_begin, 0), 3, dtype=torch.uint8, device=image.device)
     else:
         assert out.is_cuda and out.dtype == torch.uint8 and out.is_contiguous() and out.numel() == H * max(x_end - x_begin, 0) * 3
-    capi._check(_lib().gsr_frame_to_rgb8(H, W, x_begin, x_end, mode, capi._ptr(image), capi._ptr(out), capi._stream()))
+    with torch.cuda.device(image.device):
+        capi._check(_lib().gsr_frame_to_rgb8(H, W, x_begin, x_end, mode, capi._ptr(image), capi._ptr(out), capi._stream()))
     return out
 
 

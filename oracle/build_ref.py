@@ -93,6 +93,46 @@ def load_fused_ssim():
     return mod
 
 
+
+
+# ---- the reference's Python callers of the path (acceptance run) -----------------------
+# north_star: "gaussian_renderer/__init__.py and train.py use it unchanged".  The `-m gpu` acceptance test
+# (tests/test_gpu_reference_callers.py) runs those files AS THEY ARE on this package.  /root/reference does not
+# exist on the GPU box, so -- exactly like the compiled reference above -- the files are staged, byte for byte,
+# into oracle/_ref/callers/ (git-ignored: never part of the repo's history; travels with the gpurun snapshot).
+CALLERS_SRC = "/root/reference"
+CALLERS_OUT = os.path.join(OUT_DIR, "callers")
+CALLER_FILES = ["train.py", "render.py", "gaussian_renderer/__init__.py", "gaussian_renderer/network_gui.py",
+                "scene/__init__.py", "scene/cameras.py", "scene/colmap_loader.py", "scene/dataset_readers.py",
+                "scene/gaussian_model.py", "arguments/__init__.py", "utils/camera_utils.py", "utils/general_utils.py",
+                "utils/graphics_utils.py", "utils/image_utils.py", "utils/loss_utils.py", "utils/sh_utils.py",
+                "utils/system_utils.py"]
+
+
+def callers_available():
+    return os.path.exists(os.path.join(CALLERS_SRC, "train.py"))
+
+
+def callers_dir():
+    """Where the unmodified caller files can be imported from: the reference tree itself when present, else the staged
+    copy; None when neither exists."""
+    if callers_available():
+        return CALLERS_SRC
+    return CALLERS_OUT if os.path.exists(os.path.join(CALLERS_OUT, "train.py")) else None
+
+
+def stage_callers():
+    if not callers_available():
+        return CALLERS_OUT if os.path.isdir(CALLERS_OUT) else None
+    import shutil
+    for rel in CALLER_FILES:
+        dst = os.path.join(CALLERS_OUT, rel)
+        os.makedirs(os.path.dirname(dst), exist_ok=True)
+        shutil.copyfile(os.path.join(CALLERS_SRC, rel), dst)
+    return CALLERS_OUT
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv))
     print(build_fused_ssim(force="--force" in sys.argv))
+    print(stage_callers())

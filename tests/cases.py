@@ -78,6 +78,38 @@ def get_case(name):
         return synth.random_init_scene(100_000, 1001), _lego_cam(3), dict(o, bg=(1.0, 1.0, 1.0))
     if name == "mid640x360":
         return synth.trained_like_scene(400_000, 640, s0=0.008), synth.orbit_cameras(4, 640, 360, 640)[2], o
+    # ---- arguments of the boundary that round 1 left untested ----
+    if name in ("scale_half", "scale_two"):      # the viewer path passes scaling_modifier (train.py:79-80)
+        sc = synth.trained_like_scene(20_000, 41, s0=0.03)
+        return sc, synth.orbit_cameras(2, 144, 80, 41)[1], dict(o, scale_modifier=0.5 if name == "scale_half" else 2.0)
+    if name == "deg2":                           # active degree 2, M = 16 rows (training between iterations 2000-3000)
+        sc = synth.trained_like_scene(20_000, 22, s0=0.03, sh_degree=2)
+        return sc, synth.orbit_cameras(2, 128, 72, 22)[0], o
+    if name in ("m1", "m4", "m9"):               # narrower SH tensors: the non-SH16 branches of preprocess fwd / bwd
+        M = int(name[1:])
+        D = {1: 0, 4: 1, 9: 2}[M]
+        sc = synth.trained_like_scene(20_000, 50 + M, s0=0.03, sh_degree=D)
+        sc["shs"] = np.ascontiguousarray(sc["shs"][:, :M])
+        return sc, synth.orbit_cameras(2, 136, 88, 50 + M)[1], dict(o, bg=(0.2, 0.4, 0.1))
+    if name in ("quat_small", "quat_big"):       # forward.cu:123 uses the quaternion un-normalised
+        sc = synth.trained_like_scene(20_000, 61, s0=0.03)
+        sc["rotations"] = (sc["rotations"] * (0.3 if name == "quat_small" else 3.0)).astype(np.float32)
+        if name == "quat_big":
+            sc["scales"] = (sc["scales"] * 0.2).astype(np.float32)      # |q|^2 = 9 stretches the covariance ~ 81x
+        return sc, synth.orbit_cameras(2, 144, 80, 61)[0], o
+    if name == "deep_list":
+        # >= 2000 blended contributors per pixel: large, faint Gaussians (alpha just above 1/255, so T stays above
+        # 1e-4 for thousands of layers) stacked along the view axis -- the longest T-recovery chain of the backward
+        # blend (backward.cu:573 divides, render_bwd.cu multiplies by an approximate reciprocal)
+        rng = np.random.default_rng(77)
+        P = 3000
+        sc = dict(means3D=np.stack([rng.normal(0, 0.02, P), rng.normal(0, 0.02, P), rng.uniform(-1.0, 1.0, P)], 1).astype(np.float32),
+                  scales=np.full((P, 3), 8.0, np.float32) * np.exp(rng.normal(0, 0.05, (P, 3))).astype(np.float32),
+                  rotations=np.tile(np.array([[1.0, 0, 0, 0]], np.float32), (P, 1)),
+                  opacities=rng.uniform(0.00420, 0.00445, (P, 1)).astype(np.float32),
+                  shs=rng.normal(0, 0.5, (P, 16, 3)).astype(np.float32), sh_degree=3)
+        cam = synth.Camera(synth.look_at_w2c([0.0, -0.001, -4.0], [0.0, 0.0, 0.0], up=(0.0, -1.0, 0.0)), 48, 32, 0.5)
+        return sc, cam, dict(o, bg=(0.5, 0.5, 0.5))
     if name == "empty_view":     # camera looks away: every Gaussian culled, num_rendered = 0
         sc = synth.trained_like_scene(2_000, 99, s0=0.05)
         sc["means3D"] = (sc["means3D"] * 0.05).astype(np.float32)
@@ -87,6 +119,7 @@ def get_case(name):
 
 
 SMALL_CASES = ["one", "two", "tiny64", "odd167x101", "aa160x96", "deg1", "deg0", "colors", "cov3d", "empty_view"]
+ARG_CASES = ["scale_half", "scale_two", "deg2", "m1", "m4", "m9", "quat_small", "quat_big", "deep_list"]
 MEDIUM_CASES = ["lego800", "lego800_white", "mid640x360"]
 GOLDEN_CASES = ["two", "tiny64", "odd167x101", "aa160x96", "colors", "cov3d"]
 
@@ -109,6 +142,8 @@ def inputs_of(scene, cam, opts):
               projmatrix=cam.full_proj_transform, cam_pos=cam.camera_center,
               background=np.array(opts["bg"], np.float32), tan_fovx=cam.tanfovx, tan_fovy=cam.tanfovy,
               sh_degree=scene["sh_degree"], antialiasing=opts["antialiasing"])
+    if opts.get("scale_modifier", 1.0) != 1.0:
+        kw["scale_modifier"] = float(opts["scale_modifier"])
     if opts["mode"] == "colors":
         kw["colors_precomp"] = scene["colors_precomp"]
     else:
@@ -234,7 +269,8 @@ BITEXACT_FLOAT_KEYS = ["depths", "means2D", "conic_opacity"]
 
 
 def compare(a, b, borderline=None, grad_rtol=1e-4):
-    """Mismatch report between two result dicts (a = under test, b = reference)."""
+    """Mismatch report between two result dicts (a = under test, b = reference).  grad_rtol: one tolerance, or a
+    dict per gradient key (the elementwise `_viol` count uses it)."""
     rep = {}
     rep["num_rendered"] = (a["num_rendered"], b["num_rendered"])
     for k in INT_KEYS:
@@ -271,6 +307,8 @@ def compare(a, b, borderline=None, grad_rtol=1e-4):
                 continue
             rep[k + "_relmax"] = float(np.abs(x - y).max() / scale)
             # elementwise: |dx| <= rtol*|y| + 0.1*rtol*max|y|   (GRAD_RTOL = 1e-4, north_star)
-            tol = grad_rtol * np.abs(y) + 0.1 * grad_rtol * scale
+            rt = grad_rtol.get(k, 1e-4) if isinstance(grad_rtol, dict) else grad_rtol
+            tol = rt * np.abs(y) + 0.1 * rt * scale
             rep[k + "_viol"] = int((np.abs(x - y) > tol).sum())
+            rep[k + "_size"] = int(x.size)
     return rep

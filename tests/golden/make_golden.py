@@ -1,7 +1,7 @@
 """Generates the golden vectors in tests/golden/*.npz by running the UNMODIFIED reference CUDA
 rasterizer (oracle/_ref, built from /root/reference by oracle/build_ref.py) on a B200.
 
-    gpurun -- 'python tests/golden/make_golden.py gpurun_out/golden'     # then copy *.npz here
+    gpurun -- 'python tests/golden/make_golden.py gpurun_out/golden [case ...]'     # then copy *.npz here
 
 Each file holds, for one seeded case of tests/cases.py, the reference's outputs: every integer
 artefact in full (radii, tiles_touched, offsets, sorted keys, point list, tile ranges, n_contrib),
@@ -19,10 +19,10 @@ sys.path.insert(0, os.path.dirname(HERE))
 import cases  # noqa: E402
 
 
-def main(out_dir):
+def main(out_dir, names=None):
     os.makedirs(out_dir, exist_ok=True)
     import torch
-    for name in cases.GOLDEN_CASES:
+    for name in (names or cases.GOLDEN_CASES):
         scene, cam, opts = cases.get_case(name)
         grads = cases.grads_for(cam)
         r = cases.run_ref(scene, cam, opts, grads)
@@ -47,4 +47,4 @@ def main(out_dir):
 
 
 if __name__ == "__main__":
-    main(sys.argv[1] if len(sys.argv) > 1 else os.path.join(HERE))
+    main(sys.argv[1] if len(sys.argv) > 1 else os.path.join(HERE), sys.argv[2:])

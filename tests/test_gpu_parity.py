@@ -15,6 +15,13 @@ from test_oracle_golden import GRAD_TOL, GOLD
 
 pytestmark = pytest.mark.gpu
 
+# worst measured gradient error per (comparison, case, tensor), written by test_zz_worst_errors_report
+WORST = {}
+
+
+def _record(kind, name, rep):
+    WORST.setdefault(kind, {})[name] = {k: rep[k] for k in rep if k.endswith("_relmax") or k.endswith("_viol") or k.endswith("_absmax")}
+
 
 def _assert_parity(rep, against_ref, name):
     assert rep["num_rendered"][0] == rep["num_rendered"][1]
@@ -31,21 +38,32 @@ def _assert_parity(rep, against_ref, name):
     for k in cases.BWD_KEYS:
         if k + "_relmax" in rep:
             assert rep[k + "_relmax"] <= GRAD_TOL[k], (name, k, rep[k + "_relmax"])
+        # elementwise bar: |dx| <= tol |y| + 0.1 tol max|y| for every entry, not just the worst relative to the max
+        if k + "_viol" in rep and k + "_relmax" in rep:
+            assert rep[k + "_viol"] <= VIOL_FRAC * rep[k + "_size"], (name, k, rep[k + "_viol"], rep[k + "_size"])
 
 
-@pytest.mark.parametrize("name", cases.SMALL_CASES + cases.MEDIUM_CASES)
+# fraction of a gradient tensor's entries allowed outside the elementwise bound (fp32 atomics in a different order)
+VIOL_FRAC = 0.0
+
+
+@pytest.mark.parametrize("name", cases.SMALL_CASES + cases.ARG_CASES + cases.MEDIUM_CASES)
 def test_cuda_vs_oracle(cuda, name):
     scene, cam, opts = cases.get_case(name)
     grads = cases.grads_for(cam)
     o = cases.run_oracle(scene, cam, opts, grads)
     c = cases.run_cuda(scene, cam, opts, grads)
-    rep = cases.compare(c, o, o["borderline"])
+    rep = cases.compare(c, o, o["borderline"], GRAD_TOL)
+    _record("cuda_vs_oracle", name, rep)
     _assert_parity(rep, False, name)
     assert rep.get("n_contrib_borderline_mismatch", 0) <= max(3, int(o["borderline"].sum()))
-    assert o["borderline"].mean() < 1e-3
+    # deep_list: every pixel ends on the T < 1e-4 termination test after ~2100 layers, a few land on the threshold
+    assert o["borderline"].mean() < (5e-3 if name == "deep_list" else 1e-3)
+    if name == "deep_list":
+        assert int(o["n_contrib"].min()) >= 2000, "the case must keep >= 2000 layers per pixel"
 
 
-@pytest.mark.parametrize("name", cases.SMALL_CASES + cases.MEDIUM_CASES)
+@pytest.mark.parametrize("name", cases.SMALL_CASES + cases.ARG_CASES + cases.MEDIUM_CASES)
 def test_cuda_vs_reference_cuda(cuda, name):
     from oracle import ref_cuda
     if not ref_cuda.available():
@@ -54,11 +72,12 @@ def test_cuda_vs_reference_cuda(cuda, name):
     grads = cases.grads_for(cam)
     r = cases.run_ref(scene, cam, opts, grads)
     c = cases.run_cuda(scene, cam, opts, grads)
-    rep = cases.compare(c, r, None)
+    rep = cases.compare(c, r, None, GRAD_TOL)
     # gradients: both sides are fp32 with different summation orders; judge each against the oracle's scale
     for k in cases.BWD_KEYS:
         if k + "_relmax" in rep and np.abs(r[k]).max() < 1e-6 * max(1.0, float(np.abs(r["dL_dmeans3D"]).max())):
             rep.pop(k + "_relmax")      # analytically-zero gradient (identity rotations): noise vs noise
+    _record("cuda_vs_reference_cuda", name, rep)
     _assert_parity(rep, True, name)
 
 
@@ -150,7 +169,8 @@ def test_full_size_vs_reference_cuda(cuda, workload):
     grads = cases.grads_for(cam)
     r = cases.run_ref(scene, cam, opts, grads)
     c = cases.run_cuda(scene, cam, opts, grads)
-    rep = cases.compare(c, r, None)
+    rep = cases.compare(c, r, None, GRAD_TOL)
+    _record("full_size_vs_reference_cuda", workload, rep)
     assert rep["num_rendered"][0] > 1_000_000
     # north_star: gradients <= 1e-4 "given atomic-order nondeterminism".  At 6M Gaussians a handful of ill-conditioned
     # rows (dL_dconic ~ 1e6 cancelling in the conic -> covariance chain) make the REFERENCE's fp32 atomics differ from
@@ -166,5 +186,34 @@ def test_full_size_vs_reference_cuda(cuda, workload):
             e_ours = np.abs(np.asarray(c[k], np.float64).reshape(tr.shape) - tr).max() / s_
             e_ref = np.abs(np.asarray(r[k], np.float64).reshape(tr.shape) - tr).max() / s_
             assert e_ours <= max(GRAD_TOL[k], e_ref), (workload, k, e_ours, e_ref)
+            WORST["full_size_vs_reference_cuda"][workload][k + "_arbitrated"] = {"ours_vs_oracle": e_ours, "reference_vs_oracle": e_ref}
             rep.pop(k + "_relmax")
     _assert_parity(rep, True, workload)
+
+
+def test_c5_10m_forward_vs_reference_cuda(cuda):
+    """BASELINE configs[4] at its largest size: 10M Gaussians, 1920x1080, forward only, against the unmodified reference
+    CUDA rasterizer: every integer artefact bit-exact, the image to the last bits."""
+    from oracle import ref_cuda
+    if not ref_cuda.available():
+        pytest.skip("oracle/_ref/libref_rasterizer.so not built (needs /root/reference at build time)")
+    import bench
+    w, scene, cam = bench.make_workload("c5")
+    assert scene["means3D"].shape[0] == 10_000_000
+    opts = dict(bg=(0.0, 0.0, 0.0), antialiasing=False, mode="sh")
+    r = cases.run_ref(scene, cam, opts, None)
+    c = cases.run_cuda(scene, cam, opts, None)
+    rep = cases.compare(c, r, None)
+    assert rep["num_rendered"][0] > 5_000_000
+    _assert_parity(rep, True, "c5")
+
+
+def test_zz_worst_errors_report():
+    """Writes the worst measured gradient errors of this session (no assertion of its own): the 1e-3 rows of GRAD_TOL
+    carry a measured number in the log and in gpurun_out/parity_worst.json."""
+    import json
+    print(json.dumps(WORST, indent=1, default=str))
+    out_dir = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    if os.path.isdir(out_dir) and WORST:
+        with open(os.path.join(out_dir, "parity_worst.json"), "w") as f:
+            json.dump(WORST, f, indent=1, default=str)
