@@ -13,6 +13,7 @@
 #include "../../include/gsr.h"
 #include "../../include/gsr_optim.h"
 #include "gsr_common.cuh"
+#include "adam_math.cuh"      // sqrt_rn_nobranch / div_rn_nobranch / adam_update: shared with exchange.cu
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -40,47 +41,13 @@ struct AdamSeg {
 struct AdamTable {
     AdamSeg seg[GSR_ADAM_MAX_SEGMENTS];
     int n_segs;
-    float one_minus_b1, b2, one_minus_b2, bc2_sqrt, eps;
+    AdamConsts c;
     const unsigned char* visible;
     int zero_grad;
 };
 
-// torch's CUDA kernels for the same ops (fp32 opmath, -fmad=true):
-//   exp_avg.lerp_(grad, 1-beta1)                    m + w (g - m)            (weight < 0.5 branch)
-//   exp_avg_sq.mul_(beta2).addcmul_(g, g, 1-beta2)  (v beta2) + ((1-beta2) g) g
-//   denom = sqrt(v) / sqrt(1-beta2^t) + eps ;  p.addcdiv_(m, denom, -lr/(1-beta1^t))
-//
-// sqrt.rn / div.rn compile to a fast path (MUFU seed + FMA refinement, correctly rounded) guarded by a range check
-// that CALLs a slow subroutine for zero / denormal operands.  Exactly those are the common case here: a Gaussian no
-// view has touched yet has g = m = v = 0, and the moments of one that left every frustum decay into the denormals --
-// measured 1.64 ms instead of 1.02 ms for the C2 step with 57 % untouched rows.  The two helpers below are the same
-// fast-path instruction sequences (read off the SASS) made valid over the whole range this kernel sees, without the
-// branch: bit-identical to sqrtf / __fdiv_rn wherever those stay on their fast path.
-__device__ __forceinline__ float sqrt_rn_nobranch(float v) {           // v >= 0, finite
-    const bool tiny = v < 0x1p-60f;                                     // below 2^-101 the seed loses accuracy:
-    const float vs = tiny ? v * 0x1p64f : v;                            // an exact even-power scaling keeps the rounding
-    float r;
-    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(vs));
-    float s = vs * r;
-    const float h = 0.5f * r;
-    s = fmaf(fmaf(-s, s, vs), h, s);
-    s = tiny ? s * 0x1p-32f : s;
-    return v == 0.0f ? 0.0f : s;                                        // rsqrt(0) = inf
-}
-
-__device__ __forceinline__ float div_rn_nobranch(float a, float b) {   // b in [1e-15, 1e30]; a anything incl. 0 / denormal
-    float r;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(b));
-    r = fmaf(r, fmaf(r, -b, 1.0f), r);
-    const float q = fmaf(r, a, 0.0f);
-    return fmaf(r, fmaf(q, -b, a), q);
-}
-
 __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, float step, const AdamTable& t) {
-    m = fmaf(t.one_minus_b1, g - m, m);
-    v = fmaf(t.one_minus_b2 * g, g, v * t.b2);
-    const float denom = div_rn_nobranch(sqrt_rn_nobranch(v), t.bc2_sqrt) + t.eps;
-    p = fmaf(-step, div_rn_nobranch(m, denom), p);
+    adam_update(p, g, m, v, step, t.c);
 }
 
 template <bool VEC>
@@ -205,13 +172,8 @@ extern "C" int gsr_adam_step(const gsr_adam_segment* segments, int n_segments, i
     memset(&t, 0, sizeof(t));
     // bias corrections in double on the host, as torch computes them in Python floats (adam.py: _single_tensor_adam)
     // (torch rounds each scalar to fp32 once, from the double: 1-beta2 = 0.001 -> fp32, not 1.0f - 0.999f)
-    const double bc1 = 1.0 - std::pow(beta1, (double)step);
-    const double bc2 = 1.0 - std::pow(beta2, (double)step);
-    t.one_minus_b1 = (float)(1.0 - beta1);
-    t.b2 = (float)beta2;
-    t.one_minus_b2 = (float)(1.0 - beta2);
-    t.bc2_sqrt = (float)std::sqrt(bc2);
-    t.eps = (float)eps;
+    double bc1 = 1.0;
+    t.c = adam_consts(step, beta1, beta2, eps, &bc1);
     t.visible = visible;
     t.zero_grad = zero_grad;
     bool vec = true;

@@ -3,29 +3,120 @@
 // Replaces BACKWARD::render / renderCUDA<3> (diff-gaussian-rasterization-npu/cuda_rasterizer/
 // backward.cu:452-638).  The reference issues 9-10 global fp32 atomicAdd per contributing
 // (pixel, Gaussian) pair and evaluates every pair of the tile list below n_contrib.  Here:
-//   * batches start at the tile's deepest blended position (block max of n_contrib);
-//   * each warp owns an 8x4 pixel block and walks only the staged Gaussians whose 8-bit block mask
-//     (computed by the forward with rect_may_contribute, exact + conservatively rounded, and kept
-//     in the binning buffer) has its bit set -- the pairs skipped are pairs the reference would
-//     have rejected after evaluating them;
-//   * the ten per-Gaussian sums are reduced over the warp with a transposing butterfly
-//     (14 shuffles instead of 50: lanes trade halves of the value vector, so after log2 steps each
-//     value's total sits in its own lane), and the ten lanes that end up holding a total issue ONE
-//     native global RED.ADD.F32 each per (8x4 block, Gaussian): 32x fewer global atomics than the
-//     reference, no shared-memory accumulators (a shared fp32 atomicAdd is a CAS loop on sm_100),
-//     no retire phase;
-//   * the stage is double-buffered: one CTA barrier per 256-Gaussian batch, and a warp with a short
-//     list runs up to a batch ahead of its neighbours instead of waiting for them;
-//   * the next batch's records travel global -> shared with cp.async (LDGSTS) while the current one is
-//     processed: the pipeline holds two registers (a point_list entry and a mask), not fourteen.
-// The per-pixel recurrences are the reference's; power/alpha use the same exactly-rounded chain as
-// the forward so that every pair takes the same skip decision it took there.
+//   * one CTA of 4 warps per tile; a warp owns an 8x8 pixel block and every lane TWO pixels of one column
+//     (rows y and y+4, i.e. one pixel in each of the forward's two 8x4 sub-blocks).  Measured on the C2 workload
+//     (tools/blend_stats.py, profiles/r02_*): a Gaussian that reaches one 8x4 block usually reaches its vertical
+//     neighbour too, so the per-visit work that does not depend on the pixel -- list walk, record load, the
+//     cross-lane reduction and the atomics -- is paid once for both pixels; a visit whose mask reaches only one of
+//     the two sub-blocks evaluates only that pixel (warp-uniform branch);
+//   * batches start at the tile's deepest blended position (block max of n_contrib) and a warp skips the list
+//     positions behind its own deepest n_contrib;
+//   * each warp walks only the staged Gaussians whose 8-bit block mask (computed by the forward with
+//     rect_may_contribute, exact + conservatively rounded, kept in the binning buffer) reaches its block;
+//   * the ten per-Gaussian sums are NOT reduced with shuffles (a transposing butterfly costs 14 SHFL + ~30 selects
+//     and adds per visit, and the warp was issue-bound on it): every lane writes its ten partial sums to a per-warp
+//     shared-memory panel [slot][value][lane] (10 conflict-free STS), and once three visits are pending each of 30
+//     lanes sums ONE (slot, value) row with eight LDS.128 (rows padded to 36 floats: conflict-free) and issues ONE
+//     native global RED.ADD.F32 for it -- 30 of 32 lanes carry a total, where the butterfly left 10 of 32;
+//   * exp() of the skip test: ex2.approx(power * log2 e) decides; a pair whose alpha lands within 4e-6 relative of
+//     the 1/255 threshold re-evaluates with expf (the forward's function), so every pair takes the decision it took
+//     in the forward (bit-identical skip set), at 3 instructions instead of 9 for everything else;
+//   * the stage is double-buffered: one CTA barrier per 128-Gaussian batch; the next batch's records travel
+//     global -> shared with cp.async (LDGSTS) while the current one is processed.
+// The per-pixel recurrences are the reference's; power uses the same exactly-rounded chain as the forward.
 #include "gsr_common.cuh"
+#include <type_traits>
 
-#define RB_THREADS 256
+#define RB_THREADS 128
+#define RB_WARPS (RB_THREADS / 32)
+#define RB_BATCH 128
+#define RB_SLOTS 3
 #ifndef RB_MIN_CTAS
-#define RB_MIN_CTAS 5
+#define RB_MIN_CTAS 6
 #endif
+
+__device__ __forceinline__ float ex2_approx(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ void sts_f32(uint32_t a, float v) { asm volatile("st.shared.f32 [%0], %1;" :: "r"(a), "f"(v) : "memory"); }
+__device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" :: "r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t lds_u8(uint32_t a) { uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void red_add_f32(float* p, float v) { asm volatile("red.global.add.f32 [%0], %1;" :: "l"(p), "f"(v) : "memory"); }
+
+// per-pixel state of the backward recurrence
+struct PixState {
+    float T;                 // transmittance in front of the current layer (walked back from final_T)
+    f32x2 ACC01, ACC2D;      // colour / inverse depth accumulated behind the current layer: (r,g), (b,1/depth)
+    f32x2 DP01, DP2D;        // upstream gradient of the pixel: (dL/dr, dL/dg), (dL/db, dL/dinvdepth)
+    f32x2 negP;              // (-px, -py)
+    float nTf_bg;            // -T_final * sum_c bg_c dL_dpix_c   (backward.cu:612-615)
+    uint32_t last;           // n_contrib of the pixel (0 outside the image)
+};
+
+// One (pixel, Gaussian) pair: updates the pixel's recurrence and adds its ten partial sums to V*.  Returns false,
+// with nothing changed, when no lane of the warp blends this Gaussian into its pixel.
+__device__ __forceinline__ bool blend_pair_bwd(PixState& s, uint32_t pos, f32x2 XY, f32x2 AC, f32x2 BO, f32x2 RG, f32x2 BD,
+                                               f32x2& V01, f32x2& V23, f32x2& V45, f32x2& V68, f32x2& V7W) {
+    const f32x2 D = add2(XY, s.negP);           // (x - px, y - py): same rounding as fsub
+    const f32x2 M = mul2(D, AC);                // (dx A, dy C)
+    float dx, dy, dxA, dyC, cB, opac;
+    upk(D, dx, dy); upk(M, dxA, dyC); upk(BO, cB, opac);
+    // power with the forward's rounding (blend_power), keeping the partial products
+    const float dxB = fmul(dx, cB);
+    const float power = ffma(ffma(dx, dxA, fmul(dy, dyC)), -0.5f, -fmul(dy, dxB));
+    float G = ex2_approx(power * 1.4426950408889634f);
+    float a_raw = fmul(opac, G);
+    const bool live = (pos < s.last) && !(power > 0.0f);
+    // within 4e-6 relative of the threshold the approximation does not decide: use the forward's expf
+    const bool unsure = live && fabsf(a_raw - 1.0f / 255.0f) <= 4e-6f * (1.0f / 255.0f);
+    if (__any_sync(0xffffffffu, unsure)) { G = expf(power); a_raw = fmul(opac, G); }
+    const float alpha = fminf(0.99f, a_raw);
+    const bool contrib = live && (alpha >= 1.0f / 255.0f);
+    if (!__any_sync(0xffffffffu, contrib)) return false;
+    // Straight-line from here.  A lane whose pixel does not blend this Gaussian runs the same arithmetic with
+    // alpha := 0 and G := 0, which leaves its recurrences bit-identical (a zero-alpha layer: T/(1-0) = T,
+    // acc + 0*(c-acc) = acc) and makes all ten of its partial sums exactly 0.
+    const float al = contrib ? alpha : 0.0f;
+    const float Gc = contrib ? G : 0.0f;
+    const float inv = rcp_approx(1.0f - al);      // exactly 1 for al == 0
+    s.T *= inv;
+    const float dch = al * s.T;
+    // accum_rec recurrence (backward.cu:569-581), folded: ACC holds the colour behind this layer; once used it
+    // absorbs this layer, acc += alpha (c - acc).  Two channels per instruction.
+    const f32x2 d01 = sub2(RG, s.ACC01), d2d = sub2(BD, s.ACC2D);
+    const f32x2 dots = fma2(d2d, s.DP2D, mul2(d01, s.DP01));
+    s.ACC01 = fma2(pk(al, al), d01, s.ACC01);
+    s.ACC2D = fma2(pk(al, al), d2d, s.ACC2D);
+    float dot_lo, dot_hi;
+    upk(dots, dot_lo, dot_hi);
+    const float dL_dalpha = fmaf(dot_lo + dot_hi, s.T, s.nTf_bg * inv);
+    V01 = fma2(s.DP01, pk(dch, dch), V01);
+    V23 = fma2(s.DP2D, pk(dch, dch), V23);
+    // moments of w = G dL/dalpha
+    const float w = Gc * dL_dalpha;
+    const f32x2 WD = mul2(D, pk(w, w));                                     // (w dx, w dy)
+    V68 = fma2(WD, D, V68);                                                 // (w dx^2, w dy^2)
+    V45 = fma2(pk(fmaf(dy, cB, dxA), dxB + dyC), pk(w, w), V45);            // w (A dx + B dy), w (B dx + C dy)
+    float wdx, wdy;
+    upk(WD, wdx, wdy);
+    V7W = add2(V7W, pk(wdx * dy, w));                                       // (w dx dy, w)
+    return true;
+}
+
+// keeps a shared-memory address in a register: without it nvcc re-derives every address from the shared-window base
+// (S2UR SR_CgaCtaId ; UMOV ; ULEA ...) at each use inside the hot loop
+__device__ __forceinline__ uint32_t pin(uint32_t v) {
+    uint32_t r;
+    asm volatile("mov.b32 %0, %1;" : "=r"(r) : "r"(v));
+    return r;
+}
+
+#define RB_ROW 36                 // floats per panel row: 32 lanes + 4 of padding, so that the eight rows a quarter-warp
+                                  // reads with LDS.128 start 16 bytes apart (conflict-free without address rotation)
+#define RB_ROWS (RB_SLOTS * 10)   // 30 rows: one per lane when the panel is flushed
 
 template <bool HAS_DEPTH>
 __global__ void __launch_bounds__(RB_THREADS, RB_MIN_CTAS)
@@ -36,47 +127,61 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvdepth_pix,
                   float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity,
                   float* __restrict__ dL_dcolor, float* __restrict__ dL_dinvdepth) {
-    // stage: the raw 48-byte records (x,y,A,C | B,opacity,r,g | b,1/depth,0,0) of a 256-Gaussian batch,
+    // stage: the raw 48-byte records (x,y,A,C | B,opacity,r,g | b,1/depth,0,0) of a 128-Gaussian batch,
     // double-buffered, filled by cp.async
-    __shared__ float4 sRec[2][RB_THREADS * 3];
-    __shared__ uint32_t sId[2][RB_THREADS];
-    __shared__ unsigned char sMask[2][RB_THREADS];
-    __shared__ uint32_t sMax[RB_THREADS / 32];
+    __shared__ float4 sRec[2][RB_BATCH * 3];
+    __shared__ uint32_t sId[2][RB_BATCH];
+    __shared__ unsigned char sMask[2][RB_BATCH];
+    __shared__ uint32_t sMax[RB_WARPS];
+    // reduction panel of each warp: rows (slot, value 0..9) x lanes, + (Gaussian index, opacity) of every pending slot
+    __shared__ __align__(16) float sRed[RB_WARPS][RB_ROWS * RB_ROW];
+    __shared__ __align__(8) uint2 sSlot[RB_WARPS][RB_SLOTS];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.x;
     const int tx = tile % gx, ty = tile / gx;
+    // warp -> 8x8 block (column warp&1, row pair warp>>1); lane -> pixels (x, y) and (x, y+4): the forward's 8x4
+    // sub-blocks bA = (warp&1) + 4*(warp>>1) and bB = bA + 2
     const int px = tx * GSR_TILE + (warp & 1) * 8 + (lane & 7);
-    const int py = ty * GSR_TILE + (warp >> 1) * 4 + (lane >> 3);
-    const bool inside = px < W && py < H;
-    const float pxf = (float)px, pyf = (float)py;
-    const size_t pix = (size_t)py * W + px, HW = (size_t)H * W;
-
+    const int pyA = ty * GSR_TILE + (warp >> 1) * 8 + (lane >> 3), pyB = pyA + 4;
+    const int bA = (warp & 1) + 4 * (warp >> 1);
+    const size_t HW = (size_t)H * W;
     const uint2 range = ranges[tile];
-    const uint32_t last = inside ? n_contrib[pix] : 0u;
-    const float T_final = inside ? final_T[pix] : 0.0f;
-    float dpx0 = 0, dpx1 = 0, dpx2 = 0, dpd = 0;
-    if (inside) {
-        dpx0 = dL_dpix[pix]; dpx1 = dL_dpix[HW + pix]; dpx2 = dL_dpix[2 * HW + pix];
-        if (HAS_DEPTH) dpd = dL_dinvdepth_pix[pix];
-    }
-    // background term of dL/dalpha: (-T_final / (1 - alpha)) * sum_c bg_c dL_dpix_c   (backward.cu:612-615)
-    const float nTf_bg = -T_final * (background[0] * dpx0 + background[1] * dpx1 + background[2] * dpx2);
+    const float bg0 = background[0], bg1 = background[1], bg2 = background[2];
 
-    // Which of the ten per-Gaussian totals this lane holds after the butterfly, and where it goes.
-    // Totals 0..7 end in lanes 4v (register v0), totals 8, 9 in lanes 1 and 17 (register w0).
-    //   0..2 sum dch dL_dpix_c            -> dL_dcolor[3 id + c]
-    //   3    sum dch dL_dinvdepth_pix     -> dL_dinvdepth[id]
-    //   4, 5 sum w (A dx + B dy), sum w (B dx + C dy)   (w = G dL_dalpha)
-    //                                     -> dL_dmean2D[3 id + {0,1}] * (-0.5 opacity {W,H})   (backward.cu:593-607)
-    //   6..8 sum w dx^2, w dx dy, w dy^2  -> dL_dconic[4 id + {0,1,3}] * (-0.5 opacity)        (backward.cu:619-622)
-    //   9    sum w                        -> dL_dopacity[id]                                    (backward.cu:625)
-    const bool first = (lane & 3) == 0, second = (lane & 15) == 1;
-    const int vi = first ? (lane >> 2) : 8 + (lane >> 4);
+    PixState A, B;
+    auto init_pixel = [&](PixState& s, int py) {
+        const bool inside = px < W && py < H;
+        const size_t pix = (size_t)py * W + px;
+        s.last = inside ? n_contrib[pix] : 0u;
+        const float T_final = inside ? final_T[pix] : 0.0f;
+        float d0 = 0, d1 = 0, d2 = 0, dd = 0;
+        if (inside) {
+            d0 = dL_dpix[pix]; d1 = dL_dpix[HW + pix]; d2 = dL_dpix[2 * HW + pix];
+            if (HAS_DEPTH) dd = dL_dinvdepth_pix[pix];
+        }
+        s.T = T_final;
+        s.nTf_bg = -T_final * (bg0 * d0 + bg1 * d1 + bg2 * d2);
+        s.ACC01 = pk(0.0f, 0.0f); s.ACC2D = pk(0.0f, 0.0f);
+        s.DP01 = pk(d0, d1); s.DP2D = pk(d2, dd);
+        s.negP = pk(-(float)px, -(float)py);
+    };
+    init_pixel(A, pyA);
+    init_pixel(B, pyB);
+
+    // Which panel row this lane sums when the panel is flushed (lane l < 30: slot l / 10, value l % 10), and where
+    // the total goes.
+    //   value 0..2  sum dch dL_dpix_c             -> dL_dcolor[3 id + c]
+    //         3     sum dch dL_dinvdepth_pix      -> dL_dinvdepth[id]
+    //         4, 5  sum w (A dx + B dy), w (B dx + C dy)   (w = G dL_dalpha)
+    //                                             -> dL_dmean2D[3 id + {0,1}] * (-0.5 opacity {W,H})   (backward.cu:593-607)
+    //         6, 7, 8  sum w dx^2, w dx dy, w dy^2 -> dL_dconic[4 id + {0,1,3}] * (-0.5 opacity)        (backward.cu:619-622)
+    //         9     sum w                         -> dL_dopacity[id]                                    (backward.cu:625)
+    const int fslot = lane / 10, fval = lane - 10 * fslot;
     float* obase = nullptr; uint32_t ostride = 0; float oc_a = 0.0f, oc_b = 0.0f;
-    if (first || second) {
-        switch (vi) {
-            case 0: case 1: case 2: obase = dL_dcolor + vi; ostride = 3; oc_a = 1.0f; break;
+    if (lane < RB_ROWS) {
+        switch (fval) {
+            case 0: case 1: case 2: obase = dL_dcolor + fval; ostride = 3; oc_a = 1.0f; break;
             case 3: obase = HAS_DEPTH ? dL_dinvdepth : nullptr; ostride = 1; oc_a = 1.0f; break;
             case 4: obase = dL_dmean2D; ostride = 3; oc_b = -0.5f * (float)W; break;
             case 5: obase = dL_dmean2D + 1; ostride = 3; oc_b = -0.5f * (float)H; break;
@@ -86,28 +191,22 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
             default: obase = dL_dopacity; ostride = 1; oc_a = 1.0f; break;
         }
     }
-    const bool emits = obase != nullptr;
 
-    // deepest list position any pixel of this tile blended
-    const uint32_t wmax = __reduce_max_sync(0xffffffffu, last);
+    // deepest list position any pixel of this tile / this warp blended
+    const uint32_t wmax = __reduce_max_sync(0xffffffffu, max(A.last, B.last));
     if (lane == 0) sMax[warp] = wmax;
     __syncthreads();
     uint32_t remaining = 0;
 #pragma unroll
-    for (int w = 0; w < RB_THREADS / 32; w++) remaining = max(remaining, sMax[w]);
+    for (int w = 0; w < RB_WARPS; w++) remaining = max(remaining, sMax[w]);
 
-    float T = T_final;
-    // colour / inverse depth accumulated behind the current layer, as fp32x2 pairs (r,g), (b,1/depth)
-    f32x2 ACC01 = pk(0.0f, 0.0f), ACC2D = pk(0.0f, 0.0f);
-    const f32x2 DP01 = pk(dpx0, dpx1), DP2D = pk(dpx2, HAS_DEPTH ? dpd : 0.0f), negP = pk(-pxf, -pyf);
-
-    // Software pipeline without staging registers: while batch b is processed, the records of batch b+1
-    // travel global -> shared by cp.async, and the point_list entry + block mask of batch b+2 sit in two
-    // registers.  Batches walk the list backwards: batch k covers positions [remaining-256(k+1), remaining-256k).
+    // Software pipeline without staging registers: while batch b is processed, the records of batch b+1 travel
+    // global -> shared by cp.async, and the point_list entry + block mask of batch b+2 sit in two registers.
+    // Batches walk the list backwards: batch k covers positions [remaining-128(k+1), remaining-128k).
     const uint32_t my_rec0 = smem_addr(&sRec[0][tid * 3]);
     auto fetch = [&](uint32_t id, uint32_t mask, int b) {
         const float4* rec = records + 3 * (size_t)id;
-        const uint32_t dst = my_rec0 + (uint32_t)b * (RB_THREADS * 48u);
+        const uint32_t dst = my_rec0 + (uint32_t)b * (RB_BATCH * 48u);
         cp_async16(dst, rec); cp_async16(dst + 16u, rec + 1); cp_async16(dst + 32u, rec + 2);
         sId[b][tid] = id; sMask[b][tid] = (unsigned char)mask;
     };
@@ -117,122 +216,113 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         fetch(point_list[pos], block_masks[pos], 0);
     }
     cp_async_commit();
-    if ((uint32_t)(RB_THREADS + tid) < remaining) {
-        const size_t pos = (size_t)range.x + remaining - 1 - RB_THREADS - tid;
+    if ((uint32_t)(RB_BATCH + tid) < remaining) {
+        const size_t pos = (size_t)range.x + remaining - 1 - RB_BATCH - tid;
         next_id = point_list[pos]; next_mask = block_masks[pos];
     }
 
+    const uint32_t aRec0 = pin(smem_addr(&sRec[0][0])), aId0 = pin(smem_addr(&sId[0][0]));
+    const uint32_t aMaskLane0 = pin(smem_addr(&sMask[0][0]) + (uint32_t)lane);
+    const uint32_t aPanelLane = pin(smem_addr(&sRed[warp][0]) + 4u * (uint32_t)lane);        // column of this lane
+    const uint32_t aPanelRow = pin(smem_addr(&sRed[warp][0]) + (uint32_t)(RB_ROW * 4) * (uint32_t)min(lane, RB_ROWS - 1));
+    const uint32_t aSlot = pin(smem_addr(&sSlot[warp][0]));
+    const uint32_t aSlotMine = pin(smem_addr(&sSlot[warp][0]) + 8u * (uint32_t)min(fslot, RB_SLOTS - 1));
+    int slot = 0;
+
+    // sums the pending slots' rows and issues the atomics: one (slot, value) total per lane, 30 lanes busy
+    auto flush = [&](int nslots) {
+        __syncwarp();
+        if (fslot < nslots) {
+            f32x2 t0, t1;
+            lds_2x64(aPanelRow, t0, t1);
+#pragma unroll
+            for (int i = 1; i < 8; i++) {
+                f32x2 u0, u1;
+                lds_2x64(aPanelRow + 16u * i, u0, u1);
+                t0 = add2(t0, u0); t1 = add2(t1, u1);
+            }
+            t0 = add2(t0, t1);
+            float lo, hi;
+            upk(t0, lo, hi);
+            uint32_t id, opbits;
+            asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(id), "=r"(opbits) : "r"(aSlotMine));
+            const float val = (lo + hi) * fmaf(oc_b, __uint_as_float(opbits), oc_a);
+            if (obase != nullptr && val != 0.0f) red_add_f32(obase + ostride * id, val);
+        }
+        __syncwarp();
+    };
+
+    // One (Gaussian, 8x8 block) visit; HA / HB: whether the Gaussian's mask reaches the upper / lower 8x4 half
+    // (warp-uniform, so the three instantiations are straight-line code with no merges)
+    auto visit = [&](auto ha, auto hb, uint32_t aRecJ, uint32_t aIdJ, uint32_t pos) {
+        constexpr bool HA = decltype(ha)::value, HB = decltype(hb)::value;
+        f32x2 XY, AC, BO, RG;
+        lds_2x64(aRecJ, XY, AC);
+        lds_2x64(aRecJ + 16u, BO, RG);
+        const f32x2 BD = lds_64(aRecJ + 32u);
+        f32x2 V01 = pk(0.0f, 0.0f), V23 = V01, V45 = V01, V68 = V01, V7W = V01;
+        bool any = false;
+        if (HA) any = blend_pair_bwd(A, pos, XY, AC, BO, RG, BD, V01, V23, V45, V68, V7W);
+        if (HB) any = blend_pair_bwd(B, pos, XY, AC, BO, RG, BD, V01, V23, V45, V68, V7W) || any;
+        if (!any) return;
+        // park the lane's ten partial sums in the panel: row (slot, value), column lane
+        const uint32_t col = aPanelLane + (uint32_t)slot * (10u * RB_ROW * 4u);
+        float v0, v1, v2, v3, v4, v5, v6, v8, v7, v9;
+        upk(V01, v0, v1); upk(V23, v2, v3); upk(V45, v4, v5); upk(V68, v6, v8); upk(V7W, v7, v9);
+        sts_f32(col, v0); sts_f32(col + RB_ROW * 4u, v1); sts_f32(col + RB_ROW * 8u, v2);
+        if (HAS_DEPTH) sts_f32(col + RB_ROW * 12u, v3);
+        sts_f32(col + RB_ROW * 16u, v4); sts_f32(col + RB_ROW * 20u, v5); sts_f32(col + RB_ROW * 24u, v6);
+        sts_f32(col + RB_ROW * 28u, v7); sts_f32(col + RB_ROW * 32u, v8); sts_f32(col + RB_ROW * 36u, v9);
+        {   // every lane writes the same two words (Gaussian index, opacity): no divergence, one store
+            float cB_, opac_;
+            upk(BO, cB_, opac_);
+            const uint32_t id = lds_u32(aIdJ);
+            asm volatile("st.shared.v2.u32 [%0], {%1,%2};" :: "r"(aSlot + 8u * (uint32_t)slot), "r"(id), "r"(__float_as_uint(opac_)) : "memory");
+        }
+        if (++slot == RB_SLOTS) { flush(RB_SLOTS); slot = 0; }
+    };
+
     int buf = 0;
     while (remaining > 0) {
-        const int n = (int)min((uint32_t)RB_THREADS, remaining);
+        const int n = (int)min((uint32_t)RB_BATCH, remaining);
         cp_async_wait_all();                   // this thread's record of the current batch has landed
         // One barrier per batch: publishes stage `buf` and proves that every warp has left the batch before
         // this one -- the last reader of stage `buf ^ 1`, which is refilled right below.
         __syncthreads();
-        if ((uint32_t)(RB_THREADS + tid) < remaining) fetch(next_id, next_mask, buf ^ 1);
+        if ((uint32_t)(RB_BATCH + tid) < remaining) fetch(next_id, next_mask, buf ^ 1);
         cp_async_commit();
-        if ((uint32_t)(2 * RB_THREADS + tid) < remaining) {
-            const size_t pos = (size_t)range.x + remaining - 1 - 2 * RB_THREADS - tid;
+        if ((uint32_t)(2 * RB_BATCH + tid) < remaining) {
+            const size_t pos = (size_t)range.x + remaining - 1 - 2 * RB_BATCH - tid;
             next_id = point_list[pos]; next_mask = block_masks[pos];
         }
         // positions this warp still has to look at: below its deepest n_contrib
         if (remaining - (uint32_t)n < wmax) {
-            const uint32_t aRec = smem_addr(sRec[buf]);
-            const uint32_t* ids = sId[buf];
-            const unsigned char* masks = sMask[buf];
+            const uint32_t aRec = aRec0 + (uint32_t)buf * (RB_BATCH * 48u), aIds = aId0 + (uint32_t)buf * (RB_BATCH * 4u);
+            const uint32_t aMasks = aMaskLane0 + (uint32_t)buf * RB_BATCH;
+            const int jmin = remaining > wmax ? (int)(remaining - wmax) : 0;    // list positions >= wmax: nothing of this warp
 #pragma unroll 1
-            for (int k = 0; k < RB_THREADS / 32; k++) {
+            for (int k = 0; k < RB_BATCH / 32; k++) {
                 const int idx = k * 32 + lane;
-                unsigned bits = __ballot_sync(0xffffffffu, idx < n && ((masks[idx] >> warp) & 1));
+                const uint32_t m = (idx < n && idx >= jmin) ? lds_u8(aMasks + 32u * k) >> bA : 0u;
+                const unsigned bitsA = __ballot_sync(0xffffffffu, m & 1u);
+                const unsigned bitsB = __ballot_sync(0xffffffffu, m & 4u);
+                unsigned bits = bitsA | bitsB;
                 while (bits) {
-                    const int j = k * 32 + __ffs(bits) - 1;
+                    const int b = __ffs(bits) - 1;
+                    const uint32_t j = (uint32_t)(k * 32 + b);
                     bits &= bits - 1;
-                    // Straight-line body.  A lane whose pixel does not blend this Gaussian runs the same
-                    // arithmetic with alpha := 0 and G := 0, which leaves its recurrences bit-identical
-                    // (a zero-alpha layer: T/(1-0) = T, acc + 0*(c-acc) = acc) and makes all ten of its
-                    // partial sums exactly 0 -- no divergence, no zero-initialisation.
-                    f32x2 XY, AC, BO, RG;
-                    lds_2x64(aRec + 48u * j, XY, AC);
-                    lds_2x64(aRec + 48u * j + 16u, BO, RG);
-                    const f32x2 D = add2(XY, negP);             // (x - px, y - py): same rounding as fsub
-                    const f32x2 M = mul2(D, AC);                // (dx A, dy C)
-                    float dx, dy, dxA, dyC, cB, opac;
-                    upk(D, dx, dy); upk(M, dxA, dyC); upk(BO, cB, opac);
-                    // power with the forward's rounding (blend_power), keeping the partial products
-                    const float dxB = fmul(dx, cB);
-                    const float power = ffma(ffma(dx, dxA, fmul(dy, dyC)), -0.5f, -fmul(dy, dxB));
-                    const float G = expf(power);
-                    const float alpha = fminf(0.99f, fmul(opac, G));
-                    const bool contrib = (remaining - 1 - (uint32_t)j < last) && !(power > 0.0f) && (alpha >= 1.0f / 255.0f);
-                    if (!__any_sync(0xffffffffu, contrib)) continue;
-                    const f32x2 BD = lds_64(aRec + 48u * j + 32u);
-                    const float al = contrib ? alpha : 0.0f;
-                    const float Gc = contrib ? G : 0.0f;
-                    const float inv = rcp_approx(1.0f - al);      // exactly 1 for al == 0
-                    T *= inv;
-                    const float dch = al * T;
-                    // accum_rec recurrence (backward.cu:569-581), folded: ACC holds the colour behind this
-                    // layer; once used it absorbs this layer, acc += alpha (c - acc).  Two channels per
-                    // instruction; without a depth gradient the fourth lane carries DP = 0.
-                    const f32x2 d01 = sub2(RG, ACC01), d2d = sub2(BD, ACC2D);
-                    const f32x2 dots = fma2(d2d, DP2D, mul2(d01, DP01));
-                    ACC01 = fma2(pk(al, al), d01, ACC01);
-                    ACC2D = fma2(pk(al, al), d2d, ACC2D);
-                    float dot_lo, dot_hi;
-                    upk(dots, dot_lo, dot_hi);
-                    const float dL_dalpha = fmaf(dot_lo + dot_hi, T, nTf_bg * inv);
-                    const f32x2 V01 = mul2(DP01, pk(dch, dch)), V23 = mul2(DP2D, pk(dch, dch));
-                    // moments of w = G dL/dalpha over the warp's pixels
-                    float w1 = Gc * dL_dalpha;
-                    const f32x2 WD = mul2(D, pk(w1, w1));                       // (w dx, w dy)
-                    const f32x2 V68 = mul2(WD, D);                              // (w dx^2, w dy^2)
-                    const f32x2 V45 = mul2(pk(fmaf(dy, cB, dxA), dxB + dyC), pk(w1, w1));   // w (A dx + B dy), w (B dx + C dy)
-                    float v0, v1, v2, v3, v4, v5, v6, v7, w0, wdx, wdy;
-                    upk(V01, v0, v1); upk(V23, v2, v3); upk(V45, v4, v5); upk(V68, v6, w0); upk(WD, wdx, wdy);
-                    v7 = wdx * dy;
-                    // transposing butterfly: 8 values -> each lane ends with the warp total of value (lane>>2);
-                    // the adds go two per instruction
-                    f32x2 S01, S23;
-                    {
-                        const bool h = lane & 16;
-                        const f32x2 kp01 = pk(h ? v4 : v0, h ? v5 : v1), kp23 = pk(h ? v6 : v2, h ? v7 : v3);
-                        const float r0 = __shfl_xor_sync(0xffffffffu, h ? v0 : v4, 16), r1 = __shfl_xor_sync(0xffffffffu, h ? v1 : v5, 16);
-                        const float r2 = __shfl_xor_sync(0xffffffffu, h ? v2 : v6, 16), r3 = __shfl_xor_sync(0xffffffffu, h ? v3 : v7, 16);
-                        const float s = h ? w0 : w1, kp = h ? w1 : w0;
-                        w0 = kp + __shfl_xor_sync(0xffffffffu, s, 16);
-                        S01 = add2(kp01, pk(r0, r1)); S23 = add2(kp23, pk(r2, r3));
-                    }
-                    {
-                        const bool h = lane & 8;
-                        upk(S01, v0, v1); upk(S23, v2, v3);
-                        const f32x2 kp = pk(h ? v2 : v0, h ? v3 : v1);
-                        const float r0 = __shfl_xor_sync(0xffffffffu, h ? v0 : v2, 8), r1 = __shfl_xor_sync(0xffffffffu, h ? v1 : v3, 8);
-                        S01 = add2(kp, pk(r0, r1));
-                        w0 += __shfl_xor_sync(0xffffffffu, w0, 8);
-                    }
-                    f32x2 VW;    // (v0, w0) from here on
-                    {
-                        const bool h = lane & 4;
-                        upk(S01, v0, v1);
-                        const float s = h ? v0 : v1, kp = h ? v1 : v0;
-                        VW = add2(pk(kp, w0), pk(__shfl_xor_sync(0xffffffffu, s, 4), __shfl_xor_sync(0xffffffffu, w0, 4)));
-                    }
-                    upk(VW, v0, w0);
-                    VW = add2(VW, pk(__shfl_xor_sync(0xffffffffu, v0, 2), __shfl_xor_sync(0xffffffffu, w0, 2)));
-                    upk(VW, v0, w0);
-                    VW = add2(VW, pk(__shfl_xor_sync(0xffffffffu, v0, 1), __shfl_xor_sync(0xffffffffu, w0, 1)));
-                    upk(VW, v0, w0);
-                    // v0: total of value index (lane>>2) in 0..7 ; w0: total of value 8 + (lane>>4)
-                    if (emits) {
-                        const float val = (first ? v0 : w0) * fmaf(oc_b, opac, oc_a);
-                        if (val != 0.0f) atomicAdd(obase + (size_t)ostride * ids[j], val);
-                    }
+                    const uint32_t pos = remaining - 1 - j;
+                    const bool ha = (bitsA >> b) & 1u, hb = (bitsB >> b) & 1u;
+                    if (ha && hb) visit(std::true_type{}, std::true_type{}, aRec + 48u * j, aIds + 4u * j, pos);
+                    else if (ha) visit(std::true_type{}, std::false_type{}, aRec + 48u * j, aIds + 4u * j, pos);
+                    else visit(std::false_type{}, std::true_type{}, aRec + 48u * j, aIds + 4u * j, pos);
                 }
             }
         }
         remaining -= n;
         buf ^= 1;
     }
+    if (slot) flush(slot);
     cp_async_wait_all();
 }
 

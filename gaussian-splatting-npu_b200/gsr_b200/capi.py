@@ -76,6 +76,8 @@ EXPORTS = ["gsr_forward", "gsr_backward", "gsr_mark_visible", "gsr_geometry_byte
            "gsr_exposure_clamp_backward",
            # include/gsr_optim.h
            "gsr_adam_step", "gsr_densification_stats",
+           # include/gsr_dist.h (bound in gsr_b200/exchange.py)
+           "gsr_exchange_signal_words", "gsr_exchange_shard", "gsr_exchange_step",
            # include/gsr_ply.h (bound in gsr_b200/ply.py)
            "gsr_ply_parse_header", "gsr_ply_write_header", "gsr_ply_unpack", "gsr_ply_pack",
            # include/gsr_frame.h (bound in gsr_b200/frames.py)

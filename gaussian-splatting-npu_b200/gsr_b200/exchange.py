@@ -1,0 +1,180 @@
+"""The exchange step of view-parallel training as one fused kernel per rank (include/gsr_dist.h, csrc/exchange.cu):
+reduce-scatter of the gradient bucket -> Adam on the owner's shard -> all-gather of the updated parameters, plus the
+SUM / MAX all-reduce of the densification statistics, over NVLink / NVSwitch peer memory.
+
+Replaces `dist.all_reduce(bucket)` + `GaussianAdam.step()` on every rank + `DensificationStats.allreduce()` (three more
+collectives) of gsr_b200/dist.py -- the semantics of /root/reference/train.py:163-186 applied to the sum of the step's
+views.  torch.distributed is plumbing only: its symmetric-memory allocator maps every rank's buffers into every
+process (and, on NVSwitch systems, gives the multicast mapping multimem.ld_reduce / multimem.st need); the kernel and
+its barriers are this library's.  No fallback: without the library or without peer access this raises.
+"""
+import ctypes
+from ctypes import POINTER, Structure, c_double, c_float, c_int, c_size_t, c_void_p
+
+import torch
+import torch.distributed as dist
+
+from . import capi
+from .dist import SEGMENTS, FlatGaussians, _pad
+from .optim import DEFAULT_LRS
+
+MAX_RANKS = 16
+ADAM, SUM, MAX = 0, 1, 2
+STAT_SEGMENTS = (("stat_accum", SUM), ("stat_denom", SUM), ("stat_radii", MAX))
+
+
+class ExchangeSegment(Structure):
+    _fields_ = [("begin", c_size_t), ("end", c_size_t), ("kind", c_int), ("cols", c_int), ("split_col", c_int),
+                ("lr_a", c_float), ("lr_b", c_float)]
+
+
+class ExchangeArgs(Structure):
+    _fields_ = [("rank", c_int), ("world", c_int), ("n", c_size_t), ("grad_peer", c_void_p * MAX_RANKS),
+                ("param_peer", c_void_p * MAX_RANKS), ("grad_mc", c_void_p), ("param_mc", c_void_p),
+                ("signal_peer", c_void_p * MAX_RANKS), ("exp_avg", c_void_p), ("exp_avg_sq", c_void_p),
+                ("segments", POINTER(ExchangeSegment)), ("n_segments", c_int), ("step", c_int),
+                ("beta1", c_double), ("beta2", c_double), ("eps", c_double)]
+
+
+_bound = False
+
+
+def _lib():
+    global _bound
+    L = capi.lib()
+    if not _bound:
+        L.gsr_exchange_signal_words.restype = c_size_t
+        L.gsr_exchange_shard.argtypes = [c_size_t, c_int, c_int, POINTER(c_size_t), POINTER(c_size_t)]
+        L.gsr_exchange_step.restype = c_int
+        L.gsr_exchange_step.argtypes = [POINTER(ExchangeArgs), c_void_p]
+        _bound = True
+    return L
+
+
+def shard(n, rank, world):
+    """Floats [begin, end) of the flat buffers that `rank` owns (gsr_exchange_shard)."""
+    b, e = c_size_t(0), c_size_t(0)
+    _lib().gsr_exchange_shard(n, rank, world, ctypes.byref(b), ctypes.byref(e))
+    return b.value, e.value
+
+
+def layout(P):
+    """Offsets (floats) of the parameter segments followed by the three statistic segments; total length."""
+    off, offsets = 0, {}
+    for name, n in SEGMENTS:
+        offsets[name] = off
+        off += _pad(P * n)
+    n_param = off
+    for name, _ in STAT_SEGMENTS:
+        offsets[name] = off
+        off += _pad(P)
+    return offsets, n_param, off
+
+
+class SymmetricGaussians(FlatGaussians):
+    """FlatGaussians whose gradient bucket (+ the densification-statistic deltas behind it) and parameter buffer live in
+    symmetric memory: every rank's copy is mapped into every process of `group`.  With world size 1 (or no process
+    group) the buffers are ordinary device tensors."""
+
+    def __init__(self, P, device, group=None):
+        self.P, self.device = P, device
+        self.group = group if group is not None else (dist.group.WORLD if dist.is_initialized() else None)
+        self.world = dist.get_world_size(self.group) if self.group is not None else 1
+        self.rank = dist.get_rank(self.group) if self.group is not None else 0
+        self.offsets, self.n_param, self.n_grad = layout(P)
+        n_sig = int(_lib().gsr_exchange_signal_words())
+        self._n_total = self.n_grad + self.n_param + n_sig         # [gradients + statistics | parameters | signal words]
+        if self.world > 1:
+            import torch.distributed._symmetric_memory as symm_mem
+            try:
+                symm_mem.enable_symm_mem_for_group(self.group.group_name)
+            except Exception:
+                pass
+            self._storage = symm_mem.empty(self._n_total, dtype=torch.float32, device=device)
+            self._storage.zero_()
+            self._hdl = symm_mem.rendezvous(self._storage, self.group.group_name)
+            peers = [int(p) for p in self._hdl.buffer_ptrs]
+            mc = int(getattr(self._hdl, "multicast_ptr", 0) or 0)
+        else:
+            self._storage = torch.zeros(self._n_total, dtype=torch.float32, device=device)
+            self._hdl, peers, mc = None, [self._storage.data_ptr()], 0
+        self.grad_all = self._storage[:self.n_grad]
+        self.bucket = self._storage[:self.n_param]
+        self.params = self._storage[self.n_grad:self.n_grad + self.n_param]
+        self.peer_grad = peers
+        self.peer_param = [p + 4 * self.n_grad for p in peers]
+        self.peer_signal = [p + 4 * (self.n_grad + self.n_param) for p in peers]
+        self.mc_grad = mc
+        self.mc_param = mc + 4 * self.n_grad if mc else 0
+        torch.cuda.synchronize(device)
+        if self.world > 1:
+            dist.barrier(self.group)            # every rank's buffers are zeroed before anybody signals into them
+
+    def stat_views(self):
+        """Step-local densification-statistic deltas (rank-local sums over this rank's views): [P,1], [P,1], [P]."""
+        v = lambda name: self._storage[self.offsets[name]: self.offsets[name] + self.P]
+        return v("stat_accum").view(self.P, 1), v("stat_denom").view(self.P, 1), v("stat_radii")
+
+
+class FusedExchange:
+    """Per-step driver of gsr_exchange_step on a SymmetricGaussians.
+
+    step()          reduce-scatter -> sharded Adam -> all-gather (+ statistics): after the kernel every rank holds the
+                    updated parameters; the gradient bucket is consumed (the next step's first backward overwrites it).
+    allreduce()     in-place SUM all-reduce of the bucket only (no optimizer), the exchange `dist.all_reduce` did.
+    Adam hyper-parameters and learning rates are GaussianAdam's (gaussian_model.py:178-201).  Moments live on the shard's
+    owner only: 2 x 59 P / W floats per GPU."""
+
+    def __init__(self, flat, lrs=None, spatial_lr_scale=1.0, betas=(0.9, 0.999), eps=1e-15, use_multicast=True):
+        assert isinstance(flat, SymmetricGaussians)
+        self.flat, self.betas, self.eps, self.step_count = flat, betas, eps, 0
+        self.lrs = dict(DEFAULT_LRS)
+        self.lrs.update(lrs or {})
+        self.lrs["xyz"] = self.lrs["xyz"] * spatial_lr_scale
+        self.use_multicast = bool(use_multicast and flat.mc_grad)
+        b, e = shard(flat.n_grad, flat.rank, flat.world)
+        self.shard = (b, e)
+        self.exp_avg = torch.zeros(max(e - b, 4), dtype=torch.float32, device=flat.device)
+        self.exp_avg_sq = torch.zeros_like(self.exp_avg)
+
+    def set_lr(self, name, lr):
+        self.lrs[name] = float(lr)
+
+    def _segments(self, adam, stats):
+        f = self.flat
+        lr_of = dict(xyz=("xyz", "xyz", 3), shs=("f_dc", "f_rest", 3), opacity=("opacity", "opacity", 1),
+                     scales=("scaling", "scaling", 3), rotations=("rotation", "rotation", 4))
+        cols = dict(SEGMENTS)
+        segs = []
+        for name, _ in SEGMENTS:
+            a, b, split = lr_of[name]
+            begin = f.offsets[name]
+            segs.append(ExchangeSegment(begin, begin + _pad(f.P * cols[name]), ADAM if adam else SUM, cols[name], split,
+                                        self.lrs[a], self.lrs[b]))
+        if stats:
+            for name, kind in STAT_SEGMENTS:
+                begin = f.offsets[name]
+                segs.append(ExchangeSegment(begin, begin + _pad(f.P), kind, 1, 1, 0.0, 0.0))
+        return (ExchangeSegment * len(segs))(*segs)
+
+    def _launch(self, adam, stats):
+        f = self.flat
+        segs = self._segments(adam, stats)
+        a = ExchangeArgs()
+        a.rank, a.world, a.n = f.rank, f.world, f.n_grad
+        for w in range(f.world):
+            a.grad_peer[w], a.param_peer[w], a.signal_peer[w] = f.peer_grad[w], f.peer_param[w], f.peer_signal[w]
+        a.grad_mc = f.mc_grad if self.use_multicast else None
+        a.param_mc = f.mc_param if self.use_multicast else None
+        a.exp_avg, a.exp_avg_sq = self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr()
+        a.segments, a.n_segments = segs, len(segs)
+        a.step, a.beta1, a.beta2, a.eps = max(self.step_count, 1), self.betas[0], self.betas[1], self.eps
+        with torch.cuda.device(f.device):
+            capi._check(_lib().gsr_exchange_step(ctypes.byref(a), capi._stream()))
+
+    def step(self, stats=False):
+        self.step_count += 1
+        self._launch(True, stats)
+
+    def allreduce(self, stats=False):
+        self._launch(False, stats)

@@ -79,9 +79,12 @@ class SparseGaussianAdam(torch.optim.Adam):
                 state["exp_avg_sq"] = torch.zeros_like(param, memory_format=torch.preserve_format)
             step = int(state["step"]) + 1 if "step" in state else 1
             state["step"] = torch.tensor(float(step))
-            assert param.shape[0] == N and param.is_contiguous() and param.grad.is_contiguous()
+            assert param.shape[0] == N and param.is_contiguous()
+            # on the separate_sh path the gradients of _features_dc / _features_rest are slices of the [P,16,3]
+            # gradient the rasterizer returned for torch.cat([dc, shs]) (not contiguous): pack them once
+            grad = param.grad if param.grad.is_contiguous() else param.grad.contiguous()
             v2 = lambda t: t.view(N, -1)
-            seg = dict(param=v2(param.data), grad=v2(param.grad), exp_avg=v2(state["exp_avg"]),
+            seg = dict(param=v2(param.data), grad=v2(grad), exp_avg=v2(state["exp_avg"]),
                        exp_avg_sq=v2(state["exp_avg_sq"]), lr=group["lr"])
             by_step.setdefault((step, tuple(group["betas"]), group["eps"]), []).append(seg)
         vis = visibility if visibility is None or visibility.dtype in (torch.bool, torch.uint8) else visibility != 0

@@ -43,8 +43,11 @@ def _assert_parity(rep, against_ref, name):
             assert rep[k + "_viol"] <= VIOL_FRAC * rep[k + "_size"], (name, k, rep[k + "_viol"], rep[k + "_size"])
 
 
-# fraction of a gradient tensor's entries allowed outside the elementwise bound (fp32 atomics in a different order)
-VIOL_FRAC = 0.0
+# Fraction of a gradient tensor's entries allowed outside the elementwise bound.  Measured on B200 (round 2,
+# gpurun_out/parity_worst.json): 0 entries in every small / medium case; at full size 3 of 12 M (c2 dL_drotations) and
+# at most 6 of 36 M (c4 dL_dcov3D) against the reference CUDA build, whose own fp32 atomics move as many entries
+# from run to run (tools/c4_grad_noise.py).  2e-6 allows none below 500 k entries.
+VIOL_FRAC = 2e-6
 
 
 @pytest.mark.parametrize("name", cases.SMALL_CASES + cases.ARG_CASES + cases.MEDIUM_CASES)
