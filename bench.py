@@ -3,18 +3,26 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c2|c1|c3|c4]
 
-Workload at N=1 is BASELINE.json configs[1] ("c2"): 3M SH-3 Gaussians, one 1920x1080 view, forward
-+ backward.  One "step" = one view's forward + backward (+ the NCCL gradient all-reduce when N>1:
-every rank renders its own camera of the same replicated scene, weak scaling, views/s aggregate).
-Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for what each key means.
+Workload is BASELINE.json configs[1] ("c2"): 3M SH-3 Gaussians, single-view forward + backward at 1920x1080.
+One "step" = the V = 8 views of this rank (distinct cameras), each view ALONE on one CUDA stream, one after another
+(nothing of two views overlaps), gradients summed in one flat bucket; with N > 1 ranks the step ends with the gradient
+exchange (SUM over ranks of the 59 fp32/Gaussian bucket).  Fixed work per GPU => weak scaling, `value` = views/s over all
+ranks; at N = 1 that is 1 / (single-view forward+backward time).  Prints ONE JSON line (rank 0).  DESIGN.md section 6.
 
-  value        device-timed (CUDA events around the K steps) through the C ABI, inputs resident in HBM
-  e2e          the same step through the public Python API (diff_gaussian_rasterization autograd
-               Function) with the per-step inputs (camera + target image) copied from pinned host
-               memory and the loss read back to the host inside the timed region
-  roofline     the dominant kernel (backward blend, FP32-pipe bound) + roofline_stages for every stage
-  cpu_baseline the CPU oracle (a port of the reference algorithm) on the same workload, host threads
-  --impl reference : the reference algorithm's CPU implementation (the oracle port) timed alone.
+  value            device-timed (CUDA events around the K steps) through the C ABI, inputs resident in HBM
+  e2e              the same step through the public Python API (diff_gaussian_rasterization autograd Function) with the
+                   per-view inputs (camera + target image) copied from pinned host memory and the loss read back to the
+                   host inside the timed region; `stock_autograd` = the same without the grad_sink extension (gradients
+                   returned to autograd, what the reference's unchanged train.py does)
+  with_optimizer   the step followed by the densification statistics and the Adam step (N > 1: the fused exchange kernel
+                   reduce-scatter -> sharded Adam -> all-gather; N = 1: gsr_adam_step)
+  overlapped_step  the same 8 views spread over 3 CUDA streams (gsr_b200.dist.ViewStreams)
+  c3_strong        BASELINE.json configs[2] as written: 1.8M Gaussians, 979x546, 8 views per step IN TOTAL split over the
+                   N ranks, gradient exchange every step (strong scaling), with and without the optimizer
+  roofline         the dominant kernel (backward blend, FP32-pipe bound) + roofline_stages for every stage
+  cpu_baseline     the CPU oracle (a port of the reference algorithm) on one view of the workload: all host threads, and
+                   1 thread; plus the fork's own forward-only host renderer restated (gsiron_host, 1 thread, C1)
+  --impl reference : the reference algorithm's CPU implementation (the oracle port), all host threads, one view per step.
 """
 import argparse
 import json
@@ -51,24 +59,40 @@ WORKLOADS = {
 FP32_LANES = 148 * 128 * 2     # FMA lanes x 2 flop
 
 
-def make_workload(name, cam_index=0):
+def make_workload(name, cam_index=0, n_cams=8):
+    """Scene + camera `cam_index` of an orbit of `n_cams` cameras (every rank of a run passes the same n_cams = the
+    step's global view count, so all views of a step are distinct)."""
     w = WORKLOADS[name]
     if w["kind"] == "random_init":
         scene = synth.random_init_scene(w["P"], w["seed"])
-        import cases
-        cam = cases._lego_cam(1, w["W"], w["H"])
     else:
         scene = synth.trained_like_scene(w["P"], w["seed"], s0=w["s0"], extent=w.get("extent", 1.0))
-        cam = synth.orbit_cameras(8, w["W"], w["H"], w["seed"])[cam_index % 8]
-    return w, scene, cam
+    return w, scene, make_workload_camera(name, cam_index, n_cams)
 
 
-def make_workload_camera(name, cam_index):
+def make_workload_camera(name, cam_index, n_cams=8):
     w = WORKLOADS[name]
     if w["kind"] == "random_init":
         import cases
-        return cases._lego_cam(1 + cam_index % 8, w["W"], w["H"])
-    return synth.orbit_cameras(8, w["W"], w["H"], w["seed"])[cam_index % 8]
+        return cases._lego_cam(1 + cam_index % 99, w["W"], w["H"])       # lego transforms_train.json holds 100 frames
+    n_cams = max(8, n_cams)
+    assert 0 <= cam_index < n_cams
+    return synth.orbit_cameras(n_cams, w["W"], w["H"], w["seed"])[cam_index]
+
+
+def static_config(args, world):
+    """`config` of the JSON line: a function of the command line only, so both arms (--impl ours / reference) print the
+    same object.  Measured quantities (visible Gaussians, instance counts, ...) go to `workload_stats`."""
+    w = WORKLOADS[args.workload]
+    V = max(1, args.views_per_rank)
+    return {"workload": args.workload + ": " + w["desc"], "P": w["P"], "width": w["W"], "height": w["H"],
+            "antialiasing": w["aa"], "sh_degree": 3, "views_per_rank_per_step": V, "global_views_per_step": V * world,
+            "cameras": "orbit of %d distinct cameras, rank r renders cameras r*%d .. r*%d+%d" % (max(8, V * world), V, V, V - 1),
+            "step": "each rank renders its %d views one after another on ONE CUDA stream (each view alone on the GPU: "
+                    "forward + backward, parameter gradients summed in one flat 59-fp32/Gaussian bucket)%s" % (
+                        V, "; then the gradient exchange over the %d ranks (SUM of the bucket)" % world if world > 1 else ""),
+            "parallelism": ("view-parallel dp%d, replicated Gaussians" % world) if world > 1 else "single GPU",
+            "l2": "inputs (708 MB of Gaussians at C2 + scratch per view) exceed the 126 MB L2; no flush needed"}
 
 
 def oracle_step(scene, cam, w, grads):
@@ -342,45 +366,250 @@ def loss_cpu_baseline(H, W):
             "sample": "one full [3,%d,%d] view, loss forward + backward" % (H, W)}
 
 
+def host_threads():
+    """Host threads this process may use (affinity mask), NOT OMP_NUM_THREADS: torchrun exports OMP_NUM_THREADS=1."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def run_reference(args):
-    """--impl reference: the reference algorithm's CPU implementation (oracle port), all host threads."""
+    """--impl reference: the reference algorithm's CPU implementation (oracle port), all host threads.  One step = ONE
+    view (forward + backward) of the step our arm renders -- a bounded sample of the same workload: the views of rank 0,
+    cycled -- so that K steps end within minutes; value in the same unit (views/s)."""
     rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return
     from oracle import gs_oracle as go
-    w, scene, cam = make_workload(args.workload)
+    go.set_num_threads(host_threads())      # explicit: independent of the launcher's OMP_NUM_THREADS
+    V = max(1, args.views_per_rank)
+    w, scene, cam = make_workload(args.workload, 0, V * world)
+    cams = [cam] + [make_workload_camera(args.workload, v, V * world) for v in range(1, V)]
     grads = synth.upstream_grads(w["H"], w["W"], 5)
-    for _ in range(args.warmup):
-        oracle_step(scene, cam, w, grads)
+    for k in range(args.warmup):
+        oracle_step(scene, cams[k % V], w, grads)
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        oracle_step(scene, cam, w, grads)
+    for k in range(args.steps):
+        oracle_step(scene, cams[k % V], w, grads)
     dt = time.perf_counter() - t0
     val = args.steps / dt
     cores = go.num_threads()
-    sample = "full workload: one %dx%d view of %d Gaussians, fwd+bwd per step" % (w["W"], w["H"], w["P"])
+    sample = "one %dx%d view of %d Gaussians (fwd+bwd) per step, the %d cameras of rank 0 cycled; %d OpenMP threads (OMP_NUM_THREADS in the environment was %r)" % (
+        w["W"], w["H"], w["P"], V, cores, os.environ.get("OMP_NUM_THREADS"))
     print(json.dumps({
         "impl": "reference", "metric": "fwd+bwd renders/s", "value": val, "unit": "renders/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000 * dt / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload + ": " + w["desc"]},
+        "config": static_config(args, world),
         "cpu_baseline": {"value": val, "unit": "renders/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "renders/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+class Job:
+    """This rank's share of one workload: the replicated Gaussians in the flat parameter / gradient-bucket layout, the
+    rank's V cameras, one scratch workspace per stream, and the step variants the bench times."""
+
+    def __init__(self, name, V, total_views, rank, world, dev, exchange, max_streams=3):
+        import torch
+        import torch.distributed as dist
+        from gsr_b200 import capi
+        from gsr_b200.dist import FlatGaussians, ViewStreams, DensificationStats
+        self.torch, self.dist, self.capi = torch, dist, capi
+        self.name, self.V, self.rank, self.world, self.dev, self.exchange = name, V, rank, world, dev, exchange
+        self.w, self.scene, cam0 = make_workload(name, rank * V, total_views)
+        self.cams = [cam0] + [make_workload_camera(name, rank * V + v, total_views) for v in range(1, V)]
+        w = self.w
+        t = self.t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+        self.fused = None
+        if world > 1 and exchange == "fused":
+            from gsr_b200 import exchange as ex
+            self.G = ex.SymmetricGaussians.from_numpy(self.scene, dev)
+            self.fused = ex.FusedExchange(self.G)
+        else:
+            self.G = FlatGaussians.from_numpy(self.scene, dev)
+        G = self.G
+        self.bg = torch.zeros(3, device=dev)
+        self.dcol_np, self.ddep_np = synth.upstream_grads(w["H"], w["W"], 5)
+        self.dcol, self.ddep = t(self.dcol_np), t(self.ddep_np)
+        shared = dict(means3D=G.xyz, opacities=G.opacity, background=self.bg, shs=G.shs, scales=G.scales,
+                      rotations=G.rotations, sh_degree=3, antialiasing=w["aa"])
+        self.per_view = [dict(viewmatrix=t(c.world_view_transform), projmatrix=t(c.full_proj_transform),
+                              cam_pos=t(c.camera_center), tan_fovx=c.tanfovx, tan_fovy=c.tanfovy, **shared) for c in self.cams]
+        # every gradient output is a persistent tensor: the five parameter gradients are views of the exchange bucket,
+        # the per-view intermediates (means2D, conic, ...) one scratch set per stream
+        self.grad_views = G.grad_views()
+        P = w["P"]
+        e = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)
+        self.view_scratch = [dict(dL_dmeans2D=e(P, 3), dL_dconic=e(P, 2, 2), dL_dcolors=e(P, 3), dL_dinvdepths=e(P, 1),
+                                  dL_dcov3D=e(P, 6), **self.grad_views) for _ in range(max_streams)]
+        self.spaces = [capi.Workspace(dev) for _ in range(max_streams)]
+        self.streams = {1: ViewStreams(dev, 1), max_streams: ViewStreams(dev, max_streams)}
+        self.stats = DensificationStats(P, dev)
+        self.adam = None
+        self.last_state = None
+
+    # ---- one view / one step ------------------------------------------------------------------------------
+    def _fwd(self, v, slot):
+        return self.capi.forward(width=self.w["W"], height=self.w["H"], workspace=self.spaces[slot], **self.per_view[v])
+
+    def _bwd(self, v, st, acc, slot):
+        return self.capi.backward(st, dL_dcolor=self.dcol, dL_dinvdepth=self.ddep, out=self.view_scratch[slot],
+                                  accumulate=acc, **self.per_view[v])
+
+    def render_views(self, n_streams=1, with_stats=False):
+        """The rank's V views: forward + backward each, the first backward overwrites the bucket, the others add."""
+        S = n_streams
+
+        def bwd(v, st, acc):
+            g = self._bwd(v, st, acc, v % S)
+            if with_stats:       # densification statistics of this view (train.py:166-167), step-local deltas
+                acc_d, den_d, rad_d = self._stat_deltas()
+                self.capi.densification_stats(g["dL_dmeans2D"], st["radii"], acc_d, den_d, rad_d)
+            return g
+        out = self.streams[S].run(self.V, lambda v: self._fwd(v, v % S), bwd)
+        self.last_state = out[0]
+        return out
+
+    def _stat_deltas(self):
+        if self.fused is not None:
+            return self.G.stat_views()
+        return self.stats._d_accum, self.stats._d_denom, self.stats._d_radii
+
+    def exchange_gradients(self):
+        """SUM of the bucket over ranks, nothing else (the step `value` times)."""
+        if self.world == 1:
+            return
+        if self.fused is not None:
+            self.fused.allreduce()
+        else:
+            self.dist.all_reduce(self.G.bucket, op=self.dist.ReduceOp.SUM)
+
+    def step_render(self, n_streams=1):
+        self.render_views(n_streams)
+        self.exchange_gradients()
+
+    def step_train(self, n_streams=1):
+        """Render + statistics + optimizer: what train.py:163-186 does after the backward, for the whole step."""
+        torch = self.torch
+        self.render_views(n_streams, with_stats=True)
+        if self.fused is not None:
+            self.fused.step(stats=True)             # reduce-scatter -> sharded Adam -> all-gather, + SUM / MAX statistics
+            acc_d, den_d, rad_d = self.G.stat_views()
+            st = self.stats
+            st.xyz_gradient_accum += acc_d
+            st.denom += den_d
+            torch.maximum(st.max_radii2D, rad_d, out=st.max_radii2D)
+            self.G.grad_all[self.G.n_param:].zero_()
+        else:
+            if self.world > 1:
+                self.dist.all_reduce(self.G.bucket, op=self.dist.ReduceOp.SUM)
+            if self.adam is None:
+                from gsr_b200.optim import GaussianAdam
+                self.adam = GaussianAdam(self.G)
+            self.adam.step()
+            self.stats.allreduce()
+
+    def save_params(self):
+        return self.G.params.clone()
+
+    def restore_params(self, saved):
+        self.G.params.copy_(saved)
+
+
+def time_steps(torch, dist, dev, world, step_fn, steps, warmup, min_warm_s=1.5):
+    """W >= warmup untimed steps (and at least min_warm_s of them: a freshly leased GPU ramps clocks and grows
+    allocator pools during its first second), then EXACTLY `steps` steps between barrier + synchronize on both sides;
+    CUDA events on the launching stream, MAX over ranks.  Returns (total ms, sorted per-step ms, warm-up steps run)."""
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    n_warm, t0 = 0, time.perf_counter()
+    while True:
+        step_fn()
+        n_warm += 1
+        if n_warm >= warmup and (n_warm - warmup) % 4 == 0:
+            torch.cuda.synchronize()
+            # each step may hold a collective: all ranks leave after the same count (MAX of "I want more")
+            more = (time.perf_counter() - t0 < min_warm_s) and n_warm < 4000
+            if world > 1:
+                flag = torch.tensor([1.0 if more else 0.0], device=dev)
+                dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+                more = bool(flag.item() > 0)
+            if not more:
+                break
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+    barrier()
+    ev[0].record()
+    for k in range(steps):
+        step_fn()
+        ev[k + 1].record()
+    barrier()
+    ms = ev[0].elapsed_time(ev[steps])
+    per = sorted(ev[k].elapsed_time(ev[k + 1]) for k in range(steps))
+    if world > 1:
+        tms = torch.tensor([ms], device=dev)
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        ms = float(tms.item())
+    return ms, per, n_warm
+
+
+def newest_traffic(workload):
+    """DRAM bytes per launch from the newest committed `ncu --set full` capture of this workload: the highest round in
+    the file name (profiles/rNN_*traffic*.json), ties by modification time."""
+    import glob
+    import re
+    best = None
+    for tf in glob.glob(os.path.join(ROOT, "profiles", "*traffic*.json")):
+        try:
+            with open(tf) as f:
+                tj = json.load(f)
+        except (OSError, ValueError):
+            continue
+        if tj.get("workload") != workload:
+            continue
+        m = re.match(r"r(\d+)", os.path.basename(tf))
+        key = (int(m.group(1)) if m else -1, os.path.getmtime(tf))
+        if best is None or key > best[0]:
+            best = (key, tf, tj)
+    return (best[1], best[2]) if best else (None, None)
+
+
+def gsiron_host_row():
+    """the fork's own forward-only host renderer (GS-IRON/npu-1/base.cpp:209-433), restated without
+    Eigen / OpenCV in oracle/gsiron_host.c, single-threaded by construction, on workload C1 with the chair camera."""
+    from oracle import gsiron_host as gh
+    w = WORKLOADS["c1"]
+    scene = synth.random_init_scene(w["P"], w["seed"])
+    gh.render({k: (v[:2000] if hasattr(v, "shape") else v) for k, v in scene.items()}, w["W"], w["H"])    # warm (library load)
+    t0 = time.perf_counter()
+    img, info = gh.render(scene, w["W"], w["H"])
+    dt = time.perf_counter() - t0
+    return {"value": 1.0 / dt, "unit": "renders/s (forward only)", "cores": 1, "kind": "port", "ms": dt * 1e3,
+            "sample": "C1: %d random-init Gaussians, 800x800, hard-coded chair camera of base.cpp:453-457, forward only; "
+                      "not parity-comparable with the rasterizer (+0.5 px sample offset, flipped view direction, no tan_fov clamp)" % w["P"],
+            "instances": info["instances"], "image_mean": float(img.mean())}
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true")
+    ap.add_argument("--no-c3", action="store_true", help="skip the BASELINE configs[2] strong-scaling leg")
+    ap.add_argument("--no-extras", action="store_true", help="skip the loss / frame / optimizer stage reports")
+    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
+                    help="gradient exchange at N > 1: this library's kernel over NVLink peer / multicast memory, or ncclAllReduce")
     ap.add_argument("--streams", type=int, default=3,
-                    help="CUDA streams the views of a step are spread over (gsr_b200.dist.ViewStreams)")
+                    help="CUDA streams of the `overlapped_step` leg (gsr_b200.dist.ViewStreams); `value` always uses one")
     ap.add_argument("--views-per-rank", type=int, default=8,
-                    help="views every rank renders per step (gradients accumulate in the bucket; one all-reduce per step)")
+                    help="views every rank renders per step (gradients accumulate in the bucket; one exchange per step)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -406,115 +635,77 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     V = max(1, args.views_per_rank)
-    # this rank's slice of the step's camera batch: V views, global view index rank*V + v
-    w, scene, cam = make_workload(args.workload, cam_index=rank * V)
-    cams = [cam] + [make_workload_camera(args.workload, rank * V + v) for v in range(1, V)]
+    S = max(1, args.streams)
+    job = Job(args.workload, V, V * world, rank, world, dev, args.exchange, max_streams=S)
+    w, G = job.w, job.G
     W, H, P = w["W"], w["H"], w["P"]
-    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
-    # replicated Gaussians, resident in HBM; parameters live in one flat [P,59] gradient-bucket layout
-    from gsr_b200.dist import FlatGaussians
-    G = FlatGaussians.from_numpy(scene, dev)
-    bg = torch.zeros(3, device=dev)
-    dcol_np, ddep_np = synth.upstream_grads(H, W, 5)
-    dcol, ddep = t(dcol_np), t(ddep_np)
-    shared = dict(means3D=G.xyz, opacities=G.opacity, background=bg, shs=G.shs, scales=G.scales, rotations=G.rotations,
-                  sh_degree=3, antialiasing=w["aa"])
-    per_view = [dict(viewmatrix=t(c.world_view_transform), projmatrix=t(c.full_proj_transform), cam_pos=t(c.camera_center),
-                     tan_fovx=c.tanfovx, tan_fovy=c.tanfovy, **shared) for c in cams]
-    common = per_view[0]
+    warm = max(args.warmup, 3)
 
-    grad_views = G.grad_views()     # the backward kernels write straight into the all-reduce bucket
-
-    from gsr_b200.dist import ViewStreams
-    view_streams = ViewStreams(dev, args.streams)
-    # one growth-only scratch set per stream (a view's backward follows its forward on the same stream, so one live
-    # state per stream): the binning buffer's size changes with every view, and per-call sizing lets the caching
-    # allocator split / merge / occasionally cudaMalloc inside the timed region
-    spaces = [capi.Workspace(dev) for _ in range(max(1, args.streams))]
-
-    def abi_step():
-        # one step = this rank's V views: the first backward overwrites the bucket, the others add into it
-        return view_streams.run(
-            V, lambda v: capi.forward(width=W, height=H, workspace=spaces[v % len(spaces)], **per_view[v]),
-            lambda v, st, acc: capi.backward(st, dL_dcolor=dcol, dL_dinvdepth=ddep, out=grad_views, accumulate=acc, **per_view[v]))
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    # ---------------- device-timed leg (C ABI, inputs resident) ----------------
+    # ---------------- device-timed leg (C ABI, inputs resident): each view alone on one stream ----------------
     sampler = ClockSampler(local_rank)
     sampler.start()
     time.sleep(0.2)
-    # warm-up: at least W (>= 3) steps AND at least ~1.5 s of work -- on a freshly leased box the first
-    # second after context creation (clock/power-state ramp, allocator growth, lazy module loads) ran
-    # up to 2x slower than steady state, which a 3-step warm-up of a 3 ms step does not cover
-    n_warm, t_w0 = 0, time.perf_counter()
-    while True:
-        st, g = abi_step()
-        if world > 1:
-            G.allreduce_from(g)
-        n_warm += 1
-        if n_warm % 8 == 0 or n_warm == max(args.warmup, 3):
-            torch.cuda.synchronize()
-            # every rank must leave the loop after the same number of steps (each step holds a collective):
-            # the decision is rank-agreed through a MAX all-reduce of "I still want to warm up"
-            more = n_warm < max(args.warmup, 3) or (time.perf_counter() - t_w0 < 1.5 and n_warm < 2000)
-            if world > 1:
-                flag = torch.tensor([1.0 if more else 0.0], device=dev)
-                dist.all_reduce(flag, op=dist.ReduceOp.MAX)
-                more = bool(flag.item() > 0)
-            if not more:
-                break
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    step_ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
-    barrier()
-    e0.record()
-    step_ev[0].record()
-    for k in range(args.steps):
-        st, g = abi_step()
-        if world > 1:
-            G.allreduce_from(g)
-        step_ev[k + 1].record()
-    e1.record()
-    barrier()
-    ms = e0.elapsed_time(e1)
-    step_ms = sorted(step_ev[k].elapsed_time(step_ev[k + 1]) for k in range(args.steps))
+    ms, step_ms, n_warm = time_steps(torch, dist, dev, world, lambda: job.step_render(1), args.steps, warm)
     clocks = sampler.stop()
-    if world > 1:
-        tms = torch.tensor([ms], device=dev)
-        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
-        ms = float(tms.item())
     value = world * V * args.steps / (ms / 1000.0)
+    st = job.last_state
     N = st["num_rendered"]
 
-    # ---------------- single-view latency: view 0 alone, one stream, write mode (BASELINE configs[1]) ----------------
+    # the exchange alone (N > 1): device time of one SUM over ranks of the bucket, both implementations
+    exchange_ms = None
+    if world > 1:
+        exchange_ms = {}
+        G.bucket.zero_()            # repeated in-place sums of the same buffer must not run into inf
+        ex_ms, _, _ = time_steps(torch, dist, dev, world, job.exchange_gradients, 20, 3, min_warm_s=0.0)
+        exchange_ms[args.exchange] = ex_ms / 20
+        nccl_ms, _, _ = time_steps(torch, dist, dev, world, lambda: dist.all_reduce(G.bucket), 20, 3, min_warm_s=0.0)
+        exchange_ms["nccl_allreduce"] = nccl_ms / 20
+        exchange_ms["bytes"] = int(G.bucket.numel() * 4)
+
+    # ---------------- the same views overlapped on S streams (own key; not `value`) ----------------
+    ov_ms, ov_steps, _ = time_steps(torch, dist, dev, world, lambda: job.step_render(S), args.steps, warm, min_warm_s=0.3)
+    overlapped = {"streams": S, "value": world * V * args.steps / (ov_ms / 1000.0), "unit": "renders/s",
+                  "ms_per_step": ov_ms / args.steps, "ms_per_view": ov_ms / args.steps / V,
+                  "what": "the same step with view v on CUDA stream v %% %d (gsr_b200.dist.ViewStreams): the latency-bound "
+                          "stages of one view run under the blend kernels of its neighbours" % S}
+
+    # ---------------- with the optimizer: render + densification statistics + Adam (+ exchange) ----------------
+    saved = job.save_params()
+    op_ms, _, _ = time_steps(torch, dist, dev, world, lambda: job.step_train(1), args.steps, warm, min_warm_s=0.3)
+    job.restore_params(saved)
+    del saved
+    with_optimizer = {"value": world * V * args.steps / (op_ms / 1000.0), "unit": "renders/s", "ms_per_step": op_ms / args.steps,
+                      "what": ("views as in `value`, each followed by the fused densification-statistics update; then ONE fused exchange kernel per rank: "
+                               "reduce-scatter of the bucket -> Adam on the rank's 1/%d shard -> all-gather of the parameters, + SUM/MAX of the statistics" % world)
+                      if job.fused is not None else
+                      "views as in `value`, each followed by the fused densification-statistics update; then %sgsr_adam_step over all rows" % (
+                          "ncclAllReduce of the bucket + 3 statistic all-reduces + " if world > 1 else "")}
+
+    # ---------------- single view, isolated: synchronise before and after every view (latency) ----------------
     sv_ms = []
-    for _ in range(12):
+    for k in range(12):
         a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
         a_.record()
-        st = capi.forward(width=W, height=H, **per_view[0])
-        capi.backward(st, dL_dcolor=dcol, dL_dinvdepth=ddep, out=grad_views, **per_view[0])
+        st0 = job._fwd(0, 0)
+        job._bwd(0, st0, False, 0)
         b_.record()
         torch.cuda.synchronize()
         sv_ms.append(a_.elapsed_time(b_))
     single_view_ms = float(np.median(sv_ms[2:]))
 
     # ---------------- per-stage device times (profiling mode, separate pass) ----------------
+    per_view, dcol, ddep, grad_views = job.per_view, job.dcol, job.ddep, job.grad_views
     capi.set_profiling(True)
     stage = {}
-    for _ in range(3):      # view 0 of this rank, write mode: the single-view fwd+bwd the roofline figures describe
-        st = capi.forward(width=W, height=H, **per_view[0])
-        fwd_t = capi.stage_times_ms()
-        g = capi.backward(st, dL_dcolor=dcol, dL_dinvdepth=ddep, out=grad_views, **per_view[0])
+    for _ in range(5):      # view 0 of this rank, write mode: the single-view fwd+bwd the roofline figures describe
+        st = job._fwd(0, 0)
+        g = job._bwd(0, st, False, 0)
         for k, v in capi.stage_times_ms().items():
             stage.setdefault(k, []).append(v)
     acc_ms = []
     for _ in range(3):      # the same view once more in accumulate mode (views 2..V of a step)
-        capi.backward(st, dL_dcolor=dcol, dL_dinvdepth=ddep, out=grad_views, accumulate=True, **per_view[0])
+        job._bwd(0, st, True, 0)
         acc_ms.append(capi.stage_times_ms()["preprocess_bwd"])
     capi.set_profiling(False)
     stage_ms = {k: float(np.median(v)) for k, v in stage.items()}
@@ -522,8 +713,11 @@ def main():
     it = capi.introspect(st)
     pairs_bwd_eval = int(it["n_contrib"].to(torch.int64).sum().item())
     P_vis = int((st["radii"] > 0).sum().item())
+    radii0 = st["radii"].clone()
 
     # ---------------- e2e leg: public Python API, host inputs, loss read back ----------------
+    cams = job.cams
+    bg = job.bg
     rs_kw = dict(image_height=H, image_width=W, bg=bg, scale_modifier=1.0,
                  sh_degree=3, prefiltered=False, debug=False, antialiasing=w["aa"])
     from diff_gaussian_rasterization import grad_sink
@@ -532,13 +726,13 @@ def main():
     target_host = [torch.from_numpy(rng9.random((3, H, W), dtype=np.float32)).pin_memory() for _ in range(min(V, 2))]
     cam_host = [torch.from_numpy(np.concatenate([c.world_view_transform.ravel(), c.full_proj_transform.ravel(),
                                                  c.camera_center.ravel()]).astype(np.float32)).pin_memory() for c in cams]
-    NB = max(2, args.streams)                                                # one input buffer per view in flight
+    NB = 2                                                                   # one input buffer per view in flight
     target_dev = [torch.empty(3, H, W, device=dev) for _ in range(NB)]       # double-buffered: the copy of view v+1
-    cam_dev = [torch.empty(35, device=dev) for _ in range(NB)]              # may run under view v's kernels
+    cam_dev = [torch.empty(35, device=dev) for _ in range(NB)]              # runs under view v's kernels
     params = G.as_leaf_params()
     loss_host = torch.empty(1).pin_memory()
     loss_dev = torch.zeros(1, device=dev)
-    loss_slots = torch.zeros(V, 1, device=dev)              # one slot per view: views on different streams never share a word
+    loss_slots = torch.zeros(V, 1, device=dev)
     copy_stream = torch.cuda.Stream(device=dev)
     uploaded = [torch.cuda.Event() for _ in range(NB)]
     buf_free = [torch.cuda.Event() for _ in range(NB)]
@@ -547,80 +741,107 @@ def main():
     sink = (grad_views["dL_dmeans3D"], grad_views["dL_dsh"], grad_views["dL_dopacity"], grad_views["dL_dscales"],
             grad_views["dL_drotations"])
 
-    def api_step():
-        """One training-step's worth of rendering through the public API: for each of this rank's V views the camera
-        and the target image come from pinned host memory, GaussianRasterizer renders, the training loss (0.8 L1 + 0.2 D-SSIM, fused) is taken and
-        backpropagated; parameter gradients of the V views add up in the flat bucket (grad_sink), which is
-        all-reduced over ranks; the step's loss is read back to the host."""
+    def api_step(use_sink):
+        """One step through the public API: for each of this rank's V views the camera and the target image come from
+        pinned host memory (copy stream, double-buffered), GaussianRasterizer renders, the training loss
+        0.8 L1 + 0.2 D-SSIM (fused) is taken and backpropagated.  use_sink: parameter gradients of the V views add up in
+        the flat bucket inside the backward kernels (grad_sink extension).  Otherwise the STOCK autograd path: gradients
+        are returned and summed into .grad by AccumulateGrad, exactly what the reference's unchanged train.py gets;
+        with N > 1 they are then packed into the bucket, exchanged and unpacked.  The step's loss is read back."""
         main = torch.cuda.current_stream()
 
-        def upload(v):      # H2D of view v's camera + target on the copy stream, into buffer v % NB
-            copy_stream.wait_event(buf_free[v % NB])          # the view that last used this buffer is done with it
+        def upload(v):
+            copy_stream.wait_event(buf_free[v % NB])
             with torch.cuda.stream(copy_stream):
                 cam_dev[v % NB].copy_(cam_host[v], non_blocking=True)
                 target_dev[v % NB].copy_(target_host[v % len(target_host)], non_blocking=True)
                 uploaded[v % NB].record(copy_stream)
 
         upload(0)
-        streams = [main] + view_streams.side                 # view v runs on stream v % S (gsr_b200.dist.ViewStreams)
-        if len(streams) > 1:
-            start = torch.cuda.Event()
-            start.record(main)
-            for s_ in streams[1:]:
-                s_.wait_event(start)
-        first_done = None
         for v in range(V):
             cd, td = cam_dev[v % NB], target_dev[v % NB]
-            sv = streams[v % len(streams)]
-            sv.wait_event(uploaded[v % NB])
+            main.wait_event(uploaded[v % NB])
             if v + 1 < V:
-                upload(v + 1)                                 # travels while this view renders
-            with torch.cuda.stream(sv):
-                rs = GaussianRasterizationSettings(viewmatrix=cd[0:16].view(4, 4), projmatrix=cd[16:32].view(4, 4),
-                                                   campos=cd[32:35], tanfovx=cams[v].tanfovx, tanfovy=cams[v].tanfovy, **rs_kw)
-                means2D = torch.zeros_like(params["xyz"], requires_grad=True)
-                color, radii, invd = GaussianRasterizer(rs)(means3D=params["xyz"], means2D=means2D, opacities=params["opacity"],
-                                                            shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
-                loss = l1_ssim_loss(color, td, 0.2)           # train.py:118-126, two fused launches
-                if v > 0 and sv is not main and first_done is not None:
-                    sv.wait_event(first_done)                 # view 0's backward overwrites the bucket: add only after it
+                upload(v + 1)
+            rs = GaussianRasterizationSettings(viewmatrix=cd[0:16].view(4, 4), projmatrix=cd[16:32].view(4, 4),
+                                               campos=cd[32:35], tanfovx=cams[v].tanfovx, tanfovy=cams[v].tanfovy, **rs_kw)
+            means2D = torch.zeros_like(params["xyz"], requires_grad=True)
+            color, radii, invd = GaussianRasterizer(rs)(means3D=params["xyz"], means2D=means2D, opacities=params["opacity"],
+                                                        shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
+            loss = l1_ssim_loss(color, td, 0.2)
+            if use_sink:
                 with grad_sink(*sink, accumulate=(v > 0)):
                     loss.backward()
-                if v == 0 and len(streams) > 1:
-                    first_done = torch.cuda.Event()
-                    first_done.record(sv)
-                loss_slots[v].copy_(loss.detach().reshape(1))
-                buf_free[v % NB].record(sv)
-        for s_ in streams[1:]:
-            done = torch.cuda.Event()
-            done.record(s_)
-            main.wait_event(done)
+            else:
+                loss.backward()
+            loss_slots[v].copy_(loss.detach().reshape(1))
+            buf_free[v % NB].record(main)
         loss_dev.copy_(loss_slots.sum().reshape(1))
-        if world > 1:
-            dist.all_reduce(G.bucket, op=dist.ReduceOp.SUM)
+        if use_sink:
+            job.exchange_gradients()
+        else:
+            G.allreduce_param_grads(params)
+            for p_ in params.values():
+                p_.grad = None                       # optimizer.zero_grad(set_to_none=True), train.py:186
         loss_host.copy_(loss_dev, non_blocking=True)
         torch.cuda.current_stream().synchronize()
         return float(loss_host[0])
 
-    for _ in range(max(args.warmup, 5)):                    # the first steps of this leg grow the autograd path's buffers
-        api_step()
-    barrier()
-    t0 = time.perf_counter()
-    e0.record()
-    step_loss = None
-    for _ in range(args.steps):
-        step_loss = api_step()
-    e1.record()
-    barrier()
-    wall = time.perf_counter() - t0
-    e2e_ms = max(e0.elapsed_time(e1), wall * 1000.0)
-    if world > 1:
-        tms = torch.tensor([e2e_ms], device=dev)
-        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
-        e2e_ms = float(tms.item())
+    def time_api(use_sink):
+        def barrier():
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+        for _ in range(max(warm, 5)):
+            api_step(use_sink)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        loss_ = None
+        for _ in range(args.steps):
+            loss_ = api_step(use_sink)
+        e1.record()
+        barrier()
+        wall = time.perf_counter() - t0
+        ms_ = max(e0.elapsed_time(e1), wall * 1000.0)
+        if world > 1:
+            tms = torch.tensor([ms_], device=dev)
+            dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+            ms_ = float(tms.item())
+        return ms_, loss_
+
+    e2e_ms, step_loss = time_api(True)
+    bucket_checksum = float(G.bucket.double().abs().sum().item())
+    stock_ms, stock_loss = time_api(False)
     e2e_val = world * V * args.steps / (e2e_ms / 1000.0)
+    stock_val = world * V * args.steps / (stock_ms / 1000.0)
     h2d = V * (target_host[0].numel() * 4 + cam_host[0].numel() * 4)
     d2h = 4 + 12 * V    # the step's loss + the 12-byte instance/visible counts of every forward
+    del params, target_dev
+
+    # ---------------- BASELINE configs[2] as written: C3, 8 views per step in total, split over the ranks ----------------
+    c3 = None
+    if not args.no_c3 and args.workload == "c2" and 8 % world == 0:
+        torch.cuda.empty_cache()
+        j3 = Job("c3", 8 // world, 8, rank, world, dev, args.exchange, max_streams=S)
+        r_ms, _, _ = time_steps(torch, dist, dev, world, lambda: j3.step_render(1), args.steps, warm, min_warm_s=0.5)
+        saved = j3.save_params()
+        t_ms, _, _ = time_steps(torch, dist, dev, world, lambda: j3.step_train(1), args.steps, warm, min_warm_s=0.3)
+        j3.restore_params(saved)
+        o_ms, _, _ = time_steps(torch, dist, dev, world, lambda: j3.step_render(S), args.steps, warm, min_warm_s=0.3)
+        c3 = {"workload": "c3: " + WORKLOADS["c3"]["desc"] + "; 8 views per step IN TOTAL, %d per rank, gradient exchange every step" % (8 // world),
+              "scaling": "strong", "n_gpus": world, "views_per_step": 8, "exchange": args.exchange if world > 1 else None,
+              "value": 8 * args.steps / (r_ms / 1000.0), "unit": "views/s", "ms_per_step": r_ms / args.steps,
+              "with_optimizer": {"value": 8 * args.steps / (t_ms / 1000.0), "ms_per_step": t_ms / args.steps},
+              "overlapped_%d_streams" % S: {"value": 8 * args.steps / (o_ms / 1000.0), "ms_per_step": o_ms / args.steps},
+              "bucket_bytes": int(j3.G.bucket.numel() * 4), "num_rendered_last_view": j3.last_state["num_rendered"]}
+        if world > 1:
+            j3.G.bucket.zero_()
+            x_ms, _, _ = time_steps(torch, dist, dev, world, j3.exchange_gradients, 20, 3, min_warm_s=0.0)
+            c3["exchange_ms"] = x_ms / 20
+        del j3, saved
+        torch.cuda.empty_cache()
 
     out = None
     if rank == 0:
@@ -636,15 +857,26 @@ def main():
         fp32_peak_max = FP32_LANES * 1.965e9 / 1e12
         fp32_peak_clk = FP32_LANES * sm_mhz * 1e6 / 1e12
 
-        # ---------------- CPU baseline (oracle port), bounded sample = one full view ----------------
+        # ---------------- CPU baselines (bounded samples), N = 1 only ----------------
         cpu = None
         pairs_eval = pairs_blend = None
         if not args.no_cpu_baseline and world == 1:
             from oracle import gs_oracle as go
-            sec, f = oracle_step(scene, cam, w, (dcol_np, ddep_np))
+            go.set_num_threads(host_threads())
+            sec, f = oracle_step(job.scene, cams[0], w, (job.dcol_np, job.ddep_np))
             pairs_eval, pairs_blend = f["pairs_evaluated"], f["pairs_blended"]
             cpu = {"value": 1.0 / sec, "unit": "renders/s", "cores": go.num_threads(), "kind": "port",
                    "sample": "one full %dx%d view of %d Gaussians, fwd+bwd, %.1f s" % (W, H, P, sec)}
+            try:
+                go.set_num_threads(1)
+                sec1, _ = oracle_step(job.scene, cams[0], w, (job.dcol_np, job.ddep_np))
+                cpu["one_core"] = {"value": 1.0 / sec1, "unit": "renders/s", "cores": 1, "sample": "the same view, 1 thread, %.1f s" % sec1}
+            finally:
+                go.set_num_threads(host_threads())
+            try:
+                cpu["gsiron_host"] = gsiron_host_row()
+            except Exception as exc:  # informational row
+                cpu["gsiron_host"] = {"error": str(exc)[:300]}
 
         # binning = depth sort of the P_vis visible Gaussians (32 key bits -> 4 onesweep passes on 32-bit
         # key/value pairs) + stable tile-id sort of the N instances (tile_bits -> tile_passes passes)
@@ -661,7 +893,7 @@ def main():
             "duplicate": hbm(40 * P_vis + 8 * N, stage_ms.get("duplicate")),             # sorted scan + emit (32-bit key + value out)
             "sort": hbm(4 * N + tile_passes * 16 * N, stage_ms.get("sort")),
             "ranges": hbm(8 * N + 8 * ((W + 15) // 16) * ((H + 15) // 16), stage_ms.get("ranges")),
-            "preprocess_bwd": hbm(504 * P_vis + 304 * (P - P_vis) * 0 + 236 * P, stage_ms.get("preprocess_bwd")),
+            "preprocess_bwd": hbm(504 * P_vis + 236 * P, stage_ms.get("preprocess_bwd")),
         }
         def fp32(flop, ms_):
             a = flop / (ms_ / 1e3) / 1e12 if ms_ and ms_ > 0 and flop else None
@@ -674,50 +906,43 @@ def main():
         else:
             stages["render_fwd"] = fp32(None, stage_ms.get("render_fwd"))
             stages["render_bwd"] = fp32(None, stage_ms.get("render_bwd"))
-        # measured DRAM traffic per launch from the newest committed `ncu --set full` capture of this workload
-        import glob
-        for tf in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json")), reverse=True):
-            with open(tf) as f:
-                tj = json.load(f)
-            if tj.get("workload") == args.workload:
-                for k_, v_ in tj["traffic_bytes"].items():
-                    if k_ in stages:
-                        stages[k_]["traffic"] = v_
-                        stages[k_]["traffic_source"] = "profiles/" + os.path.basename(tf)
-                break
+        tf, tj = newest_traffic(args.workload)
+        if tj:
+            for k_, v_ in tj["traffic_bytes"].items():
+                if k_ in stages:
+                    stages[k_]["traffic"] = v_
+                    stages[k_]["traffic_source"] = "profiles/" + os.path.basename(tf)
         dominant = max(stage_ms, key=lambda k: stage_ms[k] if k not in ("host_sync", "preprocess_bwd_accumulate") else -1)
         roof = dict(stages.get(dominant, {}))
         roof["kernel"] = dominant
         roof.setdefault("traffic", None)
 
         # preprocess, scan_compact, depth sort (hist + 4), sorted_scan, emit_tiles, tile sort (hist + passes),
-        # tile_ranges, render_fwd, render_bwd, preprocess_bwd
-        launches_per_step = 1 + 1 + (1 + 4) + 1 + 1 + (1 + tile_passes) + 1 + 1 + 1 + 1
+        # tile_ranges, render_fwd, render_bwd, preprocess_bwd; + the exchange kernel per step when N > 1 (fused)
+        launches_per_view = 1 + 1 + (1 + 4) + 1 + 1 + (1 + tile_passes) + 1 + 1 + 1 + 1
+        launches_per_step = launches_per_view * V + (1 if job.fused is not None else 0)
         out = {
             "metric": "fwd+bwd renders/s", "value": value, "unit": "renders/s", "n_gpus": world, "steps": args.steps,
-            "warmup": n_warm, "ms_per_step": ms / args.steps, "ms_per_view": ms / args.steps / V,
+            "warmup": args.warmup, "warmup_steps_run": n_warm, "ms_per_step": ms / args.steps, "ms_per_view": ms / args.steps / V,
             "step_ms": {"min": step_ms[0], "median": step_ms[len(step_ms) // 2], "max": step_ms[-1]}, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload + ": " + w["desc"], "P": P, "P_visible": P_vis, "num_rendered": N,
-                       "width": W, "height": H, "pairs_evaluated_fwd": pairs_eval, "pairs_blended": pairs_blend,
-                       "pairs_evaluated_bwd": pairs_bwd_eval, "l2": "inputs (708 MB of Gaussians + scratch) exceed the 126 MB L2",
-                       "views_per_rank_per_step": V, "global_views_per_step": V * world, "streams": args.streams,
-                       "step": "each rank renders its %d views (fwd+bwd, parameter gradients accumulated in one flat bucket), view v on CUDA stream v %% %d%s" % (
-                           V, max(1, args.streams), ", then ONE NCCL all-reduce of the 59 fp32/Gaussian bucket" if world > 1 else ""),
-                       "roofline_view": "stage times / roofline figures are of view 0 alone on one stream (single-view fwd+bwd, write mode)",
-                       "parallelism": "view-parallel dp%d, replicated Gaussians, NCCL all-reduce of 59 fp32/Gaussian" % world
-                       if world > 1 else "single GPU", "peak_source": peak_src},
+            "config": static_config(args, world),
+            "workload_stats": {"P_visible": P_vis, "num_rendered": N, "pairs_evaluated_fwd": pairs_eval, "pairs_blended": pairs_blend,
+                               "pairs_evaluated_bwd": pairs_bwd_eval, "peak_source": peak_src, "exchange": args.exchange if world > 1 else None,
+                               "roofline_view": "stage times / roofline figures are of view 0 of rank 0 alone (single-view fwd+bwd, write mode)"},
             "clocks": clocks,
             "e2e": {"value": e2e_val, "unit": "renders/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": e2e_ms / args.steps, "step_loss": step_loss,
-                    "bucket_checksum": float(G.bucket.double().abs().sum().item()),
-                    "what": "per view: camera + target image from pinned host memory (copy stream, double-buffered, overlapping the previous view's kernels), GaussianRasterizer autograd fwd+bwd + the fused training loss 0.8*L1 + 0.2*(1-SSIM) (fused_ssim.l1_ssim_loss); per step: gradients of the rank's views summed in the bucket (grad_sink), all-reduce when N>1, loss read back"},
-            "gpu_launches": launches_per_step * V * args.steps,
-            "single_view": {"fwd_bwd_ms": single_view_ms, "renders_per_s": 1000.0 / single_view_ms,
-                            "what": "one view alone on one stream, forward + backward through the C ABI, inputs resident (latency; `value` is the throughput of the 8-view step)"},
+                    "ms_per_step": e2e_ms / args.steps, "step_loss": step_loss, "bucket_checksum": bucket_checksum,
+                    "what": "per view: camera + target image from pinned host memory (copy stream, double-buffered, overlapping the previous view's kernels), GaussianRasterizer autograd fwd+bwd + the fused training loss 0.8*L1 + 0.2*(1-SSIM) (fused_ssim.l1_ssim_loss), views one after another on one stream; per step: gradients of the rank's views summed in the bucket by the backward kernels (grad_sink), exchange when N>1, loss read back",
+                    "stock_autograd": {"value": stock_val, "unit": "renders/s", "ms_per_step": stock_ms / args.steps, "step_loss": stock_loss,
+                                       "what": "the same without grad_sink: the unchanged reference API, gradients returned to autograd and summed into .grad by AccumulateGrad (what the reference's train.py does), .grad dropped per step"}},
+            "gpu_launches": launches_per_step * args.steps,
+            "single_view_isolated": {"fwd_bwd_ms": single_view_ms, "renders_per_s": 1000.0 / single_view_ms,
+                                     "what": "one view, synchronised before and after (launch ramp included): latency, not throughput"},
+            "overlapped_step": overlapped, "with_optimizer": with_optimizer, "exchange_ms": exchange_ms, "c3_strong": c3,
             "stage_ms": stage_ms, "roofline": roof, "roofline_stages": stages, "cpu_baseline": cpu,
         }
-        if world == 1:
+        if world == 1 and not args.no_extras:
             out["loss_stage"] = loss_stage_report(dev, H, W, hbm_peak)
             if not args.no_cpu_baseline:
                 out["loss_stage"]["cpu_baseline"] = loss_cpu_baseline(H, W)
@@ -726,7 +951,7 @@ def main():
             except Exception as exc:  # informational leg only
                 out["frame_stage"] = {"error": str(exc)[:300]}
             try:
-                out["optimizer_stage"] = optimizer_stage_report(G, st["radii"], hbm_peak)
+                out["optimizer_stage"] = optimizer_stage_report(G, radii0, hbm_peak)
             except Exception as exc:  # informational leg only
                 out["optimizer_stage"] = {"error": str(exc)[:300]}
         # same-box bar: the unmodified reference CUDA kernels (oracle/_ref), informational
@@ -734,6 +959,7 @@ def main():
             try:
                 from oracle import ref_cuda
                 if ref_cuda.available():
+                    common = per_view[0]
                     R = ref_cuda.RefRasterizer()
                     for _ in range(2):
                         f = R.forward(width=W, height=H, **common)
@@ -741,16 +967,16 @@ def main():
                     torch.cuda.synchronize()
                     t0 = time.perf_counter()
                     nrep = 5
-                    tf = 0.0
+                    tf_ = 0.0
                     for _ in range(nrep):
                         t1 = time.perf_counter()
                         f = R.forward(width=W, height=H, **common)
-                        tf += time.perf_counter() - t1
+                        tf_ += time.perf_counter() - t1
                         R.backward(f["radii"], dL_dcolor=dcol, dL_dinvdepth=ddep, **common)
                     torch.cuda.synchronize()
                     dt = (time.perf_counter() - t0) / nrep
                     out["reference_cuda_same_box"] = {"renders_per_s": 1.0 / dt, "ms_per_step": dt * 1e3,
-                                                      "fwd_ms": tf / nrep * 1e3, "note": "unmodified reference kernels + CUB, sm_100a, incl. zero-fills"}
+                                                      "fwd_ms": tf_ / nrep * 1e3, "note": "unmodified reference kernels + CUB, sm_100a, incl. zero-fills"}
                     R.close()
             except Exception as exc:  # informational leg only
                 out["reference_cuda_same_box"] = {"error": str(exc)[:200]}

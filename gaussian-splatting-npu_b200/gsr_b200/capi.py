@@ -7,6 +7,7 @@ opaque scratch buffers with gsr_get_*_layout so that tests can compare every int
 No fallback: a missing library raises.
 """
 import ctypes
+import math
 import os
 from ctypes import (CFUNCTYPE, POINTER, Structure, c_char_p, c_double, c_float, c_int, c_size_t, c_ubyte,
                     c_uint32, c_uint64, c_void_p)
@@ -257,15 +258,18 @@ def backward(state, *, dL_dcolor, dL_dinvdepth=None, means3D, opacities, viewmat
     dev = means3D.device
     P, W, H, M = state["P"], state["W"], state["H"], state["M"]
     out = out or {}
-    e = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)
-    g = dict(dL_dmeans2D=e(P, 3), dL_dconic=e(P, 2, 2), dL_dopacity=e(P, 1), dL_dcolors=e(P, 3),
-             dL_dinvdepths=e(P, 1) if dL_dinvdepth is not None else None, dL_dmeans3D=e(P, 3), dL_dcov3D=e(P, 6),
-             dL_dsh=e(P, M, 3) if M else None, dL_dscales=e(P, 3) if scales is not None else None,
-             dL_drotations=e(P, 4) if scales is not None else None)
-    for k, v in out.items():
-        if g.get(k) is not None:
-            assert v.is_contiguous() and v.numel() == g[k].numel() and v.data_ptr() % 16 == 0
+    shapes = dict(dL_dmeans2D=(P, 3), dL_dconic=(P, 2, 2), dL_dopacity=(P, 1), dL_dcolors=(P, 3),
+                  dL_dinvdepths=(P, 1) if dL_dinvdepth is not None else None, dL_dmeans3D=(P, 3), dL_dcov3D=(P, 6),
+                  dL_dsh=(P, M, 3) if M else None, dL_dscales=(P, 3) if scales is not None else None,
+                  dL_drotations=(P, 4) if scales is not None else None)
+    g = {}
+    for k, shp in shapes.items():
+        v = out.get(k) if shp is not None else None
+        if v is not None:       # the caller's tensor is written in place; nothing is allocated for this output
+            assert v.is_contiguous() and v.numel() == math.prod(shp) and v.data_ptr() % 16 == 0 and v.dtype == torch.float32
             g[k] = v
+        else:
+            g[k] = torch.empty(*shp, dtype=torch.float32, device=dev) if shp is not None else None
     a = BackwardArgs(P, sh_degree, M, state["num_rendered"], W, H, _ptr(background), _ptr(means3D), _ptr(shs),
                      _ptr(colors_precomp), _ptr(opacities), _ptr(scales), scale_modifier, _ptr(rotations),
                      _ptr(cov3D_precomp), _ptr(viewmatrix), _ptr(projmatrix), _ptr(cam_pos), tan_fovx, tan_fovy,

@@ -65,7 +65,7 @@ class SparseGaussianAdam(torch.optim.Adam):
 
     @torch.no_grad()
     def step(self, visibility, N):
-        by_step = {}
+        by_step, writeback = {}, []
         for group in self.param_groups:
             assert len(group["params"]) == 1, "more than one tensor in group"
             param = group["params"][0]
@@ -79,14 +79,28 @@ class SparseGaussianAdam(torch.optim.Adam):
                 state["exp_avg_sq"] = torch.zeros_like(param, memory_format=torch.preserve_format)
             step = int(state["step"]) + 1 if "step" in state else 1
             state["step"] = torch.tensor(float(step))
-            assert param.shape[0] == N and param.is_contiguous()
+            if param.shape[0] != N:
+                raise RuntimeError("SparseGaussianAdam.step: parameter group '%s' has %d rows, N = %d"
+                                   % (group.get("name", "?"), param.shape[0], N))
             # on the separate_sh path the gradients of _features_dc / _features_rest are slices of the [P,16,3]
             # gradient the rasterizer returned for torch.cat([dc, shs]) (not contiguous): pack them once
             grad = param.grad if param.grad.is_contiguous() else param.grad.contiguous()
             v2 = lambda t: t.view(N, -1)
-            seg = dict(param=v2(param.data), grad=v2(grad), exp_avg=v2(state["exp_avg"]),
-                       exp_avg_sq=v2(state["exp_avg_sq"]), lr=group["lr"])
+            tensors = (param.data, state["exp_avg"], state["exp_avg_sq"])
+            if all(x.is_contiguous() for x in tensors):
+                work = tensors
+            else:
+                # Until the first densification `_xyz` is column-major: create_from_pcd wraps
+                # torch.tensor(np.vstack([x, y, z]).T), which keeps numpy's strides (dataset_readers.py:120-127,
+                # gaussian_model.py:150), and zeros_like(preserve_format) gives the moments the same layout.  The
+                # kernel walks row-major rows, so such a group steps on packed copies that are written back.
+                work = tuple(x.contiguous() for x in tensors)
+                writeback.append((tensors, work))
+            seg = dict(param=v2(work[0]), grad=v2(grad), exp_avg=v2(work[1]), exp_avg_sq=v2(work[2]), lr=group["lr"])
             by_step.setdefault((step, tuple(group["betas"]), group["eps"]), []).append(seg)
         vis = visibility if visibility is None or visibility.dtype in (torch.bool, torch.uint8) else visibility != 0
         for (step, betas, eps), segs in by_step.items():     # one launch unless groups have diverged step counts
             capi.adam_step(segs, step, betas[0], betas[1], eps, visible=None if vis is None else vis.contiguous())
+        for tensors, work in writeback:
+            for dst, src in zip(tensors, work):
+                dst.copy_(src)

@@ -143,6 +143,9 @@ def test_sparse_gaussian_adam_interface(cuda):
     shapes = dict(xyz=(N, 3), f_dc=(N, 1, 3), f_rest=(N, 15, 3), opacity=(N, 1), scaling=(N, 3), rotation=(N, 4))
     lrs = dict(xyz=1.6e-4, f_dc=2.5e-3, f_rest=1.25e-4, opacity=0.025, scaling=0.005, rotation=0.001)
     ours = {k: torch.nn.Parameter(torch.randn(s, device=cuda, generator=gen)) for k, s in shapes.items()}
+    # create_from_pcd hands the optimizer a column-major _xyz (torch.tensor keeps the strides of np.vstack([x,y,z]).T)
+    ours["xyz"] = torch.nn.Parameter(torch.randn(3, N, device=cuda, generator=gen).t())
+    assert not ours["xyz"].is_contiguous()
     ref = {k: torch.nn.Parameter(v.detach().clone()) for k, v in ours.items()}
     opt = SparseGaussianAdam([{"params": [ours[k]], "lr": lrs[k], "name": k} for k in ours], lr=0.0, eps=1e-15)
     topt = torch.optim.Adam([{"params": [ref[k]], "lr": lrs[k], "name": k} for k in ref], lr=0.0, eps=1e-15)

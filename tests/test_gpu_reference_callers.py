@@ -49,11 +49,12 @@ def ref_modules(cuda):
     import diff_gaussian_rasterization as dgr
     assert os.path.realpath(dgr.__file__).startswith(os.path.realpath(PKG)), "the rasterizer under test must be this repo's"
     import gaussian_renderer
+    from gaussian_renderer import network_gui     # a submodule: train.py imports it the same way
     from scene.cameras import MiniCam
     from scene.gaussian_model import GaussianModel
     assert os.path.realpath(gaussian_renderer.__file__).startswith(os.path.realpath(d))
     return types.SimpleNamespace(render=gaussian_renderer.render, MiniCam=MiniCam, GaussianModel=GaussianModel,
-                                 network_gui=gaussian_renderer.network_gui)
+                                 network_gui=network_gui)
 
 
 def _model_from_scene(ref, scene):
