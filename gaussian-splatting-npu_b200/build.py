@@ -95,7 +95,8 @@ def _compile_ext(name, sources, out, defines=()):
 
 def build_ext(force=False):
     """_C (rasterizer + loss stage) and the top-level fused_ssim_cuda module (the reference's name)."""
-    hdrs = [os.path.join(ROOT, "include", "gsr.h"), os.path.join(ROOT, "include", "gsr_loss.h"), LIB]
+    # the extensions link libgsr_b200.so dynamically (rpath): only an ABI change -- the headers -- needs a rebuild
+    hdrs = [os.path.join(ROOT, "include", "gsr.h"), os.path.join(ROOT, "include", "gsr_loss.h")]
     main_src = os.path.join(CSRC, "torch_binding.cpp")
     ssim_src = os.path.join(CSRC, "ssim_binding.cpp")
     jobs = []

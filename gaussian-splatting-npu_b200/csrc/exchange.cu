@@ -30,7 +30,7 @@
 namespace {
 
 constexpr int EX_THREADS = 256;
-constexpr int EX_BLOCKS_PER_SM = 4;
+constexpr int EX_BLOCKS_PER_SM = 2;
 constexpr int EX_MAX_BLOCKS = 148 * EX_BLOCKS_PER_SM;
 
 struct ExSeg {
@@ -144,6 +144,28 @@ __device__ __forceinline__ void broadcast_quad(const ExParams& P, float* const* 
     }
 }
 
+// One quad of an ADAM segment, given its reduced gradient: update with the shard-local moments, broadcast the parameters.
+template <bool MC>
+__device__ __forceinline__ void adam_quad(const ExParams& P, const ExSeg& sg, uint32_t e, float4 p, float4 m, float4 v, const float4 g) {
+    const uint32_t le = e - P.shard_begin;
+    uint32_t col = (e - sg.seg_begin) % sg.cols;
+    float* pp = &p.x; float* mp = &m.x; float* vp = &v.x; const float* gp = &g.x;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        adam_update(pp[j], gp[j], mp[j], vp[j], col < sg.split ? sg.step_a : sg.step_b, P.adam);
+        if (++col == sg.cols) col = 0;
+    }
+    stg_stream_f4(reinterpret_cast<float4*>(P.m + le), m);
+    stg_stream_f4(reinterpret_cast<float4*>(P.v + le), v);
+    broadcast_quad<MC>(P, P.param, P.param_mc, e, p);
+}
+
+// EX_UNROLL quads per thread and iteration: all their loads (local parameters / moments and the W peer or multicast
+// gradient loads) are issued before the first use, so a thread keeps EX_UNROLL x (W + 3) 16-byte requests in flight --
+// the NVLink round trip is several microseconds and one quad per thread left the links mostly idle (N = 2: 1.87 ms for
+// 708 MB against 1.28 ms for ncclAllReduce, profiles/r02_summary.md).
+constexpr int EX_UNROLL = 4;
+
 template <bool MC>
 __global__ void __launch_bounds__(EX_THREADS, EX_BLOCKS_PER_SM)
 exchange_kernel(const __grid_constant__ ExParams P) {
@@ -152,28 +174,33 @@ exchange_kernel(const __grid_constant__ ExParams P) {
 #pragma unroll 1
     for (int s = 0; s < P.n_segs; ++s) {
         const ExSeg& sg = P.seg[s];
+        const int kind = sg.kind;
 #pragma unroll 1
-        for (uint32_t q = sg.begin + blockIdx.x * EX_THREADS + threadIdx.x; q < sg.end; q += stride) {
-            const uint32_t e = q * 4u;
-            if (sg.kind == GSR_EXCHANGE_ADAM) {
-                // the rank's own replica of the parameters and its shard-local moments: requested before the reduction
-                const uint32_t le = e - P.shard_begin;
-                float4 p = ld_cs_f4(P.param[P.rank] + e);
-                float4 m = ld_cs_f4(P.m + le), v = ld_cs_f4(P.v + le);
-                const float4 g = reduce_quad<MC>(P, e, GSR_EXCHANGE_SUM);
-                uint32_t col = (e - sg.seg_begin) % sg.cols;
-                float* pp = &p.x; float* mp = &m.x; float* vp = &v.x; const float* gp = &g.x;
+        for (uint32_t q0 = sg.begin + blockIdx.x * EX_THREADS + threadIdx.x; q0 < sg.end; q0 += stride * EX_UNROLL) {
+            float4 g[EX_UNROLL], p[EX_UNROLL], m[EX_UNROLL], v[EX_UNROLL];
+            if (kind == GSR_EXCHANGE_ADAM) {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    adam_update(pp[j], gp[j], mp[j], vp[j], col < sg.split ? sg.step_a : sg.step_b, P.adam);
-                    if (++col == sg.cols) col = 0;
+                for (int u = 0; u < EX_UNROLL; ++u) {
+                    const uint32_t q = q0 + u * stride;
+                    if (q < sg.end) {
+                        const uint32_t e = q * 4u, le = e - P.shard_begin;
+                        p[u] = ld_cs_f4(P.param[P.rank] + e);
+                        m[u] = ld_cs_f4(P.m + le); v[u] = ld_cs_f4(P.v + le);
+                    }
                 }
-                stg_stream_f4(reinterpret_cast<float4*>(P.m + le), m);
-                stg_stream_f4(reinterpret_cast<float4*>(P.v + le), v);
-                broadcast_quad<MC>(P, P.param, P.param_mc, e, p);
-            } else {
-                const float4 g = reduce_quad<MC>(P, e, sg.kind);
-                broadcast_quad<MC>(P, P.grad, P.grad_mc, e, g);
+            }
+#pragma unroll
+            for (int u = 0; u < EX_UNROLL; ++u) {
+                const uint32_t q = q0 + u * stride;
+                if (q < sg.end) g[u] = reduce_quad<MC>(P, q * 4u, kind == GSR_EXCHANGE_MAX ? GSR_EXCHANGE_MAX : GSR_EXCHANGE_SUM);
+            }
+#pragma unroll
+            for (int u = 0; u < EX_UNROLL; ++u) {
+                const uint32_t q = q0 + u * stride;
+                if (q < sg.end) {
+                    if (kind == GSR_EXCHANGE_ADAM) adam_quad<MC>(P, sg, q * 4u, p[u], m[u], v[u], g[u]);
+                    else broadcast_quad<MC>(P, P.grad, P.grad_mc, q * 4u, g[u]);
+                }
             }
         }
     }

@@ -4,15 +4,18 @@
 // backward.cu:452-638).  The reference issues 9-10 global fp32 atomicAdd per contributing
 // (pixel, Gaussian) pair and evaluates every pair of the tile list below n_contrib.  Here:
 //   * one CTA of 4 warps per tile; a warp owns an 8x8 pixel block and every lane TWO pixels of one column
-//     (rows y and y+4, i.e. one pixel in each of the forward's two 8x4 sub-blocks).  Measured on the C2 workload
-//     (tools/blend_stats.py, profiles/r02_*): a Gaussian that reaches one 8x4 block usually reaches its vertical
-//     neighbour too, so the per-visit work that does not depend on the pixel -- list walk, record load, the
-//     cross-lane reduction and the atomics -- is paid once for both pixels; a visit whose mask reaches only one of
-//     the two sub-blocks evaluates only that pixel (warp-uniform branch);
-//   * batches start at the tile's deepest blended position (block max of n_contrib) and a warp skips the list
-//     positions behind its own deepest n_contrib;
-//   * each warp walks only the staged Gaussians whose 8-bit block mask (computed by the forward with
-//     rect_may_contribute, exact + conservatively rounded, kept in the binning buffer) reaches its block;
+//     (rows y and y+4, i.e. one pixel in each of the forward's two 8x4 sub-blocks): the per-visit work that does not
+//     depend on the pixel -- list walk, record load, the cross-lane reduction and the atomics -- is paid once for
+//     both pixels; a visit whose mask reaches only one of the two sub-blocks evaluates only that pixel
+//     (warp-uniform branch);
+//   * WARP-AUTONOMOUS: there is no CTA barrier in the kernel.  Every warp walks the tile list on its own, from its own
+//     deepest n_contrib down, in chunks of 32 list positions: lane l reads the point_list entry and the 8-bit block
+//     mask of one position (computed by the forward with rect_may_contribute, exact + conservatively rounded, kept in
+//     the binning buffer); only the lanes whose Gaussian reaches THIS warp's block fetch its 48-byte record, with
+//     cp.async (LDGSTS) into the warp's private two-stage ring -- chunk c-1's records travel and chunk c-2's
+//     masks / indices sit in two registers while chunk c is processed.  Measured on C2 with the CTA-staged version
+//     this replaces (profiles/r02_summary.md): 48 % of the staged instances reached no warp of the tile, and a warp
+//     spent 28 % of its time waiting at the per-batch barrier for the slowest of its three neighbours;
 //   * the ten per-Gaussian sums are NOT reduced with shuffles (a transposing butterfly costs 14 SHFL + ~30 selects
 //     and adds per visit, and the warp was issue-bound on it): every lane writes its ten partial sums to a per-warp
 //     shared-memory panel [slot][value][lane] (10 conflict-free STS), and once three visits are pending each of 30
@@ -20,19 +23,16 @@
 //     native global RED.ADD.F32 for it -- 30 of 32 lanes carry a total, where the butterfly left 10 of 32;
 //   * exp() of the skip test: ex2.approx(power * log2 e) decides; a pair whose alpha lands within 4e-6 relative of
 //     the 1/255 threshold re-evaluates with expf (the forward's function), so every pair takes the decision it took
-//     in the forward (bit-identical skip set), at 3 instructions instead of 9 for everything else;
-//   * the stage is double-buffered: one CTA barrier per 128-Gaussian batch; the next batch's records travel
-//     global -> shared with cp.async (LDGSTS) while the current one is processed.
+//     in the forward (bit-identical skip set), at 3 instructions instead of 9 for everything else.
 // The per-pixel recurrences are the reference's; power uses the same exactly-rounded chain as the forward.
 #include "gsr_common.cuh"
 #include <type_traits>
 
 #define RB_THREADS 128
 #define RB_WARPS (RB_THREADS / 32)
-#define RB_BATCH 128
 #define RB_SLOTS 3
 #ifndef RB_MIN_CTAS
-#define RB_MIN_CTAS 6
+#define RB_MIN_CTAS 7
 #endif
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -44,6 +44,7 @@ __device__ __forceinline__ void sts_f32(uint32_t a, float v) { asm volatile("st.
 __device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" :: "r"(a), "r"(v) : "memory"); }
 __device__ __forceinline__ uint32_t lds_u32(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
 __device__ __forceinline__ uint32_t lds_u8(uint32_t a) { uint32_t v; asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void cp_async_wait_1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 __device__ __forceinline__ void red_add_f32(float* p, float v) { asm volatile("red.global.add.f32 [%0], %1;" :: "l"(p), "f"(v) : "memory"); }
 
 // per-pixel state of the backward recurrence
@@ -127,12 +128,10 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
                   const float* __restrict__ dL_dpix, const float* __restrict__ dL_dinvdepth_pix,
                   float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity,
                   float* __restrict__ dL_dcolor, float* __restrict__ dL_dinvdepth) {
-    // stage: the raw 48-byte records (x,y,A,C | B,opacity,r,g | b,1/depth,0,0) of a 128-Gaussian batch,
-    // double-buffered, filled by cp.async
-    __shared__ float4 sRec[2][RB_BATCH * 3];
-    __shared__ uint32_t sId[2][RB_BATCH];
-    __shared__ unsigned char sMask[2][RB_BATCH];
-    __shared__ uint32_t sMax[RB_WARPS];
+    // per-warp ring: the raw 48-byte records (x,y,A,C | B,opacity,r,g | b,1/depth,0,0) and Gaussian indices of two
+    // 32-position chunks, slot = lane that fetched it
+    __shared__ float4 sRec[RB_WARPS][2][32 * 3];
+    __shared__ uint32_t sId[RB_WARPS][2][32];
     // reduction panel of each warp: rows (slot, value 0..9) x lanes, + (Gaussian index, opacity) of every pending slot
     __shared__ __align__(16) float sRed[RB_WARPS][RB_ROWS * RB_ROW];
     __shared__ __align__(8) uint2 sSlot[RB_WARPS][RB_SLOTS];
@@ -192,37 +191,35 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         }
     }
 
-    // deepest list position any pixel of this tile / this warp blended
+    // deepest list position any pixel of this warp blended; a warp with nothing to do leaves (no CTA barrier anywhere)
     const uint32_t wmax = __reduce_max_sync(0xffffffffu, max(A.last, B.last));
-    if (lane == 0) sMax[warp] = wmax;
-    __syncthreads();
-    uint32_t remaining = 0;
-#pragma unroll
-    for (int w = 0; w < RB_WARPS; w++) remaining = max(remaining, sMax[w]);
+    if (wmax == 0) return;
 
-    // Software pipeline without staging registers: while batch b is processed, the records of batch b+1 travel
-    // global -> shared by cp.async, and the point_list entry + block mask of batch b+2 sit in two registers.
-    // Batches walk the list backwards: batch k covers positions [remaining-128(k+1), remaining-128k).
-    const uint32_t my_rec0 = smem_addr(&sRec[0][tid * 3]);
-    auto fetch = [&](uint32_t id, uint32_t mask, int b) {
-        const float4* rec = records + 3 * (size_t)id;
-        const uint32_t dst = my_rec0 + (uint32_t)b * (RB_BATCH * 48u);
-        cp_async16(dst, rec); cp_async16(dst + 16u, rec + 1); cp_async16(dst + 32u, rec + 2);
-        sId[b][tid] = id; sMask[b][tid] = (unsigned char)mask;
+    // Chunk c covers list positions [32c, 32c + 32); lane l holds position 32c + 31 - l, so ascending lanes walk the
+    // list back to front.
+    const uint32_t aRec0 = pin(smem_addr(&sRec[warp][0][0])), aId0 = pin(smem_addr(&sId[warp][0][0]));
+    auto load_chunk = [&](int c, uint32_t& id, uint32_t& m) {
+        const uint32_t p = 32u * (uint32_t)c + 31u - (uint32_t)lane;
+        id = 0; m = 0;
+        if (c >= 0 && p < wmax) {
+            const size_t pos = (size_t)range.x + p;
+            id = point_list[pos];
+            m = (uint32_t)block_masks[pos] >> bA;       // bit 0: upper 8x4 half, bit 2: lower half
+        }
     };
-    uint32_t next_id = 0, next_mask = 0;
-    if ((uint32_t)tid < remaining) {
-        const size_t pos = (size_t)range.x + remaining - 1 - tid;
-        fetch(point_list[pos], block_masks[pos], 0);
-    }
-    cp_async_commit();
-    if ((uint32_t)(RB_BATCH + tid) < remaining) {
-        const size_t pos = (size_t)range.x + remaining - 1 - RB_BATCH - tid;
-        next_id = point_list[pos]; next_mask = block_masks[pos];
-    }
+    // requests the records this warp needs from a chunk into ring stage `st`; returns the two lane sets
+    auto issue_chunk = [&](uint32_t id, uint32_t m, int st, unsigned& hitA, unsigned& hitB) {
+        hitA = __ballot_sync(0xffffffffu, m & 1u);
+        hitB = __ballot_sync(0xffffffffu, m & 4u);
+        if (m & 5u) {
+            const float4* rec = records + 3 * (size_t)id;
+            const uint32_t dst = aRec0 + (uint32_t)st * (32u * 48u) + (uint32_t)lane * 48u;
+            cp_async16(dst, rec); cp_async16(dst + 16u, rec + 1); cp_async16(dst + 32u, rec + 2);
+            sts_u32(aId0 + (uint32_t)st * 128u + (uint32_t)lane * 4u, id);
+        }
+        cp_async_commit();
+    };
 
-    const uint32_t aRec0 = pin(smem_addr(&sRec[0][0])), aId0 = pin(smem_addr(&sId[0][0]));
-    const uint32_t aMaskLane0 = pin(smem_addr(&sMask[0][0]) + (uint32_t)lane);
     const uint32_t aPanelLane = pin(smem_addr(&sRed[warp][0]) + 4u * (uint32_t)lane);        // column of this lane
     const uint32_t aPanelRow = pin(smem_addr(&sRed[warp][0]) + (uint32_t)(RB_ROW * 4) * (uint32_t)min(lane, RB_ROWS - 1));
     const uint32_t aSlot = pin(smem_addr(&sSlot[warp][0]));
@@ -282,45 +279,33 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
         if (++slot == RB_SLOTS) { flush(RB_SLOTS); slot = 0; }
     };
 
-    int buf = 0;
-    while (remaining > 0) {
-        const int n = (int)min((uint32_t)RB_BATCH, remaining);
-        cp_async_wait_all();                   // this thread's record of the current batch has landed
-        // One barrier per batch: publishes stage `buf` and proves that every warp has left the batch before
-        // this one -- the last reader of stage `buf ^ 1`, which is refilled right below.
-        __syncthreads();
-        if ((uint32_t)(RB_BATCH + tid) < remaining) fetch(next_id, next_mask, buf ^ 1);
-        cp_async_commit();
-        if ((uint32_t)(2 * RB_BATCH + tid) < remaining) {
-            const size_t pos = (size_t)range.x + remaining - 1 - 2 * RB_BATCH - tid;
-            next_id = point_list[pos]; next_mask = block_masks[pos];
-        }
-        // positions this warp still has to look at: below its deepest n_contrib
-        if (remaining - (uint32_t)n < wmax) {
-            const uint32_t aRec = aRec0 + (uint32_t)buf * (RB_BATCH * 48u), aIds = aId0 + (uint32_t)buf * (RB_BATCH * 4u);
-            const uint32_t aMasks = aMaskLane0 + (uint32_t)buf * RB_BATCH;
-            const int jmin = remaining > wmax ? (int)(remaining - wmax) : 0;    // list positions >= wmax: nothing of this warp
+    int c = (int)((wmax - 1u) >> 5);
+    uint32_t id_n, m_n;
+    unsigned curA, curB, nxtA = 0, nxtB = 0;
+    load_chunk(c, id_n, m_n);
+    issue_chunk(id_n, m_n, 0, curA, curB);
+    load_chunk(c - 1, id_n, m_n);
+    int st = 0;
 #pragma unroll 1
-            for (int k = 0; k < RB_BATCH / 32; k++) {
-                const int idx = k * 32 + lane;
-                const uint32_t m = (idx < n && idx >= jmin) ? lds_u8(aMasks + 32u * k) >> bA : 0u;
-                const unsigned bitsA = __ballot_sync(0xffffffffu, m & 1u);
-                const unsigned bitsB = __ballot_sync(0xffffffffu, m & 4u);
-                unsigned bits = bitsA | bitsB;
-                while (bits) {
-                    const int b = __ffs(bits) - 1;
-                    const uint32_t j = (uint32_t)(k * 32 + b);
-                    bits &= bits - 1;
-                    const uint32_t pos = remaining - 1 - j;
-                    const bool ha = (bitsA >> b) & 1u, hb = (bitsB >> b) & 1u;
-                    if (ha && hb) visit(std::true_type{}, std::true_type{}, aRec + 48u * j, aIds + 4u * j, pos);
-                    else if (ha) visit(std::true_type{}, std::false_type{}, aRec + 48u * j, aIds + 4u * j, pos);
-                    else visit(std::false_type{}, std::true_type{}, aRec + 48u * j, aIds + 4u * j, pos);
-                }
-            }
+    for (; c >= 0; --c, st ^= 1) {
+        // stage st^1 was last read while chunk c+1 was processed: every lane is past that before anybody refills it
+        __syncwarp();
+        if (c >= 1) issue_chunk(id_n, m_n, st ^ 1, nxtA, nxtB); else cp_async_commit();
+        load_chunk(c - 2, id_n, m_n);
+        cp_async_wait_1();                     // this lane's record of chunk c has landed ...
+        __syncwarp();                          // ... and so have the other lanes'
+        const uint32_t aRec = aRec0 + (uint32_t)st * (32u * 48u), aIds = aId0 + (uint32_t)st * 128u;
+        unsigned bits = curA | curB;
+        while (bits) {
+            const int b = __ffs(bits) - 1;
+            bits &= bits - 1;
+            const uint32_t pos = 32u * (uint32_t)c + 31u - (uint32_t)b;
+            const bool ha = (curA >> b) & 1u, hb = (curB >> b) & 1u;
+            if (ha && hb) visit(std::true_type{}, std::true_type{}, aRec + 48u * b, aIds + 4u * b, pos);
+            else if (ha) visit(std::true_type{}, std::false_type{}, aRec + 48u * b, aIds + 4u * b, pos);
+            else visit(std::false_type{}, std::true_type{}, aRec + 48u * b, aIds + 4u * b, pos);
         }
-        remaining -= n;
-        buf ^= 1;
+        curA = nxtA; curB = nxtB;
     }
     if (slot) flush(slot);
     cp_async_wait_all();

@@ -60,6 +60,7 @@ out = {
             "instances_staged": int(c[4]), "warp_batches_skipped": int(c[5]), "warp_batches_processed": int(c[6]),
             "lanes_per_contributing_visit": float(c[3]) / max(1, int(c[2])),
             "lane_hist": [int(x) for x in c[16:49]],
+            "lane_private_walk_passes(window 4,8,16,32)": [int(x) for x in c[80:84]],
             "halves_touched_hist(0,1,2)": [int(x) for x in c[64:67]], "quarters_touched_hist(0..4)": [int(x) for x in c[72:77]]},
     "fwd": {"visits": int(c[7]), "visits_with_blend": int(c[8]), "pairs": int(c[9]), "visits_alpha_ok_ignoring_done": int(c[10]),
             "instances_staged": int(c[11])},

@@ -12,6 +12,8 @@
 // 10 fwd visits where alpha>=1/255 for >=1 lane ignoring done     11 fwd instances staged until the tile stopped
 // 12 bwd visits with any lane alpha-contributing ignoring `last`
 // 16..48  histogram of contributing lanes per bwd visit (0..32)
+// 80..83  sum over windows of W = 4, 8, 16, 32 consecutive contributing visits of (max over lanes of the lane's
+//         contribution count in the window): passes a lane-private-pointer walk would need; 84 = windows of 8 counted
 // 64..96  histogram of 4x4-quadrant occupancy: [64+k] visits whose contributing lanes touch k of the two 4x4 halves...
 extern "C" __global__ void blend_stats_kernel(const uint2* ranges, const uint32_t* point_list, const unsigned char* masks,
                                               const float4* records, int W, int H, int gx, const float* final_T,
@@ -34,6 +36,8 @@ extern "C" __global__ void blend_stats_kernel(const uint2* ranges, const uint32_
     for (int k = 0; k < 33; k++) hist[k] = 0;
     unsigned long long half_hist[3] = {0, 0, 0}, quad_hist[5] = {0, 0, 0, 0, 0};
     // ---- backward walk ----
+    unsigned long long win_pass[4] = {0, 0, 0, 0};
+    uint32_t win_cnt[4] = {0, 0, 0, 0}, win_vis = 0;
     uint32_t remaining = tmax;
     if (warp == 0 && lane == 0) c[4] += tmax;
     while (remaining > 0) {
@@ -52,6 +56,14 @@ extern "C" __global__ void blend_stats_kernel(const uint2* ranges, const uint32_
                 const bool contrib = a_ok && (remaining - 1 - (uint32_t)j < last);
                 const unsigned b = __ballot_sync(0xffffffffu, contrib);
                 const unsigned b2 = __ballot_sync(0xffffffffu, a_ok);
+                if (b) {
+                    win_vis++;
+#pragma unroll
+                    for (int q = 0; q < 4; q++) {
+                        win_cnt[q] += contrib ? 1u : 0u;
+                        if (win_vis % (4u << q) == 0) { win_pass[q] += __reduce_max_sync(0xffffffffu, win_cnt[q]); win_cnt[q] = 0; }
+                    }
+                }
                 if (lane == 0) {
                     c[0]++;
                     if (remaining - 1 - (uint32_t)j >= wmax) c[1]++;
@@ -70,6 +82,8 @@ extern "C" __global__ void blend_stats_kernel(const uint2* ranges, const uint32_
         } else if (lane == 0) c[5]++;
         remaining -= n;
     }
+#pragma unroll
+    for (int q = 0; q < 4; q++) win_pass[q] += __reduce_max_sync(0xffffffffu, win_cnt[q]);
     // ---- forward walk ----
     {
         bool done = !inside;
@@ -112,6 +126,7 @@ extern "C" __global__ void blend_stats_kernel(const uint2* ranges, const uint32_
         for (int k = 0; k < 33; k++) if (hist[k]) atomicAdd(cnt + 16 + k, hist[k]);
         for (int k = 0; k < 3; k++) if (half_hist[k]) atomicAdd(cnt + 64 + k, half_hist[k]);
         for (int k = 0; k < 5; k++) if (quad_hist[k]) atomicAdd(cnt + 72 + k, quad_hist[k]);
+        for (int k = 0; k < 4; k++) if (win_pass[k]) atomicAdd(cnt + 80 + k, win_pass[k]);
     }
 }
 
