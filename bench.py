@@ -936,6 +936,7 @@ def main():
             "config": static_config(args, world),
             "workload_stats": {"P_visible": P_vis, "num_rendered": N, "pairs_evaluated_fwd": pairs_eval, "pairs_blended": pairs_blend,
                                "pairs_evaluated_bwd": pairs_bwd_eval, "peak_source": peak_src, "exchange": args.exchange if world > 1 else None,
+                               "exchange_data_path": (("multicast" if job.fused.use_multicast else "peer"), job.fused.calibration_ms) if job.fused is not None else None,
                                "roofline_view": "stage times / roofline figures are of view 0 of rank 0 alone (single-view fwd+bwd, write mode)"},
             "clocks": clocks,
             "e2e": {"value": e2e_val, "unit": "renders/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

@@ -29,8 +29,14 @@
 
 namespace {
 
+#ifndef EX_BLOCKS
+#define EX_BLOCKS 2
+#endif
+#ifndef EX_UNROLL_N
+#define EX_UNROLL_N 4
+#endif
 constexpr int EX_THREADS = 256;
-constexpr int EX_BLOCKS_PER_SM = 2;
+constexpr int EX_BLOCKS_PER_SM = EX_BLOCKS;
 constexpr int EX_MAX_BLOCKS = 148 * EX_BLOCKS_PER_SM;
 
 struct ExSeg {
@@ -54,7 +60,11 @@ struct ExParams {
 
 __device__ __forceinline__ float4 ld_sys_f4(const float* p) {
     float4 v;
+#ifdef EX_WEAK_LD
+    asm volatile("ld.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+#else
     asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+#endif
     return v;
 }
 __device__ __forceinline__ void st_sys_f4(float* p, float4 v) {
@@ -164,7 +174,7 @@ __device__ __forceinline__ void adam_quad(const ExParams& P, const ExSeg& sg, ui
 // gradient loads) are issued before the first use, so a thread keeps EX_UNROLL x (W + 3) 16-byte requests in flight --
 // the NVLink round trip is several microseconds and one quad per thread left the links mostly idle (N = 2: 1.87 ms for
 // 708 MB against 1.28 ms for ncclAllReduce, profiles/r02_summary.md).
-constexpr int EX_UNROLL = 4;
+constexpr int EX_UNROLL = EX_UNROLL_N;
 
 template <bool MC>
 __global__ void __launch_bounds__(EX_THREADS, EX_BLOCKS_PER_SM)
@@ -175,13 +185,21 @@ exchange_kernel(const __grid_constant__ ExParams P) {
     for (int s = 0; s < P.n_segs; ++s) {
         const ExSeg& sg = P.seg[s];
         const int kind = sg.kind;
+#ifdef EX_CONTIG
+        // a CTA owns EX_UNROLL * EX_THREADS consecutive quads per iteration (16 KB), its threads quads EX_THREADS apart
+        const uint32_t ustride = EX_THREADS;
+#pragma unroll 1
+        for (uint32_t q0 = sg.begin + blockIdx.x * (EX_THREADS * EX_UNROLL) + threadIdx.x; q0 - threadIdx.x < sg.end; q0 += stride * EX_UNROLL) {
+#else
+        const uint32_t ustride = stride;
 #pragma unroll 1
         for (uint32_t q0 = sg.begin + blockIdx.x * EX_THREADS + threadIdx.x; q0 < sg.end; q0 += stride * EX_UNROLL) {
+#endif
             float4 g[EX_UNROLL], p[EX_UNROLL], m[EX_UNROLL], v[EX_UNROLL];
             if (kind == GSR_EXCHANGE_ADAM) {
 #pragma unroll
                 for (int u = 0; u < EX_UNROLL; ++u) {
-                    const uint32_t q = q0 + u * stride;
+                    const uint32_t q = q0 + u * ustride;
                     if (q < sg.end) {
                         const uint32_t e = q * 4u, le = e - P.shard_begin;
                         p[u] = ld_cs_f4(P.param[P.rank] + e);
@@ -191,12 +209,12 @@ exchange_kernel(const __grid_constant__ ExParams P) {
             }
 #pragma unroll
             for (int u = 0; u < EX_UNROLL; ++u) {
-                const uint32_t q = q0 + u * stride;
+                const uint32_t q = q0 + u * ustride;
                 if (q < sg.end) g[u] = reduce_quad<MC>(P, q * 4u, kind == GSR_EXCHANGE_MAX ? GSR_EXCHANGE_MAX : GSR_EXCHANGE_SUM);
             }
 #pragma unroll
             for (int u = 0; u < EX_UNROLL; ++u) {
-                const uint32_t q = q0 + u * stride;
+                const uint32_t q = q0 + u * ustride;
                 if (q < sg.end) {
                     if (kind == GSR_EXCHANGE_ADAM) adam_quad<MC>(P, sg, q * 4u, p[u], m[u], v[u], g[u]);
                     else broadcast_quad<MC>(P, P.grad, P.grad_mc, q * 4u, g[u]);

@@ -125,17 +125,48 @@ class FusedExchange:
     Adam hyper-parameters and learning rates are GaussianAdam's (gaussian_model.py:178-201).  Moments live on the shard's
     owner only: 2 x 59 P / W floats per GPU."""
 
-    def __init__(self, flat, lrs=None, spatial_lr_scale=1.0, betas=(0.9, 0.999), eps=1e-15, use_multicast=True):
+    def __init__(self, flat, lrs=None, spatial_lr_scale=1.0, betas=(0.9, 0.999), eps=1e-15, use_multicast=None):
+        """use_multicast: True / False force the data path (multimem through the switch / peer loads and stores);
+        None (default) measures both once on the zeroed gradient bucket and keeps the faster one -- which one wins
+        depends on the world size (2 GPUs: peer, 1.12 vs 1.85 ms for 708 MB; profiles/r02_summary.md)."""
         assert isinstance(flat, SymmetricGaussians)
         self.flat, self.betas, self.eps, self.step_count = flat, betas, eps, 0
         self.lrs = dict(DEFAULT_LRS)
         self.lrs.update(lrs or {})
         self.lrs["xyz"] = self.lrs["xyz"] * spatial_lr_scale
-        self.use_multicast = bool(use_multicast and flat.mc_grad)
         b, e = shard(flat.n_grad, flat.rank, flat.world)
         self.shard = (b, e)
         self.exp_avg = torch.zeros(max(e - b, 4), dtype=torch.float32, device=flat.device)
         self.exp_avg_sq = torch.zeros_like(self.exp_avg)
+        self.calibration_ms = None
+        if use_multicast is None and flat.world > 1 and flat.mc_grad:
+            self.use_multicast = self._calibrate()
+        else:
+            self.use_multicast = bool(use_multicast and flat.mc_grad)
+
+    def _calibrate(self):
+        """Times the in-place all-reduce of the (zeroed) bucket on both data paths; every rank takes the same decision
+        (MAX over ranks of the device times)."""
+        f = self.flat
+        f.grad_all.zero_()
+        times = []
+        for mc in (False, True):
+            self.use_multicast = mc
+            for _ in range(2):
+                self._launch(False, False)
+            torch.cuda.synchronize(f.device)
+            dist.barrier(f.group)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(4):
+                self._launch(False, False)
+            b.record()
+            torch.cuda.synchronize(f.device)
+            t = torch.tensor([a.elapsed_time(b) / 4], device=f.device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=f.group)
+            times.append(float(t.item()))
+        self.calibration_ms = {"peer": times[0], "multicast": times[1]}
+        return times[1] < times[0]
 
     def set_lr(self, name, lr):
         self.lrs[name] = float(lr)

@@ -77,15 +77,29 @@ def _worker(rank, world, port, use_mc, out):
             rad.copy_(torch.randint(0, 200, (P,), device=dev, generator=g).float())
             want = [acc.clone(), den.clone(), rad.clone()]
             dist.all_reduce(want[0]); dist.all_reduce(want[1]); dist.all_reduce(want[2], op=dist.ReduceOp.MAX)
-            dist.all_reduce(ref.bucket)          # reference: all-reduce, then dense Adam on every replica
+            # reference: gradients summed over ranks, then dense Adam on every replica.  The kernel's peer path adds in
+            # rank order, so the reference does too (bit-exact for every world size); the multicast path's order is
+            # the switch's: compared with a tolerance, and an element whose sum nearly cancels may even take the
+            # opposite Adam step (sign of a ~1e-8 gradient), which is counted, not forbidden.
+            parts = [torch.empty_like(ref.bucket) for _ in range(world)]
+            dist.all_gather(parts, ref.bucket)
+            total = parts[0].clone()
+            for w_ in range(1, world):
+                total += parts[w_]
+            ref.bucket.copy_(total)
             opt_ref.step()
             opt.step(stats=True)
             torch.cuda.synchronize(dev)
             dist.barrier()
-            # gradient sums of N > 2 ranks may be associated differently (ring vs rank order): parameters to 1 ulp-ish
-            same = torch.equal(ref.params, sym.params) if world == 2 else bool(
-                ((ref.params - sym.params).abs() <= 1e-6 * ref.params.abs() + 1e-9).all())
-            ok = ok and same and torch.equal(acc, want[0]) and torch.equal(den, want[1]) and torch.equal(rad, want[2])
+            if not opt.use_multicast:
+                same = torch.equal(ref.params, sym.params)
+            else:
+                d = (ref.params - sym.params).abs()
+                off = d > 1e-5 * (1.0 + ref.params.abs())
+                same = bool(off.float().mean() < 1e-3) and bool(d.max() <= 2 * 0.025 * (step + 1) + 1e-6)
+            exact_sum = world == 2
+            acc_ok = torch.equal(acc, want[0]) if exact_sum else bool(((acc - want[0]).abs() <= 1e-5 * want[0].abs() + 1e-6).all())
+            ok = ok and same and acc_ok and torch.equal(den, want[1]) and torch.equal(rad, want[2])
         # plain all-reduce mode
         g = torch.Generator(device=dev).manual_seed(999 + rank)
         sym.bucket.copy_(torch.randn(sym.bucket.numel(), device=dev, generator=g))
