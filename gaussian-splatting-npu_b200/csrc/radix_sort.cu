@@ -22,7 +22,9 @@
 #define RADIX 256
 #define SORT_MAX_PASSES 8
 
+#ifndef LOOKBACK_UNROLL
 #define LOOKBACK_UNROLL 8
+#endif
 #define STATUS_LOCAL 0x40000000u
 #define STATUS_INCL 0x80000000u
 #define STATUS_VMASK 0x3fffffffu
