@@ -87,7 +87,9 @@ def static_config(args, world):
     V = max(1, args.views_per_rank)
     return {"workload": args.workload + ": " + w["desc"], "P": w["P"], "width": w["W"], "height": w["H"],
             "antialiasing": w["aa"], "sh_degree": 3, "views_per_rank_per_step": V, "global_views_per_step": V * world,
-            "cameras": "orbit of %d distinct cameras, rank r renders cameras r*%d .. r*%d+%d" % (max(8, V * world), V, V, V - 1),
+            "cameras": ("orbit of %d distinct cameras" % max(8, V * world)) + (
+                ", rank r renders cameras r*%d .. r*%d+%d" % (V, V, V - 1) if world == 1 or args.no_balance else
+                ", %d per rank, dealt to the ranks by predicted cost (instance count of a probing forward; gsr_b200.dist.balance_views)" % V),
             "step": "each rank renders its %d views one after another on ONE CUDA stream (each view alone on the GPU: "
                     "forward + backward, parameter gradients summed in one flat 59-fp32/Gaussian bucket)%s" % (
                         V, "; then the gradient exchange over the %d ranks (SUM of the bucket)" % world if world > 1 else ""),
@@ -418,8 +420,8 @@ class Job:
         from gsr_b200.dist import FlatGaussians, ViewStreams, DensificationStats
         self.torch, self.dist, self.capi = torch, dist, capi
         self.name, self.V, self.rank, self.world, self.dev, self.exchange = name, V, rank, world, dev, exchange
-        self.w, self.scene, cam0 = make_workload(name, rank * V, total_views)
-        self.cams = [cam0] + [make_workload_camera(name, rank * V + v, total_views) for v in range(1, V)]
+        self.w, self.scene, _ = make_workload(name, rank * V, total_views)
+        self.total_views = total_views
         w = self.w
         t = self.t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
         self.fused = None
@@ -439,10 +441,9 @@ class Job:
         self.bg = torch.zeros(3, device=dev)
         self.dcol_np, self.ddep_np = synth.upstream_grads(w["H"], w["W"], 5)
         self.dcol, self.ddep = t(self.dcol_np), t(self.ddep_np)
-        shared = dict(means3D=G.xyz, opacities=G.opacity, background=self.bg, shs=G.shs, scales=G.scales,
-                      rotations=G.rotations, sh_degree=3, antialiasing=w["aa"])
-        self.per_view = [dict(viewmatrix=t(c.world_view_transform), projmatrix=t(c.full_proj_transform),
-                              cam_pos=t(c.camera_center), tan_fovx=c.tanfovx, tan_fovy=c.tanfovy, **shared) for c in self.cams]
+        self.shared = dict(means3D=G.xyz, opacities=G.opacity, background=self.bg, shs=G.shs, scales=G.scales,
+                           rotations=G.rotations, sh_degree=3, antialiasing=w["aa"])
+        self.set_views(list(range(rank * V, rank * V + V)))
         # every gradient output is a persistent tensor: the five parameter gradients are views of the exchange bucket,
         # the per-view intermediates (means2D, conic, ...) one scratch set per stream
         self.grad_views = G.grad_views()
@@ -455,6 +456,33 @@ class Job:
         self.stats = DensificationStats(P, dev)
         self.adam = None
         self.last_state = None
+
+    def set_views(self, indices):
+        """This rank's views of the step: indices into the step's orbit of `total_views` cameras."""
+        self.view_indices = list(indices)
+        self.cams = [make_workload_camera(self.name, i, self.total_views) for i in self.view_indices]
+        t = self.t
+        self.per_view = [dict(viewmatrix=t(c.world_view_transform), projmatrix=t(c.full_proj_transform),
+                              cam_pos=t(c.camera_center), tan_fovx=c.tanfovx, tan_fovy=c.tanfovy, **self.shared) for c in self.cams]
+
+    def balance(self):
+        """Deals the step's views to the ranks by predicted cost (gsr_b200.dist.balance_views): one probing forward per
+        view gives its instance count N, every rank gathers all counts and computes the same assignment."""
+        if self.world == 1:
+            return None
+        from gsr_b200.dist import balance_views
+        torch, dist = self.torch, self.dist
+        mine = torch.zeros(self.total_views, device=self.dev)
+        for v, gi in enumerate(self.view_indices):
+            mine[gi] = float(self._fwd(v, 0)["num_rendered"])
+        dist.all_reduce(mine)
+        costs = mine.cpu().tolist()
+        assign = balance_views(costs, self.world, self.V)
+        before = max(sum(costs[r * self.V:(r + 1) * self.V]) for r in range(self.world))
+        after = max(sum(costs[i] for i in a) for a in assign)
+        self.set_views(assign[self.rank])
+        return {"cost": "instance count N of a probing forward", "max_rank_sum_contiguous": before, "max_rank_sum_balanced": after,
+                "mean_rank_sum": sum(costs) / self.world}
 
     # ---- one view / one step ------------------------------------------------------------------------------
     def _fwd(self, v, slot):
@@ -610,6 +638,7 @@ def main():
     ap.add_argument("--no-ref-cuda", action="store_true")
     ap.add_argument("--no-c3", action="store_true", help="skip the BASELINE configs[2] strong-scaling leg")
     ap.add_argument("--no-extras", action="store_true", help="skip the loss / frame / optimizer stage reports")
+    ap.add_argument("--no-balance", action="store_true", help="N > 1: keep cameras r*V .. r*V+V-1 on rank r instead of dealing the step's views by predicted cost")
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
                     help="gradient exchange at N > 1: this library's kernel over NVLink peer / multicast memory, or ncclAllReduce")
     ap.add_argument("--streams", type=int, default=3,
@@ -643,6 +672,7 @@ def main():
     V = max(1, args.views_per_rank)
     S = max(1, args.streams)
     job = Job(args.workload, V, V * world, rank, world, dev, args.exchange, max_streams=S)
+    balance_info = None if args.no_balance else job.balance()
     w, G = job.w, job.G
     W, H, P = w["W"], w["H"], w["P"]
     warm = max(args.warmup, 3)
@@ -832,6 +862,8 @@ def main():
     if not args.no_c3 and args.workload == "c2" and 8 % world == 0:
         torch.cuda.empty_cache()
         j3 = Job("c3", 8 // world, 8, rank, world, dev, args.exchange, max_streams=S)
+        if not args.no_balance:
+            j3.balance()
         r_ms, _, _ = time_steps(torch, dist, dev, world, lambda: j3.step_render(1), args.steps, warm, min_warm_s=0.5)
         saved = j3.save_params()
         t_ms, _, _ = time_steps(torch, dist, dev, world, lambda: j3.step_train(1), args.steps, warm, min_warm_s=0.3)
@@ -935,7 +967,7 @@ def main():
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": static_config(args, world),
             "workload_stats": {"P_visible": P_vis, "num_rendered": N, "pairs_evaluated_fwd": pairs_eval, "pairs_blended": pairs_blend,
-                               "pairs_evaluated_bwd": pairs_bwd_eval, "peak_source": peak_src, "exchange": args.exchange if world > 1 else None,
+                               "pairs_evaluated_bwd": pairs_bwd_eval, "peak_source": peak_src, "exchange": args.exchange if world > 1 else None, "view_balance": balance_info,
                                "exchange_data_path": (("multicast" if job.fused.use_multicast else "peer"), job.fused.calibration_ms) if job.fused is not None else None,
                                "roofline_view": "stage times / roofline figures are of view 0 of rank 0 alone (single-view fwd+bwd, write mode)"},
             "clocks": clocks,

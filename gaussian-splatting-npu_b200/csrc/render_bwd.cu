@@ -3,7 +3,7 @@
 // Replaces BACKWARD::render / renderCUDA<3> (diff-gaussian-rasterization-npu/cuda_rasterizer/
 // backward.cu:452-638).  The reference issues 9-10 global fp32 atomicAdd per contributing
 // (pixel, Gaussian) pair and evaluates every pair of the tile list below n_contrib.  Here:
-//   * one CTA of 4 warps per tile; a warp owns an 8x8 pixel block and every lane TWO pixels of one column
+//   * one warp per (tile, 8x8 pixel block), one warp per CTA; every lane owns TWO pixels of one column
 //     (rows y and y+4, i.e. one pixel in each of the forward's two 8x4 sub-blocks): the per-visit work that does not
 //     depend on the pixel -- list walk, record load, the cross-lane reduction and the atomics -- is paid once for
 //     both pixels; a visit whose mask reaches only one of the two sub-blocks evaluates only that pixel
@@ -28,11 +28,14 @@
 #include "gsr_common.cuh"
 #include <type_traits>
 
-#define RB_THREADS 128
-#define RB_WARPS (RB_THREADS / 32)
+#ifndef RB_WARPS
+#define RB_WARPS 1              // warps per CTA: 1 = one CTA per (tile, 8x8 block), 4 = one CTA per tile.  The warps share
+#endif                          // nothing, so single-warp CTAs let the hardware refill a warp slot the moment its warp is
+                                // done instead of when the slowest of four is: 0.925 -> 0.897 ms at C2
+#define RB_THREADS (32 * RB_WARPS)
 #define RB_SLOTS 3
 #ifndef RB_MIN_CTAS
-#define RB_MIN_CTAS 7
+#define RB_MIN_CTAS (28 / RB_WARPS)     // 72 registers; shared memory (7.7 KB per warp + 1 KB per CTA) admits 26 single-warp CTAs
 #endif
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -136,14 +139,15 @@ render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__
     __shared__ __align__(16) float sRed[RB_WARPS][RB_ROWS * RB_ROW];
     __shared__ __align__(8) uint2 sSlot[RB_WARPS][RB_SLOTS];
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;       // warp: index into the CTA's shared arrays
+    const int item = blockIdx.x * RB_WARPS + warp;                       // (tile, 8x8 block) of this warp
+    const int tile = item >> 2, wq = item & 3;
     const int tx = tile % gx, ty = tile / gx;
-    // warp -> 8x8 block (column warp&1, row pair warp>>1); lane -> pixels (x, y) and (x, y+4): the forward's 8x4
-    // sub-blocks bA = (warp&1) + 4*(warp>>1) and bB = bA + 2
-    const int px = tx * GSR_TILE + (warp & 1) * 8 + (lane & 7);
-    const int pyA = ty * GSR_TILE + (warp >> 1) * 8 + (lane >> 3), pyB = pyA + 4;
-    const int bA = (warp & 1) + 4 * (warp >> 1);
+    // 8x8 block wq of the tile (column wq&1, row pair wq>>1); lane -> pixels (x, y) and (x, y+4): the forward's 8x4
+    // sub-blocks bA = (wq&1) + 4*(wq>>1) and bB = bA + 2
+    const int px = tx * GSR_TILE + (wq & 1) * 8 + (lane & 7);
+    const int pyA = ty * GSR_TILE + (wq >> 1) * 8 + (lane >> 3), pyB = pyA + 4;
+    const int bA = (wq & 1) + 4 * (wq >> 1);
     const size_t HW = (size_t)H * W;
     const uint2 range = ranges[tile];
     const float bg0 = background[0], bg1 = background[1], bg2 = background[2];
@@ -315,10 +319,10 @@ void launch_render_bwd(const BwdParams& p, const uint2* ranges, const uint32_t* 
                        const float4* records, const float* final_T, const uint32_t* n_contrib, cudaStream_t s) {
     const int tiles = p.gx * p.gy;
     if (p.dL_dinvdepth_pix)
-        render_bwd_kernel<true><<<tiles, RB_THREADS, 0, s>>>(ranges, point_list, block_masks, records, p.W, p.H, p.gx, p.background,
+        render_bwd_kernel<true><<<tiles * 4 / RB_WARPS, RB_THREADS, 0, s>>>(ranges, point_list, block_masks, records, p.W, p.H, p.gx, p.background,
             final_T, n_contrib, p.dL_dpix, p.dL_dinvdepth_pix, p.dL_dmean2D, p.dL_dconic, p.dop_view, p.dL_dcolor,
             p.dL_dinvdepth);
     else
-        render_bwd_kernel<false><<<tiles, RB_THREADS, 0, s>>>(ranges, point_list, block_masks, records, p.W, p.H, p.gx, p.background,
+        render_bwd_kernel<false><<<tiles * 4 / RB_WARPS, RB_THREADS, 0, s>>>(ranges, point_list, block_masks, records, p.W, p.H, p.gx, p.background,
             final_T, n_contrib, p.dL_dpix, nullptr, p.dL_dmean2D, p.dL_dconic, p.dop_view, p.dL_dcolor, nullptr);
 }

@@ -91,6 +91,24 @@ class FlatGaussians:
                 params[name].grad.copy_(self._view(self.bucket, name).view(params[name].grad.shape))
 
 
+def balance_views(costs, world, per_rank=None):
+    """Deals the views of a step to `world` ranks so that the ranks' summed costs are as equal as a greedy pass gets them:
+    views in decreasing cost order, each to the rank with the smallest sum that still has room (LPT with equal counts).
+    `costs[i]` is any predictor of view i's time -- the instance count N of the last time that camera was rendered works
+    (the step ends with the slowest rank, SURVEY.md section 8(e): "assign views to GPUs by predicted N").  Deterministic:
+    every rank computes the same assignment from the same costs.  Returns a list of `world` lists of view indices."""
+    n = len(costs)
+    per_rank = per_rank if per_rank is not None else (n + world - 1) // world
+    assert per_rank * world >= n
+    order = sorted(range(n), key=lambda i: (-float(costs[i]), i))
+    sums, out = [0.0] * world, [[] for _ in range(world)]
+    for i in order:
+        r = min((r for r in range(world) if len(out[r]) < per_rank), key=lambda r: (sums[r], r))
+        out[r].append(i)
+        sums[r] += float(costs[i])
+    return [sorted(v) for v in out]
+
+
 class ViewStreams:
     """Renders the views of one step (forward + backward, gradients accumulated in one bucket) on several CUDA streams.
 

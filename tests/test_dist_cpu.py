@@ -90,3 +90,16 @@ def test_flat_layout():
     assert np.array_equal(G2.shs.numpy(), sc["shs"]) and np.array_equal(G2.rotations.numpy(), sc["rotations"])
     leaves = G2.as_leaf_params()
     assert all(p.requires_grad and p.is_leaf for p in leaves.values())
+
+
+def test_balance_views_equalises_rank_sums():
+    from gsr_b200.dist import balance_views
+    rng = np.random.default_rng(3)
+    costs = rng.uniform(5e6, 9e6, 64)
+    naive = [list(range(r * 8, r * 8 + 8)) for r in range(8)]
+    bal = balance_views(costs, 8, 8)
+    assert sorted(i for v in bal for i in v) == list(range(64)) and all(len(v) == 8 for v in bal)
+    spread = lambda a: max(costs[v].sum() for v in a) / costs.sum() * 8
+    assert spread(bal) < 1.01 < spread(naive)
+    assert balance_views(costs, 8, 8) == bal                      # deterministic
+    assert balance_views([3, 1, 2], 2, 2) == [[0], [1, 2]]
