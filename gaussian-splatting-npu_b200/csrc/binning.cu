@@ -16,7 +16,6 @@
 #include "gsr_common.cuh"
 
 #define SCAN_THREADS 256
-#define SCAN_LOOKBACK 8
 #define SCAN_IPT (GSR_SCAN_ITEMS / SCAN_THREADS)   // 16
 
 __device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
@@ -28,36 +27,34 @@ __device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned 
     asm volatile("st.volatile.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
 }
 
-// decoupled look-back over 64-bit (flag<<32 | value) status words; returns the exclusive prefix of
-// `tile` and publishes its inclusive value.  One thread per scanned quantity calls this.
-__device__ __forceinline__ uint32_t lookback(unsigned long long* status, uint32_t tile, uint32_t aggregate) {
-    uint32_t excl = 0;
+// Decoupled look-back over 64-bit (flag<<32 | value) status words by ONE WARP: lane l reads predecessor t - l, so a round
+// trip to L2 covers 32 predecessors with one load per lane (flag 0 = not published yet, 1 = tile aggregate, 2 = inclusive
+// prefix).  The words up to the nearest inclusive one -- or up to the first unpublished one, which the next round re-reads
+// -- are summed with a warp reduction.  Returns the exclusive prefix of `tile` (in every lane) and publishes its inclusive
+// value.  With every tile of a 3M-element scan resident at once the nearest inclusive word is dozens of tiles back; one
+// thread walking 8 words per round trip was the critical path of both scans (scan 0.050 -> 0.042, scan2 + emit 0.121 -> 0.115 ms at C2, profiles/r02_summary.md).
+__device__ __forceinline__ uint32_t lookback_warp(unsigned long long* status, uint32_t tile, uint32_t aggregate, int lane) {
     if (tile == 0) {
-        st_volatile_u64(&status[0], (2ull << 32) | aggregate);
-    } else {
-        st_volatile_u64(&status[tile], (1ull << 32) | aggregate);
-        // SCAN_LOOKBACK predecessors per round trip (independent volatile loads), consumed in order; an
-        // unpublished word stops the round and is re-read by the next one
-        int t = (int)tile - 1;
-        bool found = false;
-        while (!found) {
-            unsigned long long w[SCAN_LOOKBACK];
-#pragma unroll
-            for (int k = 0; k < SCAN_LOOKBACK; k++) w[k] = (t - k >= 0) ? ld_volatile_u64(&status[t - k]) : (2ull << 32);
-            int used = 0;
-#pragma unroll
-            for (int k = 0; k < SCAN_LOOKBACK; k++) {
-                const uint32_t flag = (uint32_t)(w[k] >> 32);
-                if (!found && used == k && flag != 0) {
-                    excl += (uint32_t)w[k];
-                    used = k + 1;
-                    found = flag == 2;
-                }
-            }
-            t -= used;
-        }
-        st_volatile_u64(&status[tile], (2ull << 32) | (uint32_t)(excl + aggregate));
+        if (lane == 0) st_volatile_u64(&status[0], (2ull << 32) | aggregate);
+        return 0;
     }
+    if (lane == 0) st_volatile_u64(&status[tile], (1ull << 32) | aggregate);
+    uint32_t excl = 0;
+    int t = (int)tile - 1;
+    while (true) {
+        const int idx = t - lane;
+        const unsigned long long w = idx >= 0 ? ld_volatile_u64(&status[idx]) : (2ull << 32);
+        const uint32_t flag = (uint32_t)(w >> 32);
+        const unsigned unpub = __ballot_sync(0xffffffffu, flag == 0u);
+        const unsigned incl = __ballot_sync(0xffffffffu, flag == 2u);
+        const int first_unpub = unpub ? __ffs(unpub) - 1 : 32, first_incl = incl ? __ffs(incl) - 1 : 32;
+        const bool done = first_incl < first_unpub;
+        const int take = done ? first_incl + 1 : first_unpub;          // lanes [0, take) hold usable words
+        excl += __reduce_add_sync(0xffffffffu, lane < take ? (uint32_t)w : 0u);
+        if (done) break;
+        t -= take;
+    }
+    if (lane == 0) st_volatile_u64(&status[tile], (2ull << 32) | (uint32_t)(excl + aggregate));
     return excl;
 }
 
@@ -87,7 +84,7 @@ __device__ __forceinline__ uint32_t block_excl(uint32_t run, uint32_t* warp_sums
 //   gkeys/gvals[P_vis] the visible Gaussians (tiles_touched > 0) compacted in index order:
 //                     key = depth bits, value = Gaussian index -- input of the depth sort
 //   state[2] = N (num_rendered), state[3] = P_vis.
-// Each CTA takes a 4096-element tile by atomic ticket; two threads resolve the two prefixes
+// Each CTA takes a 4096-element tile by atomic ticket; two warps resolve the two prefixes
 // (instances, visible count) by decoupled look-back concurrently.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(SCAN_THREADS)
@@ -126,14 +123,18 @@ scan_compact_kernel(const uint32_t* __restrict__ in, const float* __restrict__ d
     const uint32_t excl_sum = block_excl(run, warp_sums[0], lane, warp, agg_sum);
     const uint32_t excl_cnt = block_excl(nvis, warp_sums[1], lane, warp, agg_cnt);
 
-    if (tid == 0) {
-        const uint32_t e = lookback(status_sum, tile, agg_sum);
-        s_excl_sum = e;
-        if ((size_t)(tile + 1) * GSR_SCAN_ITEMS >= (size_t)P) state[2] = e + agg_sum;      // grand total N
-    } else if (tid == 32) {
-        const uint32_t e = lookback(status_cnt, tile, agg_cnt);
-        s_excl_cnt = e;
-        if ((size_t)(tile + 1) * GSR_SCAN_ITEMS >= (size_t)P) state[3] = e + agg_cnt;      // P_vis
+    if (warp == 0) {
+        const uint32_t e = lookback_warp(status_sum, tile, agg_sum, lane);
+        if (lane == 0) {
+            s_excl_sum = e;
+            if ((size_t)(tile + 1) * GSR_SCAN_ITEMS >= (size_t)P) state[2] = e + agg_sum;      // grand total N
+        }
+    } else if (warp == 1) {
+        const uint32_t e = lookback_warp(status_cnt, tile, agg_cnt, lane);
+        if (lane == 0) {
+            s_excl_cnt = e;
+            if ((size_t)(tile + 1) * GSR_SCAN_ITEMS >= (size_t)P) state[3] = e + agg_cnt;      // P_vis
+        }
     }
     __syncthreads();
     const uint32_t add = s_excl_sum + excl_sum;
@@ -189,7 +190,10 @@ sorted_scan_kernel(const uint32_t* __restrict__ order, const uint32_t* __restric
     for (int k = 0; k < SCAN_IPT; k++) { run += v[k]; v[k] = run; }
     uint32_t aggregate;
     const uint32_t thread_excl = block_excl(run, warp_sums, lane, warp, aggregate);
-    if (tid == 0) s_excl = lookback(status, tile, aggregate);
+    if (warp == 0) {
+        const uint32_t e = lookback_warp(status, tile, aggregate, lane);
+        if (lane == 0) s_excl = e;
+    }
     __syncthreads();
     const uint32_t add = s_excl + thread_excl;
 #pragma unroll

@@ -5,8 +5,8 @@
 //  rasterizer_impl.cu:54-66).  One thread per Gaussian; HBM-bound.  What is different from the
 // reference:
 //   * the 192-byte SH row of each *visible* Gaussian is fetched by the whole warp with coalesced
-//     128-bit streaming loads into a swizzled shared-memory stage (conflict-free LDS.128 read-back)
-//     instead of 48 strided scalar loads per thread; rows of culled Gaussians are never read;
+//     16-byte cp.async (LDGSTS) requests straight into a swizzled shared-memory stage (conflict-free LDS.128
+//     read-back) instead of 48 strided scalar loads per thread; rows of culled Gaussians are never read;
 //   * xy / conic / opacity / rgb / 1/depth are emitted as ONE packed 48-byte record per Gaussian
 //     (3 x float4) so the blend kernels gather 2 sectors per instance instead of 4 arrays;
 //   * the clamp flags are one bitmask byte.
@@ -228,8 +228,12 @@ preprocess_fwd_kernel(FwdParams p, GeomView g, int* __restrict__ radii) {
                 for (int it = 0; it < 12; it++) {
                     const int f = it * 32 + lane;
                     const int row = f / 12, j = f - row * 12;
-                    if ((vis >> row) & 1u) st[row * 12 + (j ^ ((row >> 1) & 3))] = ldg_stream_f4(src + f);
+                    if ((vis >> row) & 1u) cp_async16(smem_addr(st + row * 12 + (j ^ ((row >> 1) & 3))), src + f);
                 }
+                // LDGSTS: the twelve requests of a lane are in flight together and take no staging registers (through
+                // registers the compiler issued them a few at a time: 0.204 -> 0.134 ms at C2, profiles/r02_summary.md)
+                cp_async_commit();
+                cp_async_wait_all();
                 __syncwarp();
                 if (visible) {
                     const StageRow E = { reinterpret_cast<const float*>(st + lane * 12), (lane >> 1) & 3 };

@@ -223,8 +223,12 @@ def test_view_streams_match_single_stream(cuda, n_streams):
         torch.cuda.synchronize()
         return {k: b.double().cpu().numpy() for k, b in bucket.items()}
     want, got = run(1), run(n_streams)
+    # dL_dscales / dL_drotations come out of the covariance backward with heavy cancellation: the order of the fp32 atomics
+    # of the blend (different from run to run on ONE stream as well) moves them by ~1e-4 of the tensor maximum -- the same
+    # three tensors tests/test_oracle_golden.py holds to 1e-3 for the reference's own noise
+    tol = dict(dL_dscales=1e-3, dL_drotations=1e-3)
     for k in want:
-        assert np.abs(got[k] - want[k]).max() <= 1e-4 * (np.abs(want[k]).max() + 1e-30), k
+        assert np.abs(got[k] - want[k]).max() <= tol.get(k, 1e-4) * (np.abs(want[k]).max() + 1e-30), k
 
 
 def test_workspace_reuse_gives_the_same_render(cuda):

@@ -41,5 +41,13 @@ for mode in ("fwd", "fwd+bwd"):
     b.record()
     torch.cuda.synchronize()
     res[mode + "_ms"] = a.elapsed_time(b) / 100
+capi.set_profiling(True)
+acc = {}
+for _ in range(9):
+    st = capi.forward(width=W, height=H, workspace=ws, **kw)
+    for k, v in capi.stage_times_ms().items():
+        acc.setdefault(k, []).append(v)
+capi.set_profiling(False)
+res["stage_ms"] = {k: round(float(np.median(v)), 4) for k, v in acc.items() if k in ("preprocess", "sh_color", "scan", "depth_sort", "duplicate", "sort", "ranges", "render_fwd")}
 res["color_sum"] = float(st["out_color"].double().sum().item())
 print(json.dumps(res))
