@@ -136,6 +136,18 @@ onesweep_kernel(const KeyT* __restrict__ kin, const uint32_t* __restrict__ vin, 
     const uint32_t tile_n = (uint32_t)min((size_t)SORT_TILE, n - tile_base);
     const size_t my_base = tile_base + (size_t)warp * (32 * SORT_IPT) + lane;
 
+    // 0. the values travel global -> shared (input order, into the array the reorder fills later) while the keys are
+    //    ranked and the look-back runs: loaded only in step 6, they cost a third dependent trip to HBM per CTA
+    {
+        const uint32_t dst0 = smem_addr(&sm.vals[warp * (32 * SORT_IPT) + lane]);
+#pragma unroll
+        for (int i = 0; i < SORT_IPT; i++) {
+            const size_t idx = my_base + i * 32;
+            if (idx < n) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(dst0 + (uint32_t)i * 128u), "l"(vin + idx) : "memory");
+        }
+        cp_async_commit();
+    }
+
     // 1. load keys, warp-striped: item i of this warp covers 32 consecutive keys
     KeyT key[SORT_IPT];
     const bool full = tile_n == SORT_TILE;
@@ -227,17 +239,29 @@ onesweep_kernel(const KeyT* __restrict__ kin, const uint32_t* __restrict__ vin, 
     sm.gofs[tid] = g_excl + prefix - bin_base;
     __syncthreads();
 
-    // 6. reorder the tile in shared memory (values are loaded only now to keep registers low)
+    // 6. reorder the tile in shared memory: keys first (their positions replace the ranks, two per register), then the
+    //    staged values -- every thread takes its own sixteen out of the stage before anybody overwrites it
 #pragma unroll
     for (int i = 0; i < SORT_IPT; i++) {
         const size_t idx = my_base + i * 32;
+        uint32_t pos = 0;
         if (full || idx < n) {
             const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
             const uint32_t r = (i & 1) ? (rank2[i >> 1] >> 16) : (rank2[i >> 1] & 0xffffu);
-            const uint32_t pos = sm.bin_base[d] + wh[d] + r;
+            pos = sm.bin_base[d] + wh[d] + r;
             sm.keys[pos] = key[i];
-            sm.vals[pos] = vin[idx];
         }
+        if (i & 1) rank2[i >> 1] = (rank2[i >> 1] & 0xffffu) | (pos << 16); else rank2[i >> 1] = (rank2[i >> 1] & 0xffff0000u) | pos;
+    }
+    cp_async_wait_all();
+    uint32_t val[SORT_IPT];
+#pragma unroll
+    for (int i = 0; i < SORT_IPT; i++) val[i] = sm.vals[warp * (32 * SORT_IPT) + i * 32 + lane];      // this thread's own copies
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < SORT_IPT; i++) {
+        const size_t idx = my_base + i * 32;
+        if (full || idx < n) sm.vals[(i & 1) ? (rank2[i >> 1] >> 16) : (rank2[i >> 1] & 0xffffu)] = val[i];
     }
     __syncthreads();
 
