@@ -17,6 +17,7 @@ ranks; at N = 1 that is 1 / (single-view forward+backward time).  Prints ONE JSO
   with_optimizer   the step followed by the densification statistics and the Adam step (N > 1: the fused exchange kernel
                    reduce-scatter -> sharded Adam -> all-gather; N = 1: gsr_adam_step)
   overlapped_step  the same 8 views spread over 3 CUDA streams (gsr_b200.dist.ViewStreams)
+  batched_step     the same 8 views through gsr_forward_batch / gsr_backward_batch (one per-Gaussian launch for all cameras)
   c3_strong        BASELINE.json configs[2] as written: 1.8M Gaussians, 979x546, 8 views per step IN TOTAL split over the
                    N ranks, gradient exchange every step (strong scaling), with and without the optimizer
   roofline         the dominant kernel (backward blend, FP32-pipe bound) + roofline_stages for every stage
@@ -524,6 +525,23 @@ class Job:
         self.render_views(n_streams)
         self.exchange_gradients()
 
+    def step_batched(self):
+        """The same V views through gsr_forward_batch / gsr_backward_batch: the per-Gaussian stages run ONCE for all
+        cameras (parameters and SH rows read once, the 59 gradient floats written once), the rest per view."""
+        capi, torch = self.capi, self.torch
+        if not hasattr(self, "batch_ws"):
+            P = self.w["P"]
+            e = lambda *s: torch.empty(*s, dtype=torch.float32, device=self.dev)
+            self.batch_ws = [capi.Workspace(self.dev) for _ in range(self.V)]
+            self.batch_scratch = [dict(dL_dmeans2D=e(P, 3), dL_dconic=e(P, 2, 2), dL_dcolors=e(P, 3), dL_dinvdepths=e(P, 1))
+                                  for _ in range(self.V)]
+        cam_kw = [{k: pv[k] for k in ("viewmatrix", "projmatrix", "cam_pos", "tan_fovx", "tan_fovy")} for pv in self.per_view]
+        states = capi.forward_batch(cam_kw, width=self.w["W"], height=self.w["H"], workspaces=self.batch_ws, **self.shared)
+        capi.backward_batch(states, cam_kw, dL_dcolor=self.dcol, dL_dinvdepth=self.ddep, out=self.grad_views,
+                            scratch=self.batch_scratch, **self.shared)
+        self.last_state = states[-1]
+        self.exchange_gradients()
+
     def step_train(self, n_streams=1):
         """Render + statistics + optimizer: what train.py:163-186 does after the backward, for the whole step."""
         torch = self.torch
@@ -705,6 +723,17 @@ def main():
                   "what": "the same step with view v on CUDA stream v %% %d (gsr_b200.dist.ViewStreams): the latency-bound "
                           "stages of one view run under the blend kernels of its neighbours" % S}
 
+    # ---------------- the same views through the batched entry points (own key; not `value`) ----------------
+    bt_ms, _, _ = time_steps(torch, dist, dev, world, job.step_batched, args.steps, warm, min_warm_s=0.3)
+    batched = {"value": world * V * args.steps / (bt_ms / 1000.0), "unit": "renders/s", "ms_per_step": bt_ms / args.steps,
+               "ms_per_view": bt_ms / args.steps / V,
+               "what": "the same %d views through gsr_forward_batch / gsr_backward_batch on one stream: ONE per-Gaussian launch each way "
+                       "for all cameras (parameters and SH rows read once, the 59 gradient floats written once), scan / sorts / "
+                       "emission / blend per view" % V}
+    if hasattr(job, "batch_ws"):
+        del job.batch_ws, job.batch_scratch
+        torch.cuda.empty_cache()
+
     # ---------------- with the optimizer: render + densification statistics + Adam (+ exchange) ----------------
     saved = job.save_params()
     op_ms, _, _ = time_steps(torch, dist, dev, world, lambda: job.step_train(1), args.steps, warm, min_warm_s=0.3)
@@ -869,11 +898,13 @@ def main():
         t_ms, _, _ = time_steps(torch, dist, dev, world, lambda: j3.step_train(1), args.steps, warm, min_warm_s=0.3)
         j3.restore_params(saved)
         o_ms, _, _ = time_steps(torch, dist, dev, world, lambda: j3.step_render(S), args.steps, warm, min_warm_s=0.3)
+        b_ms, _, _ = time_steps(torch, dist, dev, world, j3.step_batched, args.steps, warm, min_warm_s=0.3)
         c3 = {"workload": "c3: " + WORKLOADS["c3"]["desc"] + "; 8 views per step IN TOTAL, %d per rank, gradient exchange every step" % (8 // world),
               "scaling": "strong", "n_gpus": world, "views_per_step": 8, "exchange": args.exchange if world > 1 else None,
               "value": 8 * args.steps / (r_ms / 1000.0), "unit": "views/s", "ms_per_step": r_ms / args.steps,
               "with_optimizer": {"value": 8 * args.steps / (t_ms / 1000.0), "ms_per_step": t_ms / args.steps},
               "overlapped_%d_streams" % S: {"value": 8 * args.steps / (o_ms / 1000.0), "ms_per_step": o_ms / args.steps},
+              "batched": {"value": 8 * args.steps / (b_ms / 1000.0), "ms_per_step": b_ms / args.steps},
               "bucket_bytes": int(j3.G.bucket.numel() * 4), "num_rendered_last_view": j3.last_state["num_rendered"]}
         if world > 1:
             j3.G.bucket.zero_()
@@ -979,7 +1010,7 @@ def main():
             "gpu_launches": launches_per_step * args.steps,
             "single_view_isolated": {"fwd_bwd_ms": single_view_ms, "renders_per_s": 1000.0 / single_view_ms,
                                      "what": "one view, synchronised before and after (launch ramp included): latency, not throughput"},
-            "overlapped_step": overlapped, "with_optimizer": with_optimizer, "exchange_ms": exchange_ms, "c3_strong": c3,
+            "overlapped_step": overlapped, "batched_step": batched, "with_optimizer": with_optimizer, "exchange_ms": exchange_ms, "c3_strong": c3,
             "stage_ms": stage_ms, "roofline": roof, "roofline_stages": stages, "cpu_baseline": cpu,
         }
         if world == 1 and not args.no_extras:

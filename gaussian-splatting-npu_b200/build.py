@@ -20,7 +20,7 @@ LIB = os.path.join(HERE, "gsr_b200", "libgsr_b200.so")
 PKG = os.path.join(HERE, "diff_gaussian_rasterization")
 
 CU_SOURCES = ["gsr_api.cu", "preprocess_fwd.cu", "binning.cu", "radix_sort.cu", "render_fwd.cu",
-              "render_bwd.cu", "preprocess_bwd.cu", "ssim.cu", "adam.cu", "ply_io.cu", "epilogue.cu", "frame_out.cu", "exchange.cu"]
+              "render_bwd.cu", "preprocess_bwd.cu", "ssim.cu", "adam.cu", "ply_io.cu", "epilogue.cu", "frame_out.cu", "exchange.cu", "preprocess_batch.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
 
@@ -38,7 +38,7 @@ def ext_path():
 
 def build_lib(force=False, verbose=False):
     os.makedirs(OBJ, exist_ok=True)
-    headers = [os.path.join(CSRC, "gsr_common.cuh"), os.path.join(CSRC, "adam_math.cuh"), os.path.join(ROOT, "include", "gsr.h"),
+    headers = [os.path.join(CSRC, "gsr_common.cuh"), os.path.join(CSRC, "adam_math.cuh"), os.path.join(CSRC, "preprocess_math.cuh"), os.path.join(ROOT, "include", "gsr.h"),
                os.path.join(ROOT, "include", "gsr_dist.h"),
                os.path.join(ROOT, "include", "gsr_loss.h"), os.path.join(ROOT, "include", "gsr_optim.h"),
                os.path.join(ROOT, "include", "gsr_ply.h"), os.path.join(ROOT, "include", "gsr_frame.h")]

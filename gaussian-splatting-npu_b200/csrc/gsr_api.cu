@@ -344,6 +344,189 @@ extern "C" int gsr_backward(const gsr_backward_args* a, void* stream_) {
     return GSR_OK;
 }
 
+// ---- the views of a step in one call (include/gsr.h: gsr_forward_batch / gsr_backward_batch) ---------------------
+static int batch_shared_check(int n, int P0, int D0, int M0, const float* m0, const float* sh0, const float* op0, const float* sc0,
+                              const float* ro0, float mod0, int aa0, int P, int D, int M, const float* m, const float* sh,
+                              const float* op, const float* sc, const float* ro, float mod, int aa, const float* colors,
+                              const float* cov3D) {
+    (void)n;
+    if (P != P0 || D != D0 || M != M0 || m != m0 || sh != sh0 || op != op0 || sc != sc0 || ro != ro0 || mod != mod0 || aa != aa0)
+        return fail(GSR_ERR_INVALID, "batch: the views must share the Gaussians, SH layout, scale_modifier and antialiasing");
+    if (colors || cov3D || !sh || M != 16 || !sc || !ro)
+        return fail(GSR_ERR_INVALID, "batch: needs shs with M = 16 and scales + rotations (no colors_precomp / cov3D_precomp)");
+    return GSR_OK;
+}
+
+extern "C" int gsr_forward_batch(int n_views, const gsr_forward_args* views, gsr_alloc_fn geom_alloc, void* const* geom_users,
+                                 gsr_alloc_fn binning_alloc, void* const* binning_users, gsr_alloc_fn image_alloc,
+                                 void* const* image_users, void* stream_, int* num_rendered) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!views || !num_rendered || !geom_alloc || !binning_alloc || !image_alloc || !geom_users || !binning_users || !image_users)
+        return fail(GSR_ERR_INVALID, "null argument");
+    if (n_views < 1 || n_views > GSR_MAX_VIEWS) return fail(GSR_ERR_INVALID, "batch: n_views = %d outside 1..%d", n_views, GSR_MAX_VIEWS);
+    const gsr_forward_args& a0 = views[0];
+    const int P = a0.P;
+    for (int v = 0; v < n_views; v++) {
+        const gsr_forward_args& a = views[v];
+        num_rendered[v] = 0;
+        if (a.P < 0 || a.width <= 0 || a.height <= 0) return fail(GSR_ERR_INVALID, "bad sizes");
+        if (!a.out_color) return fail(GSR_ERR_INVALID, "out_color is null");
+        if (P == 0) continue;
+        if (!a.means3D || !a.opacities || !a.viewmatrix || !a.projmatrix || !a.cam_pos || !a.background || !a.radii)
+            return fail(GSR_ERR_INVALID, "missing required input pointer");
+        if (a.D < 0 || a.D > 3 || (a.D + 1) * (a.D + 1) > a.M) return fail(GSR_ERR_INVALID, "SH degree %d does not fit M=%d", a.D, a.M);
+        if (batch_shared_check(n_views, a0.P, a0.D, a0.M, a0.means3D, a0.shs, a0.opacities, a0.scales, a0.rotations, a0.scale_modifier,
+                               a0.antialiasing, a.P, a.D, a.M, a.means3D, a.shs, a.opacities, a.scales, a.rotations, a.scale_modifier,
+                               a.antialiasing, a.colors_precomp, a.cov3D_precomp)) return GSR_ERR_INVALID;
+        if (a.prefiltered != a0.prefiltered) return fail(GSR_ERR_INVALID, "batch: prefiltered differs between views");
+    }
+    if (P == 0) return GSR_OK;
+    if (check_aligned16(a0.rotations, "rotations") || check_aligned16(a0.shs, "shs")) return GSR_ERR_INVALID;
+
+    GeomView g[GSR_MAX_VIEWS]; ImageView im[GSR_MAX_VIEWS];
+    FwdBatchParams bp;
+    bp.P = P; bp.D = a0.D; bp.V = n_views; bp.prefiltered = a0.prefiltered; bp.antialiasing = a0.antialiasing;
+    bp.scale_modifier = a0.scale_modifier;
+    bp.means3D = a0.means3D; bp.shs = a0.shs; bp.opacities = a0.opacities; bp.scales = a0.scales; bp.rotations = a0.rotations;
+    for (int v = 0; v < n_views; v++) {
+        const gsr_forward_args& a = views[v];
+        char* geom_raw = geom_alloc(gsr_geometry_bytes(P), geom_users[v]);
+        if (!geom_raw) return fail(GSR_ERR_ALLOC, "geometry allocator returned null");
+        char* img_raw = image_alloc(gsr_image_bytes(a.width, a.height), image_users[v]);
+        if (!img_raw) return fail(GSR_ERR_ALLOC, "image allocator returned null");
+        g[v] = geom_view(geom_raw, P);
+        im[v] = image_view(img_raw, a.width, a.height);
+        FwdBatchView& w = bp.view[v];
+        w.viewmatrix = a.viewmatrix; w.projmatrix = a.projmatrix; w.cam_pos = a.cam_pos;
+        w.tan_fovx = a.tan_fovx; w.tan_fovy = a.tan_fovy;
+        w.focal_y = a.height / (2.0f * a.tan_fovy); w.focal_x = a.width / (2.0f * a.tan_fovx);
+        w.W = a.width; w.H = a.height; w.gx = (a.width + GSR_TILE - 1) / GSR_TILE; w.gy = (a.height + GSR_TILE - 1) / GSR_TILE;
+        w.depths = g[v].depths; w.records = g[v].records; w.cov3D = g[v].cov3D; w.clamped = g[v].clamped;
+        w.tiles_touched = g[v].tiles_touched; w.scan_state = g[v].scan_state; w.radii = a.radii;
+        CUDA_TRY(cudaMemsetAsync(g[v].scan_state, 0, gsr_scan_state_words((size_t)P) * 4, stream));
+    }
+    launch_preprocess_fwd_batch(bp, stream);
+    STAGE_CHECK(a0.debug, stream, "preprocess (batch)");
+
+    // per view: scan + counts on their way to the host; then all depth sorts run while the host waits for the counts
+    static thread_local uint32_t* pinned = nullptr;
+    static thread_local cudaEvent_t counts_ready_dev[64] = {};
+    int dev_id = 0;
+    CUDA_TRY(cudaGetDevice(&dev_id));
+    if (dev_id < 0 || dev_id >= 64) return fail(GSR_ERR_INVALID, "device ordinal %d out of range", dev_id);
+    if (!pinned) CUDA_TRY(cudaHostAlloc((void**)&pinned, 4 * 4 * GSR_MAX_VIEWS, cudaHostAllocPortable));
+    if (!counts_ready_dev[dev_id]) CUDA_TRY(cudaEventCreateWithFlags(&counts_ready_dev[dev_id], cudaEventDisableTiming));
+    const int gsort_bits = 32, gsort_passes = (gsort_bits + 7) / 8;
+    const int g0 = (gsort_passes & 1) ? 1 : 0;
+    for (int v = 0; v < n_views; v++) {
+        launch_scan_compact(P, g[v], g[v].gsort_keys[g0], g[v].gsort_vals[g0], stream);
+        CUDA_TRY(cudaMemcpyAsync(pinned + 4 * v, g[v].scan_state + 1, 12, cudaMemcpyDeviceToHost, stream));
+    }
+    CUDA_TRY(cudaEventRecord(counts_ready_dev[dev_id], stream));
+    STAGE_CHECK(a0.debug, stream, "scan (batch)");
+    for (int v = 0; v < n_views; v++) {
+        int in_b = 0;
+        launch_sort_pairs32_pingpong(g[v].gsort_keys[g0], g[v].gsort_vals[g0], g[v].gsort_keys[1 - g0], g[v].gsort_vals[1 - g0],
+                                     (size_t)P, g[v].scan_state + 3, gsort_bits, g[v].gsort_temp, stream, &in_b);
+    }
+    STAGE_CHECK(a0.debug, stream, "depth sort (batch)");
+    CUDA_TRY(cudaEventSynchronize(counts_ready_dev[dev_id]));
+    for (int v = 0; v < n_views; v++) {
+        if (pinned[4 * v]) return fail(GSR_ERR_PREFILTERED, "Point is filtered although prefiltered is set. This shouldn't happen!");
+        if (pinned[4 * v + 1] >= (1u << 30)) return fail(GSR_ERR_INVALID, "num_rendered=%u exceeds the supported 2^30", pinned[4 * v + 1]);
+        num_rendered[v] = (int)pinned[4 * v + 1];
+    }
+    for (int v = 0; v < n_views; v++) {
+        const gsr_forward_args& a = views[v];
+        const size_t N = (size_t)num_rendered[v];
+        const int W = a.width, H = a.height, gx = bp.view[v].gx, gy = bp.view[v].gy;
+        char* bin_raw = binning_alloc(gsr_binning_bytes(N, W, H), binning_users[v]);
+        if (!bin_raw) return fail(GSR_ERR_ALLOC, "binning allocator returned null");
+        BinningView b = binning_view(bin_raw, N, W, H);
+        const int end_bit = (int)higher_msb((uint32_t)(gx * gy));
+        const int passes = (end_bit + 7) / 8;
+        uint32_t* k_start = (passes & 1) ? b.tile_keys_alt : b.tile_keys;
+        uint32_t* v_start = (passes & 1) ? b.point_list_alt : b.point_list;
+        uint32_t* k_other = (passes & 1) ? b.tile_keys : b.tile_keys_alt;
+        uint32_t* v_other = (passes & 1) ? b.point_list : b.point_list_alt;
+        if (N > 0) {
+            launch_sorted_scan(P, g[v], g[v].depth_order, g[v].sorted_offsets, stream);
+            launch_emit_tiles(P, gx, gy, g[v], g[v].depth_order, g[v].sorted_offsets, a.radii, k_start, v_start, stream);
+            int in_b = 0;
+            launch_sort_pairs32_pingpong(k_start, v_start, k_other, v_other, N, nullptr, end_bit, b.sort_temp, stream, &in_b);
+        }
+        launch_tile_ranges(N, b.tile_keys, im[v].ranges, gx * gy, stream);
+        launch_render_fwd(W, H, gx, gy, im[v].ranges, b.point_list, b.block_masks, g[v].records, a.background, im[v].final_T,
+                          im[v].n_contrib, a.out_color, a.out_invdepth, stream);
+        STAGE_CHECK(a.debug, stream, "render (batch)");
+    }
+    return GSR_OK;
+}
+
+extern "C" int gsr_backward_batch(int n_views, const gsr_backward_args* views, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!views) return fail(GSR_ERR_INVALID, "null argument");
+    if (n_views < 1 || n_views > GSR_MAX_VIEWS) return fail(GSR_ERR_INVALID, "batch: n_views = %d outside 1..%d", n_views, GSR_MAX_VIEWS);
+    const gsr_backward_args& a0 = views[0];
+    const int P = a0.P;
+    if (P < 0) return fail(GSR_ERR_INVALID, "bad sizes");
+    if (P == 0) return GSR_OK;
+    if (!a0.dL_dmean3D || !a0.dL_dsh || !a0.dL_dopacity || !a0.dL_dscale || !a0.dL_drot)
+        return fail(GSR_ERR_INVALID, "batch: views[0] must carry the five parameter-gradient outputs");
+    if (check_aligned16(a0.rotations, "rotations") || check_aligned16(a0.dL_drot, "dL_drot") || check_aligned16(a0.shs, "shs") ||
+        check_aligned16(a0.dL_dsh, "dL_dsh")) return GSR_ERR_INVALID;
+    BwdBatchParams bp;
+    bp.P = P; bp.D = a0.D; bp.V = n_views; bp.antialiasing = a0.antialiasing; bp.accumulate = a0.accumulate != 0;
+    bp.scale_modifier = a0.scale_modifier;
+    bp.means3D = a0.means3D; bp.shs = a0.shs; bp.opacities = a0.opacities; bp.scales = a0.scales; bp.rotations = a0.rotations;
+    bp.dL_dmean3D = a0.dL_dmean3D; bp.dL_dsh = a0.dL_dsh; bp.dL_dopacity = a0.dL_dopacity; bp.dL_dscale = a0.dL_dscale; bp.dL_drot = a0.dL_drot;
+    for (int v = 0; v < n_views; v++) {
+        const gsr_backward_args& a = views[v];
+        const int W = a.width, H = a.height;
+        if (W <= 0 || H <= 0 || a.R < 0) return fail(GSR_ERR_INVALID, "bad sizes");
+        if (batch_shared_check(n_views, a0.P, a0.D, a0.M, a0.means3D, a0.shs, a0.opacities, a0.scales, a0.rotations, a0.scale_modifier,
+                               a0.antialiasing, a.P, a.D, a.M, a.means3D, a.shs, a.opacities, a.scales, a.rotations, a.scale_modifier,
+                               a.antialiasing, a.colors_precomp, a.cov3D_precomp)) return GSR_ERR_INVALID;
+        if (!a.geom_buffer || !a.binning_buffer || !a.image_buffer || !a.dL_dpix || !a.radii)
+            return fail(GSR_ERR_INVALID, "missing buffer");
+        if (!a.dL_dmean2D || !a.dL_dconic || !a.dL_dcolor) return fail(GSR_ERR_INVALID, "missing per-view gradient output");
+        if (a.dL_dinvdepth_pix && !a.dL_dinvdepth) return fail(GSR_ERR_INVALID, "dL_dinvdepth output required");
+        if (check_aligned16(a.dL_dconic, "dL_dconic")) return GSR_ERR_INVALID;
+        const int gx = (W + GSR_TILE - 1) / GSR_TILE, gy = (H + GSR_TILE - 1) / GSR_TILE;
+        GeomView g = geom_view(a.geom_buffer, P);
+        ImageView im = image_view(a.image_buffer, W, H);
+        BinningView b = binning_view(a.binning_buffer, (size_t)a.R, W, H);
+        BwdParams p;
+        memset(&p, 0, sizeof(p));
+        p.P = P; p.D = a.D; p.M = a.M; p.W = W; p.H = H; p.gx = gx; p.gy = gy;
+        p.background = a.background;
+        p.dop_view = reinterpret_cast<float*>(g.gsort_keys[0]);
+        p.dL_dpix = a.dL_dpix; p.dL_dinvdepth_pix = a.dL_dinvdepth_pix;
+        p.dL_dmean2D = a.dL_dmean2D; p.dL_dconic = a.dL_dconic; p.dL_dcolor = a.dL_dcolor;
+        p.dL_dinvdepth = a.dL_dinvdepth_pix ? a.dL_dinvdepth : nullptr;
+        const size_t sp = (size_t)P;
+        CUDA_TRY(cudaMemsetAsync(a.dL_dmean2D, 0, sp * 3 * 4, stream));
+        CUDA_TRY(cudaMemsetAsync(a.dL_dconic, 0, sp * 4 * 4, stream));
+        CUDA_TRY(cudaMemsetAsync(p.dop_view, 0, sp * 4, stream));
+        CUDA_TRY(cudaMemsetAsync(a.dL_dcolor, 0, sp * 3 * 4, stream));
+        if (p.dL_dinvdepth) CUDA_TRY(cudaMemsetAsync(p.dL_dinvdepth, 0, sp * 4, stream));
+        if (a.R > 0) {
+            launch_render_bwd(p, im.ranges, b.point_list, b.block_masks, g.records, im.final_T, im.n_contrib, stream);
+            STAGE_CHECK(a.debug, stream, "render backward (batch)");
+        }
+        BwdBatchView& w = bp.view[v];
+        w.viewmatrix = a.viewmatrix; w.projmatrix = a.projmatrix; w.cam_pos = a.cam_pos;
+        w.tan_fovx = a.tan_fovx; w.tan_fovy = a.tan_fovy;
+        w.focal_y = H / (2.0f * a.tan_fovy); w.focal_x = W / (2.0f * a.tan_fovx);
+        w.radii = a.radii; w.clamped = g.clamped;
+        w.dL_dconic = a.dL_dconic; w.dL_dmean2D = a.dL_dmean2D; w.dL_dcolor = a.dL_dcolor; w.dL_dinvdepth = p.dL_dinvdepth;
+        w.dop_view = p.dop_view;
+    }
+    launch_preprocess_bwd_batch(bp, stream);
+    STAGE_CHECK(a0.debug, stream, "preprocess backward (batch)");
+    return GSR_OK;
+}
+
 extern "C" int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                                 unsigned char* present, void* stream_) {
     (void)projmatrix;   // the reference's projected-bounds test is commented out (auxiliary.h:166)

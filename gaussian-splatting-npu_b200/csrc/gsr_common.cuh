@@ -263,3 +263,35 @@ void launch_render_bwd(const BwdParams& p, const uint2* ranges, const uint32_t* 
                        const unsigned char* block_masks, const float4* records, const float* final_T, const uint32_t* n_contrib,
                        cudaStream_t s);
 void launch_preprocess_bwd(const BwdParams& p, const GeomView& g, cudaStream_t s);
+
+// ---- all cameras of a step in one launch (preprocess_batch.cu) ---------------------------------------
+#define GSR_MAX_VIEWS 8
+struct FwdBatchView {
+    const float *viewmatrix, *projmatrix, *cam_pos;
+    float tan_fovx, tan_fovy, focal_x, focal_y;
+    int W, H, gx, gy;
+    float* depths; float4* records; float* cov3D; unsigned char* clamped; uint32_t* tiles_touched; uint32_t* scan_state;
+    int* radii;
+};
+struct FwdBatchParams {
+    int P, D, V, prefiltered, antialiasing;
+    float scale_modifier;
+    const float *means3D, *shs, *opacities, *scales, *rotations;
+    FwdBatchView view[GSR_MAX_VIEWS];
+};
+struct BwdBatchView {
+    const float *viewmatrix, *projmatrix, *cam_pos;
+    float tan_fovx, tan_fovy, focal_x, focal_y;
+    const int* radii;
+    const unsigned char* clamped;
+    const float *dL_dconic, *dL_dmean2D, *dL_dcolor, *dL_dinvdepth, *dop_view;
+};
+struct BwdBatchParams {
+    int P, D, V, antialiasing, accumulate;
+    float scale_modifier;
+    const float *means3D, *shs, *opacities, *scales, *rotations;
+    float *dL_dmean3D, *dL_dsh, *dL_dopacity, *dL_dscale, *dL_drot;
+    BwdBatchView view[GSR_MAX_VIEWS];
+};
+void launch_preprocess_fwd_batch(const FwdBatchParams& p, cudaStream_t s);
+void launch_preprocess_bwd_batch(const BwdBatchParams& p, cudaStream_t s);

@@ -12,133 +12,10 @@
 //   * the clamp flags are one bitmask byte.
 // Every value that feeds a bit-exact output (depth, radius, rect, pixel centre, conic, opacity) is
 // computed with explicitly rounded intrinsics in the reference build's own FFMA placement.
-#include "gsr_common.cuh"
+#include "preprocess_math.cuh"
 
 #define PRE_THREADS 128
 #define PRE_WARPS (PRE_THREADS / 32)
-
-__device__ __forceinline__ void cov3d_from_scale_rot(const float sx_, const float sy_, const float sz_, float mod,
-                                                     float4 q, float* cov) {
-    const float sx = fmul(mod, sx_), sy = fmul(mod, sy_), sz = fmul(mod, sz_);
-    const float r = q.x, x = q.y, y = q.z, z = q.w;
-    const float xz = fmul(x, z), rx = fmul(r, x), yy = fmul(y, y), rz = fmul(r, z), zz = fmul(z, z);
-    const float xz_p_ry = ffma(r, y, xz);
-    const float xz_m_ry = ffma(-r, y, xz);
-    const float yz_m_rx = ffma(y, z, -rx);
-    const float yz_p_rx = ffma(y, z, rx);
-    const float xx_p_yy = ffma(x, x, yy);
-    const float xy_m_rz = ffma(x, y, -rz);
-    const float xy_p_rz = ffma(x, y, rz);
-    const float yy_p_zz = fadd(yy, zz);
-    const float xx_p_zz = ffma(x, x, zz);
-    const float R00 = fsub(1.0f, fadd(yy_p_zz, yy_p_zz));
-    const float R11 = fsub(1.0f, fadd(xx_p_zz, xx_p_zz));
-    const float R22 = fsub(1.0f, fadd(xx_p_yy, xx_p_yy));
-    const float m00 = fmul(sx, R00), m01 = fmul(sy, fadd(xy_m_rz, xy_m_rz)), m02 = fmul(sz, fadd(xz_p_ry, xz_p_ry));
-    const float m10 = fmul(sx, fadd(xy_p_rz, xy_p_rz)), m11 = fmul(sy, R11), m12 = fmul(sz, fadd(yz_m_rx, yz_m_rx));
-    const float m20 = fmul(sx, fadd(xz_m_ry, xz_m_ry)), m21 = fmul(sy, fadd(yz_p_rx, yz_p_rx)), m22 = fmul(sz, R22);
-    cov[0] = ffma(m02, m02, ffma(m00, m00, fmul(m01, m01)));
-    cov[1] = ffma(m12, m02, ffma(m10, m00, fmul(m11, m01)));
-    cov[2] = ffma(m22, m02, ffma(m20, m00, fmul(m21, m01)));
-    cov[3] = ffma(m12, m12, ffma(m10, m10, fmul(m11, m11)));
-    cov[4] = ffma(m22, m12, ffma(m20, m10, fmul(m21, m11)));
-    cov[5] = ffma(m22, m22, ffma(m20, m20, fmul(m21, m21)));
-}
-
-__device__ __forceinline__ void cov2d_ewa(float x, float y, float z, float fx, float fy, float tanx, float tany,
-                                          const float* c, const float* V, float& cxx, float& cxy, float& cyy) {
-    const float tx = xform_row(V, 0, x, y, z);
-    const float ty = xform_row(V, 1, x, y, z);
-    const float tz = xform_row(V, 2, x, y, z);
-    const float limx = fmul(tanx, 1.3f), limy = fmul(tany, 1.3f);
-    const float cx = fminf(limx, fmaxf(-limx, fdiv(tx, tz)));
-    const float cy = fminf(limy, fmaxf(-limy, fdiv(ty, tz)));
-    const float ntz = -tz, tz2 = fmul(tz, tz);
-    const float J00 = fdiv(fx, tz);
-    const float J02 = fdiv(fmul(fx, fmul(cx, ntz)), tz2);
-    const float J11 = fdiv(fy, tz);
-    const float J12 = fdiv(fmul(fy, fmul(cy, ntz)), tz2);
-    const float T00 = ffma(V[2], J02, fmul(V[0], J00));
-    const float T01 = ffma(V[6], J02, fmul(V[4], J00));
-    const float T02 = ffma(J02, V[10], fmul(V[8], J00));
-    const float T10 = ffma(V[2], J12, fmul(J11, V[1]));
-    const float T11 = ffma(V[6], J12, fmul(J11, V[5]));
-    const float T12 = ffma(J12, V[10], fmul(J11, V[9]));
-    const float a0 = ffma(T02, c[2], ffma(T00, c[0], fmul(T01, c[1])));
-    const float b0 = ffma(T12, c[2], ffma(T10, c[0], fmul(T11, c[1])));
-    const float a1 = ffma(T02, c[4], ffma(T00, c[1], fmul(T01, c[3])));
-    const float b1 = ffma(T12, c[4], ffma(T10, c[1], fmul(T11, c[3])));
-    const float a2 = ffma(T02, c[5], ffma(T00, c[2], fmul(T01, c[4])));
-    const float b2 = ffma(T12, c[5], ffma(T10, c[2], fmul(T11, c[4])));
-    cxx = ffma(T02, a2, ffma(T00, a0, fmul(T01, a1)));
-    cxy = ffma(T02, b2, ffma(T00, b0, fmul(T01, b1)));
-    cyy = ffma(T12, b2, ffma(T10, b0, fmul(T11, b1)));
-}
-
-// SH basis (reference auxiliary.h:21-38)
-#define SHC0 0.28209479177387814f
-#define SHC1 0.4886025119029199f
-#define SHC2_0 1.0925484305920792f
-#define SHC2_1 -1.0925484305920792f
-#define SHC2_2 0.31539156525252005f
-#define SHC2_3 -1.0925484305920792f
-#define SHC2_4 0.5462742152960396f
-#define SHC3_0 -0.5900435899266435f
-#define SHC3_1 2.890611442640554f
-#define SHC3_2 -0.4570457994644658f
-#define SHC3_3 0.3731763325901154f
-#define SHC3_4 -0.4570457994644658f
-#define SHC3_5 1.445305721320277f
-#define SHC3_6 -0.5900435899266435f
-
-// Colour from an SH row (forward.cu:20-71).  `E(i)` yields element i = k*3+c of the row; the row is
-// streamed (from the swizzled shared-memory stage, or from global for generic M) band by band so
-// that no 48-float register array is ever live, and coefficients above the active degree are
-// never touched (they may hold anything).
-template <typename Row>
-__device__ __forceinline__ void sh_to_rgb(int deg, const Row& E, float dx, float dy, float dz,
-                                          float& r, float& g, float& b, unsigned& clamp_bits) {
-    const float len = sqrtf(fmaf(dz, dz, fmaf(dx, dx, dy * dy)));
-    const float x = dx / len, y = dy / len, z = dz / len;
-    float res[3];
-#pragma unroll
-    for (int c = 0; c < 3; c++) res[c] = SHC0 * E(c);
-    if (deg > 0) {
-#pragma unroll
-        for (int c = 0; c < 3; c++) res[c] = res[c] - SHC1 * y * E(3 + c) + SHC1 * z * E(6 + c) - SHC1 * x * E(9 + c);
-        if (deg > 1) {
-            const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-#pragma unroll
-            for (int c = 0; c < 3; c++)
-                res[c] = res[c] + SHC2_0 * xy * E(12 + c) + SHC2_1 * yz * E(15 + c) +
-                         SHC2_2 * (2.0f * zz - xx - yy) * E(18 + c) + SHC2_3 * xz * E(21 + c) +
-                         SHC2_4 * (xx - yy) * E(24 + c);
-            if (deg > 2) {
-#pragma unroll
-                for (int c = 0; c < 3; c++)
-                    res[c] = res[c] + SHC3_0 * y * (3.0f * xx - yy) * E(27 + c) + SHC3_1 * xy * z * E(30 + c) +
-                             SHC3_2 * y * (4.0f * zz - xx - yy) * E(33 + c) +
-                             SHC3_3 * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * E(36 + c) +
-                             SHC3_4 * x * (4.0f * zz - xx - yy) * E(39 + c) + SHC3_5 * z * (xx - yy) * E(42 + c) +
-                             SHC3_6 * x * (xx - 3.0f * yy) * E(45 + c);
-            }
-        }
-    }
-#pragma unroll
-    for (int c = 0; c < 3; c++) res[c] += 0.5f;
-    clamp_bits = (res[0] < 0.0f ? 1u : 0u) | (res[1] < 0.0f ? 2u : 0u) | (res[2] < 0.0f ? 4u : 0u);
-    r = fmaxf(res[0], 0.0f); g = fmaxf(res[1], 0.0f); b = fmaxf(res[2], 0.0f);
-}
-
-// element i of lane's row in the swizzled stage (float index (row*12 + (j ^ swz))*4 + i%4)
-struct StageRow {
-    const float* base; int swz;
-    __device__ __forceinline__ float operator()(int i) const { return base[(((i >> 2) ^ swz) << 2) + (i & 3)]; }
-};
-struct GlobalRow {
-    const float* row; int limit;
-    __device__ __forceinline__ float operator()(int i) const { return i < limit ? row[i] : 0.0f; }
-};
 
 template <bool SH16>
 __global__ void __launch_bounds__(PRE_THREADS)
@@ -168,47 +45,29 @@ preprocess_fwd_kernel(FwdParams p, GeomView g, int* __restrict__ radii) {
             s0 = p.scales[3 * (size_t)i]; s1 = p.scales[3 * (size_t)i + 1]; s2 = p.scales[3 * (size_t)i + 2];
         }
         const float opacity_in = p.opacities[i];
-        pvz = xform_row(V, 2, x, y, z);
-        if (pvz <= 0.2f) {
-            if (p.prefiltered) atomicAdd(&g.scan_state[1], 1u);
-        } else {
-            const float hx = xform_row(PM, 0, x, y, z), hy = xform_row(PM, 1, x, y, z), hw = xform_row(PM, 3, x, y, z);
-            const float pw = frcp(fadd(hw, 0.0000001f));
-            const float ppx = fmul(hx, pw), ppy = fmul(hy, pw);
-            float c6[6];
+        float c6[6] = { 0, 0, 0, 0, 0, 0 };
+        const bool near_ok = xform_row(V, 2, x, y, z) > 0.2f;
+        if (near_ok) {
             if (p.cov3D_precomp) {
 #pragma unroll
                 for (int k = 0; k < 6; k++) c6[k] = p.cov3D_precomp[6 * (size_t)i + k];
             } else {
                 cov3d_from_scale_rot(s0, s1, s2, p.scale_modifier, q, c6);
             }
-            float cxx, cxy, cyy;
-            cov2d_ewa(x, y, z, p.focal_x, p.focal_y, p.tan_fovx, p.tan_fovy, c6, V, cxx, cxy, cyy);
-            const float yy = fmul(cxy, cxy);
-            const float det_cov = ffma(cxx, cyy, -yy);
-            const float cxh = fadd(cxx, 0.3f), czh = fadd(cyy, 0.3f);
-            const float det = ffma(cxh, czh, -yy);
-            float hscale = 1.0f;
-            if (p.antialiasing) hscale = fsqrt(fmaxf(fdiv(det_cov, det), 0.000025f));
-            if (det != 0.0f) {
-                const float dinv = frcp(det);
-                conx = fmul(czh, dinv); cony = fmul(dinv, -cxy); conz = fmul(cxh, dinv);
-                const float mid = fmul(fadd(cxh, czh), 0.5f);
-                const float sq = fsqrt(fmaxf(ffma(mid, mid, -det), 0.1f));
-                const float l1 = fadd(mid, sq), l2 = fsub(mid, sq);
-                const float rad_f = ceilf(fmul(fsqrt(fmaxf(l1, l2)), 3.0f));
-                px = ndc2pix(ppx, p.W); py = ndc2pix(ppy, p.H);
-                rad = __float2int_rz(rad_f);
-                int x0, y0, x1, y1;
-                get_rect(px, py, rad, p.gx, p.gy, x0, y0, x1, y1);
-                tiles = (x1 - x0) * (y1 - y0);
-                if (tiles != 0) {
-                    visible = true;
-                    opac = fmul(opacity_in, hscale);
-                    if (!p.cov3D_precomp) {
-                        float2* cv = reinterpret_cast<float2*>(g.cov3D + 6 * (size_t)i);
-                        cv[0] = make_float2(c6[0], c6[1]); cv[1] = make_float2(c6[2], c6[3]); cv[2] = make_float2(c6[4], c6[5]);
-                    }
+        }
+        const Projected pj = project_gaussian(V, PM, p.focal_x, p.focal_y, p.tan_fovx, p.tan_fovy, p.W, p.H, p.gx, p.gy,
+                                              p.antialiasing != 0, x, y, z, c6, opacity_in);
+        pvz = pj.pvz;
+        if (pj.near_culled) {
+            if (p.prefiltered) atomicAdd(&g.scan_state[1], 1u);
+        } else {
+            conx = pj.conx; cony = pj.cony; conz = pj.conz; px = pj.px; py = pj.py; rad = pj.rad; tiles = pj.tiles;
+            if (pj.visible) {
+                visible = true;
+                opac = pj.opac;
+                if (!p.cov3D_precomp) {
+                    float2* cv = reinterpret_cast<float2*>(g.cov3D + 6 * (size_t)i);
+                    cv[0] = make_float2(c6[0], c6[1]); cv[1] = make_float2(c6[2], c6[3]); cv[2] = make_float2(c6[4], c6[5]);
                 }
             }
         }

@@ -66,7 +66,7 @@ class AdamSegment(ctypes.Structure):
                 ("rows", c_size_t), ("cols", c_int), ("split_col", c_int), ("lr_a", c_float), ("lr_b", c_float)]
 
 
-EXPORTS = ["gsr_forward", "gsr_backward", "gsr_mark_visible", "gsr_geometry_bytes", "gsr_image_bytes",
+EXPORTS = ["gsr_forward", "gsr_backward", "gsr_forward_batch", "gsr_backward_batch", "gsr_mark_visible", "gsr_geometry_bytes", "gsr_image_bytes",
            "gsr_binning_bytes", "gsr_sort_temp_bytes", "gsr_sort_pairs", "gsr_get_geometry_layout",
            "gsr_get_binning_layout", "gsr_get_image_layout", "gsr_materialize_keys", "gsr_set_profiling",
            "gsr_last_stage_ms",
@@ -117,6 +117,11 @@ def lib():
         L.gsr_get_image_layout.argtypes = [c_int, c_int, POINTER(ImageLayout)]
         L.gsr_materialize_keys.restype = c_int
         L.gsr_materialize_keys.argtypes = [c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]
+        L.gsr_forward_batch.restype = c_int
+        L.gsr_forward_batch.argtypes = [c_int, POINTER(ForwardArgs), ALLOC_FN, POINTER(c_void_p), ALLOC_FN, POINTER(c_void_p), ALLOC_FN,
+                                        POINTER(c_void_p), c_void_p, POINTER(c_int)]
+        L.gsr_backward_batch.restype = c_int
+        L.gsr_backward_batch.argtypes = [c_int, POINTER(BackwardArgs), c_void_p]
         L.gsr_set_profiling.argtypes = [c_int]
         L.gsr_last_stage_ms.restype = c_float
         L.gsr_last_stage_ms.argtypes = [c_int]
@@ -174,25 +179,21 @@ class _Buf:
     def __init__(self, device):
         self.t = torch.empty(0, dtype=torch.uint8, device=device)
         self.device = device
+        self.cb = ALLOC_FN(lambda nbytes, _user: self.alloc(nbytes))
 
-        def cb(nbytes, _user):
-            self.t = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
-            return self.t.data_ptr()
-        self.cb = ALLOC_FN(cb)
+    def alloc(self, nbytes):
+        self.t = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+        return self.t.data_ptr()
 
 
 class _GrowBuf(_Buf):
     """A scratch tensor that only grows (25 % headroom): a request that fits is served without touching the allocator."""
 
-    def __init__(self, device):
-        super().__init__(device)
-
-        def cb(nbytes, _user):
-            if self.t.numel() < nbytes:
-                self.t = torch.empty(0, dtype=torch.uint8, device=self.device)     # release before growing
-                self.t = torch.empty(int(nbytes) + int(nbytes) // 4, dtype=torch.uint8, device=self.device)
-            return self.t.data_ptr()
-        self.cb = ALLOC_FN(cb)
+    def alloc(self, nbytes):
+        if self.t.numel() < nbytes:
+            self.t = torch.empty(0, dtype=torch.uint8, device=self.device)     # release before growing
+            self.t = torch.empty(int(nbytes) + int(nbytes) // 4, dtype=torch.uint8, device=self.device)
+        return self.t.data_ptr()
 
 
 class Workspace:
@@ -281,6 +282,87 @@ def backward(state, *, dL_dcolor, dL_dinvdepth=None, means3D, opacities, viewmat
     with torch.cuda.device(dev):
         _check(L.gsr_backward(ctypes.byref(a), _stream()))
     return g
+
+
+_CAMERA_KEYS = ("viewmatrix", "projmatrix", "cam_pos", "tan_fovx", "tan_fovy")
+
+
+def forward_batch(cameras, *, means3D, opacities, background, width, height, shs, scales, rotations, sh_degree=3,
+                  scale_modifier=1.0, prefiltered=False, antialiasing=False, debug=False, want_invdepth=True, workspaces=None):
+    """gsr_forward_batch: the views of a step in one call -- the per-Gaussian stage runs once for all cameras (parameters
+    and SH rows read once), the rest per view.  `cameras`: list of dicts(viewmatrix, projmatrix, cam_pos, tan_fovx,
+    tan_fovy[, width, height]).  Returns one state per view, identical to forward()'s."""
+    L = lib()
+    dev = means3D.device
+    P, M, V = means3D.shape[0], shs.shape[1], len(cameras)
+    arr = (ForwardArgs * V)()
+    bufs, outs = [], []
+    for v, c in enumerate(cameras):
+        w, h = c.get("width", width), c.get("height", height)
+        out_color = torch.empty(3, h, w, dtype=torch.float32, device=dev)
+        out_invdepth = torch.empty(1, h, w, dtype=torch.float32, device=dev) if want_invdepth else None
+        radii = torch.empty(P, dtype=torch.int32, device=dev)
+        arr[v] = ForwardArgs(P, sh_degree, M, w, h, _ptr(background), _ptr(means3D), _ptr(shs), None, _ptr(opacities),
+                             _ptr(scales), scale_modifier, _ptr(rotations), None, _ptr(c["viewmatrix"]), _ptr(c["projmatrix"]),
+                             _ptr(c["cam_pos"]), c["tan_fovx"], c["tan_fovy"], int(prefiltered), int(antialiasing), int(debug),
+                             _ptr(out_color), _ptr(out_invdepth), _ptr(radii))
+        ws = workspaces[v] if workspaces is not None else None
+        bufs.append((ws.geom, ws.binning, ws.img) if ws is not None else (_Buf(dev), _Buf(dev), _Buf(dev)))
+        outs.append((out_color, out_invdepth, radii, w, h))
+    # one callback per buffer kind; the user pointer carries the view index (+1: NULL arrives as None)
+    cbs = [ALLOC_FN(lambda nbytes, user, k=k: bufs[int(user) - 1][k].alloc(nbytes)) for k in range(3)]
+    users = (c_void_p * V)(*[c_void_p(v + 1) for v in range(V)])
+    n = (c_int * V)()
+    with torch.cuda.device(dev):
+        _check(L.gsr_forward_batch(V, arr, cbs[0], users, cbs[1], users, cbs[2], users, _stream(), n))
+    return [dict(num_rendered=n[v], out_color=outs[v][0], out_invdepth=outs[v][1], radii=outs[v][2], geom=bufs[v][0].t,
+                 binning=bufs[v][1].t, img=bufs[v][2].t, P=P, W=outs[v][3], H=outs[v][4], M=M) for v in range(V)]
+
+
+def backward_batch(states, cameras, *, dL_dcolor, dL_dinvdepth=None, means3D, opacities, background, shs, scales, rotations,
+                   sh_degree=3, scale_modifier=1.0, antialiasing=False, debug=False, out=None, accumulate=False, scratch=None):
+    """gsr_backward_batch: per view the backward blend, then ONE per-Gaussian launch that sums the views' gradients in
+    registers and writes (or, with `accumulate`, adds) the five parameter gradients once.  dL_dcolor / dL_dinvdepth: one
+    tensor per view (or one shared by all).  `out`: the five parameter-gradient tensors (e.g. views of the exchange
+    bucket); `scratch`: optional list of per-view dicts with dL_dmeans2D / dL_dconic / dL_dcolors / dL_dinvdepths.
+    Returns (parameter gradients, list of per-view dicts)."""
+    L = lib()
+    dev = means3D.device
+    V = len(states)
+    P, M = states[0]["P"], states[0]["M"]
+    e = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)
+    out = out or {}
+    g = {}
+    for k, shp in dict(dL_dmeans3D=(P, 3), dL_dsh=(P, M, 3), dL_dopacity=(P, 1), dL_dscales=(P, 3), dL_drotations=(P, 4)).items():
+        g[k] = out[k] if out.get(k) is not None else e(*shp)
+        assert g[k].is_contiguous() and g[k].numel() == math.prod(shp) and g[k].data_ptr() % 16 == 0
+    per_view = []
+    arr = (BackwardArgs * V)()
+    for v, (st, c) in enumerate(zip(states, cameras)):
+        s = scratch[v] if scratch is not None else {}
+        pv = dict(dL_dmeans2D=s.get("dL_dmeans2D", None), dL_dconic=s.get("dL_dconic", None), dL_dcolors=s.get("dL_dcolors", None),
+                  dL_dinvdepths=s.get("dL_dinvdepths", None))
+        pv["dL_dmeans2D"] = pv["dL_dmeans2D"] if pv["dL_dmeans2D"] is not None else e(P, 3)
+        pv["dL_dconic"] = pv["dL_dconic"] if pv["dL_dconic"] is not None else e(P, 2, 2)
+        pv["dL_dcolors"] = pv["dL_dcolors"] if pv["dL_dcolors"] is not None else e(P, 3)
+        dcol = dL_dcolor[v] if isinstance(dL_dcolor, (list, tuple)) else dL_dcolor
+        ddep = dL_dinvdepth[v] if isinstance(dL_dinvdepth, (list, tuple)) else dL_dinvdepth
+        if ddep is not None and pv["dL_dinvdepths"] is None:
+            pv["dL_dinvdepths"] = e(P, 1)
+        first = v == 0
+        arr[v] = BackwardArgs(P, sh_degree, M, st["num_rendered"], st["W"], st["H"], _ptr(background), _ptr(means3D), _ptr(shs),
+                              None, _ptr(opacities), _ptr(scales), scale_modifier, _ptr(rotations), None, _ptr(c["viewmatrix"]),
+                              _ptr(c["projmatrix"]), _ptr(c["cam_pos"]), c["tan_fovx"], c["tan_fovy"], _ptr(st["radii"]),
+                              _ptr(st["geom"]), _ptr(st["binning"]), _ptr(st["img"]), _ptr(dcol), _ptr(ddep),
+                              _ptr(pv["dL_dmeans2D"]), _ptr(pv["dL_dconic"]), _ptr(g["dL_dopacity"]) if first else None,
+                              _ptr(pv["dL_dcolors"]), _ptr(pv["dL_dinvdepths"]) if ddep is not None else None,
+                              _ptr(g["dL_dmeans3D"]) if first else None, None, _ptr(g["dL_dsh"]) if first else None,
+                              _ptr(g["dL_dscales"]) if first else None, _ptr(g["dL_drotations"]) if first else None,
+                              int(antialiasing), int(debug), int(accumulate))
+        per_view.append(pv)
+    with torch.cuda.device(dev):
+        _check(L.gsr_backward_batch(V, arr, _stream()))
+    return g, per_view
 
 
 def mark_visible(means3D, viewmatrix, projmatrix):

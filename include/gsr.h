@@ -134,6 +134,31 @@ int gsr_forward(const gsr_forward_args* args,
 /* Rasterizer::backward (rasterizer.h:63, rasterizer_impl.cu:345-450).  Asynchronous on `stream`. */
 int gsr_backward(const gsr_backward_args* args, void* stream);
 
+/*
+ * The views of one step in one call.  The reference renders the cameras of a step -- a
+ * training batch, or the frames of render.py:30-46 -- one Rasterizer::forward / backward after another
+ * (train.py:74-87, :111), and every call reads every Gaussian again.  Here the per-Gaussian stages run ONCE for all
+ * n_views cameras: parameters and the SH row are read once in the forward (preprocess_fwd_batch_kernel) and the 59
+ * parameter-gradient floats are written once in the backward (preprocess_bwd_batch_kernel, the views' gradients summed
+ * in registers); everything between (scan, sorts, key emission, tile ranges, the two blend kernels) runs per view as in
+ * gsr_forward / gsr_backward, and every per-view output is bit-identical to the single-view call's.
+ *
+ * views[v] are ordinary argument structs that differ in camera, image size and per-view outputs only: P, D, M (= 16),
+ * means3D, shs, opacities, scales, rotations, scale_modifier, prefiltered and antialiasing must be the same in all of them,
+ * and colors_precomp / cov3D_precomp must be NULL (other configurations: call the single-view entry points).
+ * 1 <= n_views <= GSR_MAX_BATCH_VIEWS.  The allocators are called once per view with that view's user pointer.
+ * gsr_backward_batch writes (accumulate = 0) or adds (accumulate = 1, taken from views[0]) the SUM over the views into the
+ * parameter-gradient outputs of views[0] (dL_dmean3D, dL_dsh, dL_dopacity, dL_dscale, dL_drot); the per-view outputs
+ * dL_dmean2D, dL_dconic, dL_dcolor, dL_dinvdepth are those of each view; dL_dcov3D is not produced (it only exists per view).
+ */
+#define GSR_MAX_BATCH_VIEWS 8
+int gsr_forward_batch(int n_views, const gsr_forward_args* views,
+                      gsr_alloc_fn geom_alloc, void* const* geom_users,
+                      gsr_alloc_fn binning_alloc, void* const* binning_users,
+                      gsr_alloc_fn image_alloc, void* const* image_users,
+                      void* stream, int* num_rendered /* [n_views] */);
+int gsr_backward_batch(int n_views, const gsr_backward_args* views, void* stream);
+
 /* Rasterizer::markVisible (rasterizer.h:28-33, rasterizer_impl.cu:141-153). present is bool[P] (1 byte each). */
 int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      unsigned char* present, void* stream);
