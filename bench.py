@@ -525,7 +525,7 @@ class Job:
         self.render_views(n_streams)
         self.exchange_gradients()
 
-    def step_batched(self):
+    def step_batched(self, n_streams=1):
         """The same V views through gsr_forward_batch / gsr_backward_batch: the per-Gaussian stages run ONCE for all
         cameras (parameters and SH rows read once, the 59 gradient floats written once), the rest per view."""
         capi, torch = self.capi, self.torch
@@ -536,9 +536,11 @@ class Job:
             self.batch_scratch = [dict(dL_dmeans2D=e(P, 3), dL_dconic=e(P, 2, 2), dL_dcolors=e(P, 3), dL_dinvdepths=e(P, 1))
                                   for _ in range(self.V)]
         cam_kw = [{k: pv[k] for k in ("viewmatrix", "projmatrix", "cam_pos", "tan_fovx", "tan_fovy")} for pv in self.per_view]
-        states = capi.forward_batch(cam_kw, width=self.w["W"], height=self.w["H"], workspaces=self.batch_ws, **self.shared)
+        streams = None if n_streams <= 1 else [torch.cuda.current_stream()] + self.streams[n_streams].side
+        states = capi.forward_batch(cam_kw, width=self.w["W"], height=self.w["H"], workspaces=self.batch_ws, streams=streams,
+                                    **self.shared)
         capi.backward_batch(states, cam_kw, dL_dcolor=self.dcol, dL_dinvdepth=self.ddep, out=self.grad_views,
-                            scratch=self.batch_scratch, **self.shared)
+                            scratch=self.batch_scratch, streams=streams, **self.shared)
         self.last_state = states[-1]
         self.exchange_gradients()
 
@@ -724,12 +726,14 @@ def main():
                           "stages of one view run under the blend kernels of its neighbours" % S}
 
     # ---------------- the same views through the batched entry points (own key; not `value`) ----------------
-    bt_ms, _, _ = time_steps(torch, dist, dev, world, job.step_batched, args.steps, warm, min_warm_s=0.3)
+    bt_ms, _, _ = time_steps(torch, dist, dev, world, lambda: job.step_batched(S), args.steps, warm, min_warm_s=0.3)
+    b1_ms, _, _ = time_steps(torch, dist, dev, world, lambda: job.step_batched(1), args.steps, warm, min_warm_s=0.3)
     batched = {"value": world * V * args.steps / (bt_ms / 1000.0), "unit": "renders/s", "ms_per_step": bt_ms / args.steps,
-               "ms_per_view": bt_ms / args.steps / V,
-               "what": "the same %d views through gsr_forward_batch / gsr_backward_batch on one stream: ONE per-Gaussian launch each way "
-                       "for all cameras (parameters and SH rows read once, the 59 gradient floats written once), scan / sorts / "
-                       "emission / blend per view" % V}
+               "ms_per_view": bt_ms / args.steps / V, "streams": S,
+               "one_stream": {"value": world * V * args.steps / (b1_ms / 1000.0), "ms_per_step": b1_ms / args.steps},
+               "what": "the same %d views through gsr_forward_batch / gsr_backward_batch: ONE per-Gaussian launch each way for all cameras "
+                       "(parameters and SH rows read once, the 59 gradient floats written once), scan / sorts / emission / blend per "
+                       "view, the views' chains on %d streams (`one_stream`: everything on one)" % (V, S)}
     if hasattr(job, "batch_ws"):
         del job.batch_ws, job.batch_scratch
         torch.cuda.empty_cache()
@@ -898,13 +902,13 @@ def main():
         t_ms, _, _ = time_steps(torch, dist, dev, world, lambda: j3.step_train(1), args.steps, warm, min_warm_s=0.3)
         j3.restore_params(saved)
         o_ms, _, _ = time_steps(torch, dist, dev, world, lambda: j3.step_render(S), args.steps, warm, min_warm_s=0.3)
-        b_ms, _, _ = time_steps(torch, dist, dev, world, j3.step_batched, args.steps, warm, min_warm_s=0.3)
+        b_ms, _, _ = time_steps(torch, dist, dev, world, lambda: j3.step_batched(S), args.steps, warm, min_warm_s=0.3)
         c3 = {"workload": "c3: " + WORKLOADS["c3"]["desc"] + "; 8 views per step IN TOTAL, %d per rank, gradient exchange every step" % (8 // world),
               "scaling": "strong", "n_gpus": world, "views_per_step": 8, "exchange": args.exchange if world > 1 else None,
               "value": 8 * args.steps / (r_ms / 1000.0), "unit": "views/s", "ms_per_step": r_ms / args.steps,
               "with_optimizer": {"value": 8 * args.steps / (t_ms / 1000.0), "ms_per_step": t_ms / args.steps},
               "overlapped_%d_streams" % S: {"value": 8 * args.steps / (o_ms / 1000.0), "ms_per_step": o_ms / args.steps},
-              "batched": {"value": 8 * args.steps / (b_ms / 1000.0), "ms_per_step": b_ms / args.steps},
+              "batched_%d_streams" % S: {"value": 8 * args.steps / (b_ms / 1000.0), "ms_per_step": b_ms / args.steps},
               "bucket_bytes": int(j3.G.bucket.numel() * 4), "num_rendered_last_view": j3.last_state["num_rendered"]}
         if world > 1:
             j3.G.bucket.zero_()

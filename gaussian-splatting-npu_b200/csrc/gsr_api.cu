@@ -357,10 +357,22 @@ static int batch_shared_check(int n, int P0, int D0, int M0, const float* m0, co
     return GSR_OK;
 }
 
+// Per-(thread, device) events of the batch entry points: [0] = the batched kernel has run on the caller's stream,
+// [1 + v] = view v's work on its own stream (counts copied / chain finished).
+static cudaEvent_t* batch_events(int dev_id) {
+    static thread_local cudaEvent_t ev[64][1 + GSR_MAX_VIEWS] = {};
+    if (!ev[dev_id][0])
+        for (int k = 0; k < 1 + GSR_MAX_VIEWS; k++)
+            if (cudaEventCreateWithFlags(&ev[dev_id][k], cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    return ev[dev_id];
+}
+
 extern "C" int gsr_forward_batch(int n_views, const gsr_forward_args* views, gsr_alloc_fn geom_alloc, void* const* geom_users,
                                  gsr_alloc_fn binning_alloc, void* const* binning_users, gsr_alloc_fn image_alloc,
-                                 void* const* image_users, void* stream_, int* num_rendered) {
+                                 void* const* image_users, void* stream_, void* const* view_streams, int* num_rendered) {
     cudaStream_t stream = (cudaStream_t)stream_;
+    // the per-view chains run on view_streams[v] when given (they are independent of each other), else on `stream`
+    auto vstream = [&](int v) { return (view_streams && view_streams[v]) ? (cudaStream_t)view_streams[v] : stream; };
     if (!views || !num_rendered || !geom_alloc || !binning_alloc || !image_alloc || !geom_users || !binning_users || !image_users)
         return fail(GSR_ERR_INVALID, "null argument");
     if (n_views < 1 || n_views > GSR_MAX_VIEWS) return fail(GSR_ERR_INVALID, "batch: n_views = %d outside 1..%d", n_views, GSR_MAX_VIEWS);
@@ -408,29 +420,29 @@ extern "C" int gsr_forward_batch(int n_views, const gsr_forward_args* views, gsr
     launch_preprocess_fwd_batch(bp, stream);
     STAGE_CHECK(a0.debug, stream, "preprocess (batch)");
 
-    // per view: scan + counts on their way to the host; then all depth sorts run while the host waits for the counts
+    // per view: scan + counts on their way to the host, then the depth sort, which runs while the host waits for the counts
     static thread_local uint32_t* pinned = nullptr;
-    static thread_local cudaEvent_t counts_ready_dev[64] = {};
     int dev_id = 0;
     CUDA_TRY(cudaGetDevice(&dev_id));
     if (dev_id < 0 || dev_id >= 64) return fail(GSR_ERR_INVALID, "device ordinal %d out of range", dev_id);
     if (!pinned) CUDA_TRY(cudaHostAlloc((void**)&pinned, 4 * 4 * GSR_MAX_VIEWS, cudaHostAllocPortable));
-    if (!counts_ready_dev[dev_id]) CUDA_TRY(cudaEventCreateWithFlags(&counts_ready_dev[dev_id], cudaEventDisableTiming));
+    cudaEvent_t* ev = batch_events(dev_id);
+    if (!ev) return fail(GSR_ERR_CUDA, "batch: cannot create events");
+    CUDA_TRY(cudaEventRecord(ev[0], stream));
     const int gsort_bits = 32, gsort_passes = (gsort_bits + 7) / 8;
     const int g0 = (gsort_passes & 1) ? 1 : 0;
     for (int v = 0; v < n_views; v++) {
-        launch_scan_compact(P, g[v], g[v].gsort_keys[g0], g[v].gsort_vals[g0], stream);
-        CUDA_TRY(cudaMemcpyAsync(pinned + 4 * v, g[v].scan_state + 1, 12, cudaMemcpyDeviceToHost, stream));
-    }
-    CUDA_TRY(cudaEventRecord(counts_ready_dev[dev_id], stream));
-    STAGE_CHECK(a0.debug, stream, "scan (batch)");
-    for (int v = 0; v < n_views; v++) {
+        cudaStream_t sv = vstream(v);
+        if (sv != stream) CUDA_TRY(cudaStreamWaitEvent(sv, ev[0], 0));
+        launch_scan_compact(P, g[v], g[v].gsort_keys[g0], g[v].gsort_vals[g0], sv);
+        CUDA_TRY(cudaMemcpyAsync(pinned + 4 * v, g[v].scan_state + 1, 12, cudaMemcpyDeviceToHost, sv));
+        CUDA_TRY(cudaEventRecord(ev[1 + v], sv));
         int in_b = 0;
         launch_sort_pairs32_pingpong(g[v].gsort_keys[g0], g[v].gsort_vals[g0], g[v].gsort_keys[1 - g0], g[v].gsort_vals[1 - g0],
-                                     (size_t)P, g[v].scan_state + 3, gsort_bits, g[v].gsort_temp, stream, &in_b);
+                                     (size_t)P, g[v].scan_state + 3, gsort_bits, g[v].gsort_temp, sv, &in_b);
     }
-    STAGE_CHECK(a0.debug, stream, "depth sort (batch)");
-    CUDA_TRY(cudaEventSynchronize(counts_ready_dev[dev_id]));
+    STAGE_CHECK(a0.debug, stream, "scan + depth sort (batch)");
+    for (int v = 0; v < n_views; v++) CUDA_TRY(cudaEventSynchronize(ev[1 + v]));
     for (int v = 0; v < n_views; v++) {
         if (pinned[4 * v]) return fail(GSR_ERR_PREFILTERED, "Point is filtered although prefiltered is set. This shouldn't happen!");
         if (pinned[4 * v + 1] >= (1u << 30)) return fail(GSR_ERR_INVALID, "num_rendered=%u exceeds the supported 2^30", pinned[4 * v + 1]);
@@ -438,6 +450,7 @@ extern "C" int gsr_forward_batch(int n_views, const gsr_forward_args* views, gsr
     }
     for (int v = 0; v < n_views; v++) {
         const gsr_forward_args& a = views[v];
+        cudaStream_t sv = vstream(v);
         const size_t N = (size_t)num_rendered[v];
         const int W = a.width, H = a.height, gx = bp.view[v].gx, gy = bp.view[v].gy;
         char* bin_raw = binning_alloc(gsr_binning_bytes(N, W, H), binning_users[v]);
@@ -450,21 +463,32 @@ extern "C" int gsr_forward_batch(int n_views, const gsr_forward_args* views, gsr
         uint32_t* k_other = (passes & 1) ? b.tile_keys : b.tile_keys_alt;
         uint32_t* v_other = (passes & 1) ? b.point_list : b.point_list_alt;
         if (N > 0) {
-            launch_sorted_scan(P, g[v], g[v].depth_order, g[v].sorted_offsets, stream);
-            launch_emit_tiles(P, gx, gy, g[v], g[v].depth_order, g[v].sorted_offsets, a.radii, k_start, v_start, stream);
+            launch_sorted_scan(P, g[v], g[v].depth_order, g[v].sorted_offsets, sv);
+            launch_emit_tiles(P, gx, gy, g[v], g[v].depth_order, g[v].sorted_offsets, a.radii, k_start, v_start, sv);
             int in_b = 0;
-            launch_sort_pairs32_pingpong(k_start, v_start, k_other, v_other, N, nullptr, end_bit, b.sort_temp, stream, &in_b);
+            launch_sort_pairs32_pingpong(k_start, v_start, k_other, v_other, N, nullptr, end_bit, b.sort_temp, sv, &in_b);
         }
-        launch_tile_ranges(N, b.tile_keys, im[v].ranges, gx * gy, stream);
+        launch_tile_ranges(N, b.tile_keys, im[v].ranges, gx * gy, sv);
         launch_render_fwd(W, H, gx, gy, im[v].ranges, b.point_list, b.block_masks, g[v].records, a.background, im[v].final_T,
-                          im[v].n_contrib, a.out_color, a.out_invdepth, stream);
-        STAGE_CHECK(a.debug, stream, "render (batch)");
+                          im[v].n_contrib, a.out_color, a.out_invdepth, sv);
+        STAGE_CHECK(a.debug, sv, "render (batch)");
+        if (sv != stream) {             // the caller's stream continues after every view's chain
+            CUDA_TRY(cudaEventRecord(ev[1 + v], sv));
+            CUDA_TRY(cudaStreamWaitEvent(stream, ev[1 + v], 0));
+        }
     }
     return GSR_OK;
 }
 
-extern "C" int gsr_backward_batch(int n_views, const gsr_backward_args* views, void* stream_) {
+extern "C" int gsr_backward_batch(int n_views, const gsr_backward_args* views, void* stream_, void* const* view_streams) {
     cudaStream_t stream = (cudaStream_t)stream_;
+    auto vstream = [&](int v) { return (view_streams && view_streams[v]) ? (cudaStream_t)view_streams[v] : stream; };
+    int dev_id = 0;
+    CUDA_TRY(cudaGetDevice(&dev_id));
+    if (dev_id < 0 || dev_id >= 64) return fail(GSR_ERR_INVALID, "device ordinal %d out of range", dev_id);
+    cudaEvent_t* ev = batch_events(dev_id);
+    if (!ev) return fail(GSR_ERR_CUDA, "batch: cannot create events");
+    CUDA_TRY(cudaEventRecord(ev[0], stream));
     if (!views) return fail(GSR_ERR_INVALID, "null argument");
     if (n_views < 1 || n_views > GSR_MAX_VIEWS) return fail(GSR_ERR_INVALID, "batch: n_views = %d outside 1..%d", n_views, GSR_MAX_VIEWS);
     const gsr_backward_args& a0 = views[0];
@@ -505,14 +529,20 @@ extern "C" int gsr_backward_batch(int n_views, const gsr_backward_args* views, v
         p.dL_dmean2D = a.dL_dmean2D; p.dL_dconic = a.dL_dconic; p.dL_dcolor = a.dL_dcolor;
         p.dL_dinvdepth = a.dL_dinvdepth_pix ? a.dL_dinvdepth : nullptr;
         const size_t sp = (size_t)P;
-        CUDA_TRY(cudaMemsetAsync(a.dL_dmean2D, 0, sp * 3 * 4, stream));
-        CUDA_TRY(cudaMemsetAsync(a.dL_dconic, 0, sp * 4 * 4, stream));
-        CUDA_TRY(cudaMemsetAsync(p.dop_view, 0, sp * 4, stream));
-        CUDA_TRY(cudaMemsetAsync(a.dL_dcolor, 0, sp * 3 * 4, stream));
-        if (p.dL_dinvdepth) CUDA_TRY(cudaMemsetAsync(p.dL_dinvdepth, 0, sp * 4, stream));
+        cudaStream_t sv = vstream(v);
+        if (sv != stream) CUDA_TRY(cudaStreamWaitEvent(sv, ev[0], 0));
+        CUDA_TRY(cudaMemsetAsync(a.dL_dmean2D, 0, sp * 3 * 4, sv));
+        CUDA_TRY(cudaMemsetAsync(a.dL_dconic, 0, sp * 4 * 4, sv));
+        CUDA_TRY(cudaMemsetAsync(p.dop_view, 0, sp * 4, sv));
+        CUDA_TRY(cudaMemsetAsync(a.dL_dcolor, 0, sp * 3 * 4, sv));
+        if (p.dL_dinvdepth) CUDA_TRY(cudaMemsetAsync(p.dL_dinvdepth, 0, sp * 4, sv));
         if (a.R > 0) {
-            launch_render_bwd(p, im.ranges, b.point_list, b.block_masks, g.records, im.final_T, im.n_contrib, stream);
-            STAGE_CHECK(a.debug, stream, "render backward (batch)");
+            launch_render_bwd(p, im.ranges, b.point_list, b.block_masks, g.records, im.final_T, im.n_contrib, sv);
+            STAGE_CHECK(a.debug, sv, "render backward (batch)");
+        }
+        if (sv != stream) {             // the one per-Gaussian launch below needs every view's blend gradients
+            CUDA_TRY(cudaEventRecord(ev[1 + v], sv));
+            CUDA_TRY(cudaStreamWaitEvent(stream, ev[1 + v], 0));
         }
         BwdBatchView& w = bp.view[v];
         w.viewmatrix = a.viewmatrix; w.projmatrix = a.projmatrix; w.cam_pos = a.cam_pos;

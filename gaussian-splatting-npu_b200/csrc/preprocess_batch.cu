@@ -156,23 +156,41 @@ preprocess_bwd_batch_kernel(const BwdBatchParams p) {
     cp_async_wait_all();
     __syncwarp();
     const StageRow E = { reinterpret_cast<const float*>(st + lane * 12), (lane >> 1) & 3 };
+    // The per-view inputs of the NEXT camera that sees this Gaussian are requested before the current one is processed:
+    // with the loads inside a plain loop every camera cost its own dependent trip to HBM.
+    struct ViewIn { float4 dcon; float dop, g2x, g2y, dinv, dr, dg, db; unsigned clamp; };
+    auto load_view = [&](int v) {
+        const BwdBatchView& w = p.view[v];
+        ViewIn in_;
+        in_.dcon = reinterpret_cast<const float4*>(w.dL_dconic)[i];
+        in_.dop = w.dop_view[i];
+        in_.g2x = w.dL_dmean2D[3 * (size_t)i]; in_.g2y = w.dL_dmean2D[3 * (size_t)i + 1];
+        in_.dinv = w.dL_dinvdepth ? w.dL_dinvdepth[i] : 0.0f;
+        in_.dr = w.dL_dcolor[3 * (size_t)i]; in_.dg = w.dL_dcolor[3 * (size_t)i + 1]; in_.db = w.dL_dcolor[3 * (size_t)i + 2];
+        in_.clamp = w.clamped[i];
+        return in_;
+    };
+    unsigned todo = vbits;
+    ViewIn cur;
+    if (todo) cur = load_view(__ffs(todo) - 1);
 #pragma unroll 1
-    for (int v = 0; v < p.V; v++) {
-        if (!((vbits >> v) & 1u)) continue;
+    while (todo) {
+        const int v = __ffs(todo) - 1;
+        todo &= todo - 1;
+        ViewIn nxt = cur;
+        if (todo) nxt = load_view(__ffs(todo) - 1);
         const BwdBatchView& w = p.view[v];
         float dc[6] = { 0, 0, 0, 0, 0, 0 }, vx = 0, vy = 0, vz = 0, dop_out = 0;
         cov2d_proj_backward(cam[v], cam[v] + 16, w.tan_fovx, w.tan_fovy, w.focal_x, w.focal_y, p.antialiasing != 0, mx, my, mz, c6,
-                            reinterpret_cast<const float4*>(w.dL_dconic)[i], w.dop_view[i], opacity_i, w.dL_dinvdepth != nullptr,
-                            w.dL_dinvdepth ? w.dL_dinvdepth[i] : 0.0f, w.dL_dmean2D[3 * (size_t)i], w.dL_dmean2D[3 * (size_t)i + 1],
-                            dc, vx, vy, vz, dop_out);
+                            cur.dcon, cur.dop, opacity_i, w.dL_dinvdepth != nullptr, cur.dinv, cur.g2x, cur.g2y, dc, vx, vy, vz, dop_out);
         float wk[16], d[3];
-        sh_backward(p.D, E, mx - cam[v][32], my - cam[v][33], mz - cam[v][34], w.clamped[i], w.dL_dcolor[3 * (size_t)i],
-                    w.dL_dcolor[3 * (size_t)i + 1], w.dL_dcolor[3 * (size_t)i + 2], wk, d, vx, vy, vz);
+        sh_backward(p.D, E, mx - cam[v][32], my - cam[v][33], mz - cam[v][34], cur.clamp, cur.dr, cur.dg, cur.db, wk, d, vx, vy, vz);
         dmx += vx; dmy += vy; dmz += vz; dop_sum += dop_out;
 #pragma unroll
         for (int k = 0; k < 6; k++) dcov[k] += dc[k];
 #pragma unroll
         for (int k = 0; k < 16; k++) { acc[3 * k] += wk[k] * d[0]; acc[3 * k + 1] += wk[k] * d[1]; acc[3 * k + 2] += wk[k] * d[2]; }
+        cur = nxt;
     }
 
     // ---- the SH gradient rows leave through the stage (coalesced 16-byte stores / REDs) --------------

@@ -119,9 +119,9 @@ def lib():
         L.gsr_materialize_keys.argtypes = [c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]
         L.gsr_forward_batch.restype = c_int
         L.gsr_forward_batch.argtypes = [c_int, POINTER(ForwardArgs), ALLOC_FN, POINTER(c_void_p), ALLOC_FN, POINTER(c_void_p), ALLOC_FN,
-                                        POINTER(c_void_p), c_void_p, POINTER(c_int)]
+                                        POINTER(c_void_p), c_void_p, POINTER(c_void_p), POINTER(c_int)]
         L.gsr_backward_batch.restype = c_int
-        L.gsr_backward_batch.argtypes = [c_int, POINTER(BackwardArgs), c_void_p]
+        L.gsr_backward_batch.argtypes = [c_int, POINTER(BackwardArgs), c_void_p, POINTER(c_void_p)]
         L.gsr_set_profiling.argtypes = [c_int]
         L.gsr_last_stage_ms.restype = c_float
         L.gsr_last_stage_ms.argtypes = [c_int]
@@ -287,11 +287,20 @@ def backward(state, *, dL_dcolor, dL_dinvdepth=None, means3D, opacities, viewmat
 _CAMERA_KEYS = ("viewmatrix", "projmatrix", "cam_pos", "tan_fovx", "tan_fovy")
 
 
+def _view_streams(streams, V):
+    if not streams:
+        return None
+    return (c_void_p * V)(*[c_void_p(streams[v % len(streams)].cuda_stream) for v in range(V)])
+
+
 def forward_batch(cameras, *, means3D, opacities, background, width, height, shs, scales, rotations, sh_degree=3,
-                  scale_modifier=1.0, prefiltered=False, antialiasing=False, debug=False, want_invdepth=True, workspaces=None):
+                  scale_modifier=1.0, prefiltered=False, antialiasing=False, debug=False, want_invdepth=True, workspaces=None,
+                  streams=None):
     """gsr_forward_batch: the views of a step in one call -- the per-Gaussian stage runs once for all cameras (parameters
     and SH rows read once), the rest per view.  `cameras`: list of dicts(viewmatrix, projmatrix, cam_pos, tan_fovx,
-    tan_fovy[, width, height]).  Returns one state per view, identical to forward()'s."""
+    tan_fovy[, width, height]).  `streams`: optional torch.cuda.Stream list; view v's chain (scan, sorts, emission, blend)
+    runs on streams[v % len(streams)], the one-launch stage on the current stream, which continues after all of them.
+    Returns one state per view, identical to forward()'s."""
     L = lib()
     dev = means3D.device
     P, M, V = means3D.shape[0], shs.shape[1], len(cameras)
@@ -314,13 +323,14 @@ def forward_batch(cameras, *, means3D, opacities, background, width, height, shs
     users = (c_void_p * V)(*[c_void_p(v + 1) for v in range(V)])
     n = (c_int * V)()
     with torch.cuda.device(dev):
-        _check(L.gsr_forward_batch(V, arr, cbs[0], users, cbs[1], users, cbs[2], users, _stream(), n))
+        _check(L.gsr_forward_batch(V, arr, cbs[0], users, cbs[1], users, cbs[2], users, _stream(), _view_streams(streams, V), n))
     return [dict(num_rendered=n[v], out_color=outs[v][0], out_invdepth=outs[v][1], radii=outs[v][2], geom=bufs[v][0].t,
                  binning=bufs[v][1].t, img=bufs[v][2].t, P=P, W=outs[v][3], H=outs[v][4], M=M) for v in range(V)]
 
 
 def backward_batch(states, cameras, *, dL_dcolor, dL_dinvdepth=None, means3D, opacities, background, shs, scales, rotations,
-                   sh_degree=3, scale_modifier=1.0, antialiasing=False, debug=False, out=None, accumulate=False, scratch=None):
+                   sh_degree=3, scale_modifier=1.0, antialiasing=False, debug=False, out=None, accumulate=False, scratch=None,
+                   streams=None):
     """gsr_backward_batch: per view the backward blend, then ONE per-Gaussian launch that sums the views' gradients in
     registers and writes (or, with `accumulate`, adds) the five parameter gradients once.  dL_dcolor / dL_dinvdepth: one
     tensor per view (or one shared by all).  `out`: the five parameter-gradient tensors (e.g. views of the exchange
@@ -361,7 +371,7 @@ def backward_batch(states, cameras, *, dL_dcolor, dL_dinvdepth=None, means3D, op
                               int(antialiasing), int(debug), int(accumulate))
         per_view.append(pv)
     with torch.cuda.device(dev):
-        _check(L.gsr_backward_batch(V, arr, _stream()))
+        _check(L.gsr_backward_batch(V, arr, _stream(), _view_streams(streams, V)))
     return g, per_view
 
 

@@ -150,14 +150,17 @@ int gsr_backward(const gsr_backward_args* args, void* stream);
  * gsr_backward_batch writes (accumulate = 0) or adds (accumulate = 1, taken from views[0]) the SUM over the views into the
  * parameter-gradient outputs of views[0] (dL_dmean3D, dL_dsh, dL_dopacity, dL_dscale, dL_drot); the per-view outputs
  * dL_dmean2D, dL_dconic, dL_dcolor, dL_dinvdepth are those of each view; dL_dcov3D is not produced (it only exists per view).
+ * view_streams (optional): the per-view chains are independent of each other, so view v's may run on view_streams[v]
+ * (several views may share a stream); the one-launch stages run on `stream`, which is ordered before the chains and
+ * continues after all of them.  NULL (or a NULL entry): everything on `stream`.
  */
 #define GSR_MAX_BATCH_VIEWS 8
 int gsr_forward_batch(int n_views, const gsr_forward_args* views,
                       gsr_alloc_fn geom_alloc, void* const* geom_users,
                       gsr_alloc_fn binning_alloc, void* const* binning_users,
                       gsr_alloc_fn image_alloc, void* const* image_users,
-                      void* stream, int* num_rendered /* [n_views] */);
-int gsr_backward_batch(int n_views, const gsr_backward_args* views, void* stream);
+                      void* stream, void* const* view_streams /* [n_views] or NULL */, int* num_rendered /* [n_views] */);
+int gsr_backward_batch(int n_views, const gsr_backward_args* views, void* stream, void* const* view_streams /* or NULL */);
 
 /* Rasterizer::markVisible (rasterizer.h:28-33, rasterizer_impl.cu:141-153). present is bool[P] (1 byte each). */
 int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,

@@ -48,6 +48,14 @@ def test_forward_batch_is_bitwise_the_single_view_forward(cuda, aa, degree):
         # compiler may contract it differently in the two kernels
         assert (ia["rgb"][vis] - ib["rgb"][vis]).abs().max().item() <= 2e-6
         assert (a["out_color"] - b["out_color"]).abs().max().item() <= 2e-6
+    # the views' chains on their own streams: same results
+    side = [torch.cuda.Stream(), torch.cuda.Stream()]
+    fanned = capi.forward_batch(cam_kw, width=W, height=H, streams=[torch.cuda.current_stream()] + side, **shared)
+    torch.cuda.synchronize()
+    for b, c in zip(batch, fanned):
+        assert b["num_rendered"] == c["num_rendered"]
+        assert torch.equal(b["out_color"], c["out_color"]) and torch.equal(b["radii"], c["radii"])
+        assert torch.equal(capi.introspect(b)["n_contrib"], capi.introspect(c)["n_contrib"])
     # and one view against the oracle (radii, image)
     ref = cases.run_oracle(scene, cams[2], opts)
     assert np.array_equal(batch[2]["radii"].cpu().numpy(), ref["radii"])
@@ -71,7 +79,8 @@ def test_backward_batch_sums_the_single_view_backwards(cuda, aa):
         for k in keys:
             want[k] = want[k] + g[k].double()
         per_view_want.append({k: g[k].clone() for k in ("dL_dmeans2D", "dL_dconic", "dL_dcolors", "dL_dinvdepths")})
-    got, per_view = capi.backward_batch(states, cam_kw, dL_dcolor=dcol, dL_dinvdepth=ddep, **shared)
+    got, per_view = capi.backward_batch(states, cam_kw, dL_dcolor=dcol, dL_dinvdepth=ddep,
+                                        streams=[torch.cuda.current_stream(), torch.cuda.Stream()] if aa else None, **shared)
     tol = dict(dL_dscales=1e-3, dL_drotations=1e-3)        # the two cancellation-heavy tensors
     for k in keys:
         w = want[k].cpu().numpy()
