@@ -17,9 +17,15 @@
 
 #define PBT_THREADS 128
 #define PBT_WARPS (PBT_THREADS / 32)
+#ifndef PBT_BWD_MIN
+#define PBT_BWD_MIN 4
+#endif
+#ifndef PBT_FWD_MIN
+#define PBT_FWD_MIN 1
+#endif
 
 // ------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(PBT_THREADS)
+__global__ void __launch_bounds__(PBT_THREADS, PBT_FWD_MIN)
 preprocess_fwd_batch_kernel(const FwdBatchParams p) {
     __shared__ float cam[GSR_MAX_VIEWS][36];          // V[16], PM[16], campos[3]
     __shared__ float4 stage[PBT_WARPS * 384];          // 32 rows x 12 float4 per warp, swizzled
@@ -103,7 +109,7 @@ void launch_preprocess_fwd_batch(const FwdBatchParams& p, cudaStream_t s) {
 
 // ------------------------------------------------------------------------------------------------------------------
 template <bool ACC>
-__global__ void __launch_bounds__(PBT_THREADS, 4)
+__global__ void __launch_bounds__(PBT_THREADS, PBT_BWD_MIN)
 preprocess_bwd_batch_kernel(const BwdBatchParams p) {
     __shared__ float cam[GSR_MAX_VIEWS][36];
     __shared__ float4 stage[PBT_WARPS * 384];
