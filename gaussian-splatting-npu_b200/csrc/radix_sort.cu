@@ -16,7 +16,12 @@
 
 #define SORT_THREADS 256
 #define SORT_WARPS (SORT_THREADS / 32)
+#ifndef SORT_IPT
 #define SORT_IPT 16
+#endif
+#ifndef SORT_MIN_CTAS32
+#define SORT_MIN_CTAS32 4
+#endif
 #define SORT_TILE (SORT_THREADS * SORT_IPT)        // 4096 pairs per CTA
 #define RADIX_BITS 8
 #define RADIX 256
@@ -112,7 +117,7 @@ struct OnesweepSmem {
 };
 
 template <typename KeyT>
-__global__ void __launch_bounds__(SORT_THREADS, sizeof(KeyT) == 8 ? 3 : 4)
+__global__ void __launch_bounds__(SORT_THREADS, sizeof(KeyT) == 8 ? (SORT_IPT > 16 ? 2 : 3) : SORT_MIN_CTAS32)
 onesweep_kernel(const KeyT* __restrict__ kin, const uint32_t* __restrict__ vin, KeyT* __restrict__ kout,
                 uint32_t* __restrict__ vout, size_t n_host, const uint32_t* __restrict__ n_dev, int shift, uint32_t mask,
                 const uint32_t* __restrict__ ghist, uint32_t* counter, uint32_t* status) {
