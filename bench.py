@@ -610,6 +610,17 @@ def time_steps(torch, dist, dev, world, step_fn, steps, warmup, min_warm_s=1.5):
     return ms, per, n_warm
 
 
+def optional_leg(name, fn):
+    """Runs one of the bench's extra legs; a failure there is reported under the leg's key instead of costing the whole
+    line (`value`, `e2e` and the roofline are computed outside these)."""
+    try:
+        return fn()
+    except Exception as exc:      # noqa: BLE001 -- reported, not swallowed
+        import traceback
+        sys.stderr.write("bench: leg '%s' failed\n%s\n" % (name, traceback.format_exc()))
+        return {"error": "%s: %s" % (type(exc).__name__, str(exc)[:300])}
+
+
 def newest_traffic(workload):
     """DRAM bytes per launch from the newest committed `ncu --set full` capture of this workload: the highest round in
     the file name (profiles/rNN_*traffic*.json), ties by modification time."""
@@ -719,37 +730,44 @@ def main():
         exchange_ms["bytes"] = int(G.bucket.numel() * 4)
 
     # ---------------- the same views overlapped on S streams (own key; not `value`) ----------------
-    ov_ms, ov_steps, _ = time_steps(torch, dist, dev, world, lambda: job.step_render(S), args.steps, warm, min_warm_s=0.3)
-    overlapped = {"streams": S, "value": world * V * args.steps / (ov_ms / 1000.0), "unit": "renders/s",
-                  "ms_per_step": ov_ms / args.steps, "ms_per_view": ov_ms / args.steps / V,
-                  "what": "the same step with view v on CUDA stream v %% %d (gsr_b200.dist.ViewStreams): the latency-bound "
-                          "stages of one view run under the blend kernels of its neighbours" % S}
+    def leg_overlapped():
+        ov_ms, _, _ = time_steps(torch, dist, dev, world, lambda: job.step_render(S), args.steps, warm, min_warm_s=0.3)
+        return {"streams": S, "value": world * V * args.steps / (ov_ms / 1000.0), "unit": "renders/s",
+                "ms_per_step": ov_ms / args.steps, "ms_per_view": ov_ms / args.steps / V,
+                "what": "the same step with view v on CUDA stream v %% %d (gsr_b200.dist.ViewStreams): the latency-bound "
+                        "stages of one view run under the blend kernels of its neighbours" % S}
+    overlapped = optional_leg("overlapped_step", leg_overlapped)
 
     # ---------------- the same views through the batched entry points (own key; not `value`) ----------------
-    bt_ms, _, _ = time_steps(torch, dist, dev, world, lambda: job.step_batched(S), args.steps, warm, min_warm_s=0.3)
-    b1_ms, _, _ = time_steps(torch, dist, dev, world, lambda: job.step_batched(1), args.steps, warm, min_warm_s=0.3)
-    batched = {"value": world * V * args.steps / (bt_ms / 1000.0), "unit": "renders/s", "ms_per_step": bt_ms / args.steps,
-               "ms_per_view": bt_ms / args.steps / V, "streams": S,
-               "one_stream": {"value": world * V * args.steps / (b1_ms / 1000.0), "ms_per_step": b1_ms / args.steps},
-               "what": "the same %d views through gsr_forward_batch / gsr_backward_batch: ONE per-Gaussian launch each way for all cameras "
-                       "(parameters and SH rows read once, the 59 gradient floats written once), scan / sorts / emission / blend per "
-                       "view, the views' chains on %d streams (`one_stream`: everything on one)" % (V, S)}
+    def leg_batched():
+        bt_ms, _, _ = time_steps(torch, dist, dev, world, lambda: job.step_batched(S), args.steps, warm, min_warm_s=0.3)
+        b1_ms, _, _ = time_steps(torch, dist, dev, world, lambda: job.step_batched(1), args.steps, warm, min_warm_s=0.3)
+        return {"value": world * V * args.steps / (bt_ms / 1000.0), "unit": "renders/s", "ms_per_step": bt_ms / args.steps,
+                "ms_per_view": bt_ms / args.steps / V, "streams": S,
+                "one_stream": {"value": world * V * args.steps / (b1_ms / 1000.0), "ms_per_step": b1_ms / args.steps},
+                "what": "the same %d views through gsr_forward_batch / gsr_backward_batch: ONE per-Gaussian launch each way for all cameras "
+                        "(parameters and SH rows read once, the 59 gradient floats written once), scan / sorts / emission / blend per "
+                        "view, the views' chains on %d streams (`one_stream`: everything on one)" % (V, S)}
+    batched = optional_leg("batched_step", leg_batched)
     if hasattr(job, "batch_ws"):
         del job.batch_ws, job.batch_scratch
         torch.cuda.empty_cache()
 
     # ---------------- with the optimizer: render + densification statistics + Adam (+ exchange) ----------------
-    saved = job.save_params()
-    op_ms, _, _ = time_steps(torch, dist, dev, world, lambda: job.step_train(1), args.steps, warm, min_warm_s=0.3)
-    job.restore_params(saved)
-    del saved
-    with_optimizer = {"value": world * V * args.steps / (op_ms / 1000.0), "unit": "renders/s", "ms_per_step": op_ms / args.steps,
-                      "what": ("views as in `value`, each followed by the fused densification-statistics update; then ONE fused exchange kernel per rank: "
-                               "reduce-scatter of the bucket -> Adam on the rank's 1/%d shard -> all-gather of the parameters, + SUM/MAX of the statistics" % world)
-                      if job.fused is not None else
-                      "views as in `value`, each followed by the fused densification-statistics update; then %sgsr_adam_step over all rows" % (
-                          "ncclAllReduce of the bucket + 3 statistic all-reduces + " if world > 1 else ""),
-                      "learning_rates": "the reference's x 1e-6 (same arithmetic and traffic; keeps the timed steps on the same scene)"}
+    def leg_optimizer():
+        saved = job.save_params()
+        try:
+            op_ms, _, _ = time_steps(torch, dist, dev, world, lambda: job.step_train(1), args.steps, warm, min_warm_s=0.3)
+        finally:
+            job.restore_params(saved)
+        return {"value": world * V * args.steps / (op_ms / 1000.0), "unit": "renders/s", "ms_per_step": op_ms / args.steps,
+                "what": ("views as in `value`, each followed by the fused densification-statistics update; then ONE fused exchange kernel per rank: "
+                         "reduce-scatter of the bucket -> Adam on the rank's 1/%d shard -> all-gather of the parameters, + SUM/MAX of the statistics" % world)
+                if job.fused is not None else
+                "views as in `value`, each followed by the fused densification-statistics update; then %sgsr_adam_step over all rows" % (
+                    "ncclAllReduce of the bucket + 3 statistic all-reduces + " if world > 1 else ""),
+                "learning_rates": "the reference's x 1e-6 (same arithmetic and traffic; keeps the timed steps on the same scene)"}
+    with_optimizer = optional_leg("with_optimizer", leg_optimizer)
 
     # ---------------- single view, isolated: synchronise before and after every view (latency) ----------------
     sv_ms = []
@@ -883,16 +901,19 @@ def main():
 
     e2e_ms, step_loss = time_api(True)
     bucket_checksum = float(G.bucket.double().abs().sum().item())
-    stock_ms, stock_loss = time_api(False)
+    def leg_stock():
+        stock_ms, stock_loss = time_api(False)
+        return {"value": world * V * args.steps / (stock_ms / 1000.0), "unit": "renders/s", "ms_per_step": stock_ms / args.steps,
+                "step_loss": stock_loss,
+                "what": "the same without grad_sink: the unchanged reference API, gradients returned to autograd and summed into .grad by AccumulateGrad (what the reference's train.py does), .grad dropped per step"}
+    stock = optional_leg("e2e.stock_autograd", leg_stock)
     e2e_val = world * V * args.steps / (e2e_ms / 1000.0)
-    stock_val = world * V * args.steps / (stock_ms / 1000.0)
     h2d = V * (target_host[0].numel() * 4 + cam_host[0].numel() * 4)
     d2h = 4 + 12 * V    # the step's loss + the 12-byte instance/visible counts of every forward
     del params, target_dev
 
     # ---------------- BASELINE configs[2] as written: C3, 8 views per step in total, split over the ranks ----------------
-    c3 = None
-    if not args.no_c3 and args.workload == "c2" and 8 % world == 0:
+    def leg_c3():
         torch.cuda.empty_cache()
         j3 = Job("c3", 8 // world, 8, rank, world, dev, args.exchange, max_streams=S)
         if not args.no_balance:
@@ -903,18 +924,21 @@ def main():
         j3.restore_params(saved)
         o_ms, _, _ = time_steps(torch, dist, dev, world, lambda: j3.step_render(S), args.steps, warm, min_warm_s=0.3)
         b_ms, _, _ = time_steps(torch, dist, dev, world, lambda: j3.step_batched(S), args.steps, warm, min_warm_s=0.3)
-        c3 = {"workload": "c3: " + WORKLOADS["c3"]["desc"] + "; 8 views per step IN TOTAL, %d per rank, gradient exchange every step" % (8 // world),
-              "scaling": "strong", "n_gpus": world, "views_per_step": 8, "exchange": args.exchange if world > 1 else None,
-              "value": 8 * args.steps / (r_ms / 1000.0), "unit": "views/s", "ms_per_step": r_ms / args.steps,
-              "with_optimizer": {"value": 8 * args.steps / (t_ms / 1000.0), "ms_per_step": t_ms / args.steps},
-              "overlapped_%d_streams" % S: {"value": 8 * args.steps / (o_ms / 1000.0), "ms_per_step": o_ms / args.steps},
-              "batched_%d_streams" % S: {"value": 8 * args.steps / (b_ms / 1000.0), "ms_per_step": b_ms / args.steps},
-              "bucket_bytes": int(j3.G.bucket.numel() * 4), "num_rendered_last_view": j3.last_state["num_rendered"]}
+        res = {"workload": "c3: " + WORKLOADS["c3"]["desc"] + "; 8 views per step IN TOTAL, %d per rank, gradient exchange every step" % (8 // world),
+               "scaling": "strong", "n_gpus": world, "views_per_step": 8, "exchange": args.exchange if world > 1 else None,
+               "value": 8 * args.steps / (r_ms / 1000.0), "unit": "views/s", "ms_per_step": r_ms / args.steps,
+               "with_optimizer": {"value": 8 * args.steps / (t_ms / 1000.0), "ms_per_step": t_ms / args.steps},
+               "overlapped_%d_streams" % S: {"value": 8 * args.steps / (o_ms / 1000.0), "ms_per_step": o_ms / args.steps},
+               "batched_%d_streams" % S: {"value": 8 * args.steps / (b_ms / 1000.0), "ms_per_step": b_ms / args.steps},
+               "bucket_bytes": int(j3.G.bucket.numel() * 4), "num_rendered_last_view": j3.last_state["num_rendered"]}
         if world > 1:
             j3.G.bucket.zero_()
             x_ms, _, _ = time_steps(torch, dist, dev, world, j3.exchange_gradients, 20, 3, min_warm_s=0.0)
-            c3["exchange_ms"] = x_ms / 20
-        del j3, saved
+            res["exchange_ms"] = x_ms / 20
+        return res
+    c3 = None
+    if not args.no_c3 and args.workload == "c2" and 8 % world == 0:
+        c3 = optional_leg("c3_strong", leg_c3)
         torch.cuda.empty_cache()
 
     out = None
@@ -1009,8 +1033,7 @@ def main():
             "e2e": {"value": e2e_val, "unit": "renders/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms / args.steps, "step_loss": step_loss, "bucket_checksum": bucket_checksum,
                     "what": "per view: camera + target image from pinned host memory (copy stream, double-buffered, overlapping the previous view's kernels), GaussianRasterizer autograd fwd+bwd + the fused training loss 0.8*L1 + 0.2*(1-SSIM) (fused_ssim.l1_ssim_loss), views one after another on one stream; per step: gradients of the rank's views summed in the bucket by the backward kernels (grad_sink), exchange when N>1, loss read back",
-                    "stock_autograd": {"value": stock_val, "unit": "renders/s", "ms_per_step": stock_ms / args.steps, "step_loss": stock_loss,
-                                       "what": "the same without grad_sink: the unchanged reference API, gradients returned to autograd and summed into .grad by AccumulateGrad (what the reference's train.py does), .grad dropped per step"}},
+                    "stock_autograd": stock},
             "gpu_launches": launches_per_step * args.steps,
             "single_view_isolated": {"fwd_bwd_ms": single_view_ms, "renders_per_s": 1000.0 / single_view_ms,
                                      "what": "one view, synchronised before and after (launch ramp included): latency, not throughput"},
