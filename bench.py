@@ -816,7 +816,7 @@ def main():
                                                  c.camera_center.ravel()]).astype(np.float32)).pin_memory() for c in cams]
     NB = 2                                                                   # one input buffer per view in flight
     target_dev = [torch.empty(3, H, W, device=dev) for _ in range(NB)]       # double-buffered: the copy of view v+1
-    cam_dev = [torch.empty(35, device=dev) for _ in range(NB)]              # runs under view v's kernels
+    cam_dev = [torch.empty(35, device=dev) for _ in range(V)]               # one per view: the deferred sink reads the cameras at the end of the step
     params = G.as_leaf_params()
     loss_host = torch.empty(1).pin_memory()
     loss_dev = torch.zeros(1, device=dev)
@@ -832,8 +832,9 @@ def main():
     def api_step(use_sink):
         """One step through the public API: for each of this rank's V views the camera and the target image come from
         pinned host memory (copy stream, double-buffered), GaussianRasterizer renders, the training loss
-        0.8 L1 + 0.2 D-SSIM (fused) is taken and backpropagated.  use_sink: parameter gradients of the V views add up in
-        the flat bucket inside the backward kernels (grad_sink extension).  Otherwise the STOCK autograd path: gradients
+        0.8 L1 + 0.2 D-SSIM (fused) is taken and backpropagated.  use_sink "defer": one grad_sink(defer=True) context around
+        the step (blend stage per backward, ONE batched per-Gaussian launch at the end writes the bucket); "per_view": a
+        grad_sink context per view (the kernels add into the bucket).  False: the STOCK autograd path: gradients
         are returned and summed into .grad by AccumulateGrad, exactly what the reference's unchanged train.py gets;
         with N > 1 they are then packed into the bucket, exchanged and unpacked.  The step's loss is read back."""
         main = torch.cuda.current_stream()
@@ -841,29 +842,32 @@ def main():
         def upload(v):
             copy_stream.wait_event(buf_free[v % NB])
             with torch.cuda.stream(copy_stream):
-                cam_dev[v % NB].copy_(cam_host[v], non_blocking=True)
+                cam_dev[v].copy_(cam_host[v], non_blocking=True)
                 target_dev[v % NB].copy_(target_host[v % len(target_host)], non_blocking=True)
                 uploaded[v % NB].record(copy_stream)
 
+        import contextlib
+        step_ctx = grad_sink(*sink, accumulate=False, defer=True) if use_sink == "defer" else contextlib.nullcontext()
         upload(0)
-        for v in range(V):
-            cd, td = cam_dev[v % NB], target_dev[v % NB]
-            main.wait_event(uploaded[v % NB])
-            if v + 1 < V:
-                upload(v + 1)
-            rs = GaussianRasterizationSettings(viewmatrix=cd[0:16].view(4, 4), projmatrix=cd[16:32].view(4, 4),
-                                               campos=cd[32:35], tanfovx=cams[v].tanfovx, tanfovy=cams[v].tanfovy, **rs_kw)
-            means2D = torch.zeros_like(params["xyz"], requires_grad=True)
-            color, radii, invd = GaussianRasterizer(rs)(means3D=params["xyz"], means2D=means2D, opacities=params["opacity"],
-                                                        shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
-            loss = l1_ssim_loss(color, td, 0.2)
-            if use_sink:
-                with grad_sink(*sink, accumulate=(v > 0)):
-                    loss.backward()
-            else:
-                loss.backward()
-            loss_slots[v].copy_(loss.detach().reshape(1))
-            buf_free[v % NB].record(main)
+        with step_ctx:
+          for v in range(V):
+              cd, td = cam_dev[v], target_dev[v % NB]
+              main.wait_event(uploaded[v % NB])
+              if v + 1 < V:
+                  upload(v + 1)
+              rs = GaussianRasterizationSettings(viewmatrix=cd[0:16].view(4, 4), projmatrix=cd[16:32].view(4, 4),
+                                                 campos=cd[32:35], tanfovx=cams[v].tanfovx, tanfovy=cams[v].tanfovy, **rs_kw)
+              means2D = torch.zeros_like(params["xyz"], requires_grad=True)
+              color, radii, invd = GaussianRasterizer(rs)(means3D=params["xyz"], means2D=means2D, opacities=params["opacity"],
+                                                          shs=params["shs"], scales=params["scales"], rotations=params["rotations"])
+              loss = l1_ssim_loss(color, td, 0.2)
+              if use_sink == "per_view":
+                  with grad_sink(*sink, accumulate=(v > 0)):
+                      loss.backward()
+              else:
+                  loss.backward()
+              loss_slots[v].copy_(loss.detach().reshape(1))
+              buf_free[v % NB].record(main)
         loss_dev.copy_(loss_slots.sum().reshape(1))
         if use_sink:
             job.exchange_gradients()
@@ -899,8 +903,15 @@ def main():
             ms_ = float(tms.item())
         return ms_, loss_
 
-    e2e_ms, step_loss = time_api(True)
+    e2e_ms, step_loss = time_api("defer")
     bucket_checksum = float(G.bucket.double().abs().sum().item())
+
+    def leg_per_view_sink():
+        pv_ms, pv_loss = time_api("per_view")
+        return {"value": world * V * args.steps / (pv_ms / 1000.0), "unit": "renders/s", "ms_per_step": pv_ms / args.steps, "step_loss": pv_loss,
+                "bucket_checksum": float(G.bucket.double().abs().sum().item()),
+                "what": "grad_sink per view (accumulate from the second view on): every backward runs its own per-Gaussian stage"}
+    per_view_sink = optional_leg("e2e.grad_sink_per_view", leg_per_view_sink)
     def leg_stock():
         stock_ms, stock_loss = time_api(False)
         return {"value": world * V * args.steps / (stock_ms / 1000.0), "unit": "renders/s", "ms_per_step": stock_ms / args.steps,
@@ -1032,8 +1043,8 @@ def main():
             "clocks": clocks,
             "e2e": {"value": e2e_val, "unit": "renders/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms / args.steps, "step_loss": step_loss, "bucket_checksum": bucket_checksum,
-                    "what": "per view: camera + target image from pinned host memory (copy stream, double-buffered, overlapping the previous view's kernels), GaussianRasterizer autograd fwd+bwd + the fused training loss 0.8*L1 + 0.2*(1-SSIM) (fused_ssim.l1_ssim_loss), views one after another on one stream; per step: gradients of the rank's views summed in the bucket by the backward kernels (grad_sink), exchange when N>1, loss read back",
-                    "stock_autograd": stock},
+                    "what": "per view: camera + target image from pinned host memory (copy stream, double-buffered, overlapping the previous view's kernels), GaussianRasterizer autograd fwd+bwd + the fused training loss 0.8*L1 + 0.2*(1-SSIM) (fused_ssim.l1_ssim_loss), views one after another on one stream; per step: ONE grad_sink(defer=True) context around the views -- every backward runs its blend stage at once, the per-Gaussian stage of all views is one batched launch when the context closes and writes the bucket once; exchange when N>1, loss read back",
+                    "grad_sink_per_view": per_view_sink, "stock_autograd": stock},
             "gpu_launches": launches_per_step * args.steps,
             "single_view_isolated": {"fwd_bwd_ms": single_view_ms, "renders_per_s": 1000.0 / single_view_ms,
                                      "what": "one view, synchronised before and after (launch ramp included): latency, not throughput"},

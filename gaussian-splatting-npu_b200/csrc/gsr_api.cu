@@ -480,7 +480,8 @@ extern "C" int gsr_forward_batch(int n_views, const gsr_forward_args* views, gsr
     return GSR_OK;
 }
 
-extern "C" int gsr_backward_batch(int n_views, const gsr_backward_args* views, void* stream_, void* const* view_streams) {
+// stages: 1 = backward blend of every view, 2 = the one per-Gaussian launch over all views, 3 = both
+static int backward_batch_impl(int n_views, const gsr_backward_args* views, void* stream_, void* const* view_streams, int stages) {
     cudaStream_t stream = (cudaStream_t)stream_;
     auto vstream = [&](int v) { return (view_streams && view_streams[v]) ? (cudaStream_t)view_streams[v] : stream; };
     int dev_id = 0;
@@ -495,7 +496,7 @@ extern "C" int gsr_backward_batch(int n_views, const gsr_backward_args* views, v
     const int P = a0.P;
     if (P < 0) return fail(GSR_ERR_INVALID, "bad sizes");
     if (P == 0) return GSR_OK;
-    if (!a0.dL_dmean3D || !a0.dL_dsh || !a0.dL_dopacity || !a0.dL_dscale || !a0.dL_drot)
+    if ((stages & 2) && (!a0.dL_dmean3D || !a0.dL_dsh || !a0.dL_dopacity || !a0.dL_dscale || !a0.dL_drot))
         return fail(GSR_ERR_INVALID, "batch: views[0] must carry the five parameter-gradient outputs");
     if (check_aligned16(a0.rotations, "rotations") || check_aligned16(a0.dL_drot, "dL_drot") || check_aligned16(a0.shs, "shs") ||
         check_aligned16(a0.dL_dsh, "dL_dsh")) return GSR_ERR_INVALID;
@@ -511,15 +512,13 @@ extern "C" int gsr_backward_batch(int n_views, const gsr_backward_args* views, v
         if (batch_shared_check(n_views, a0.P, a0.D, a0.M, a0.means3D, a0.shs, a0.opacities, a0.scales, a0.rotations, a0.scale_modifier,
                                a0.antialiasing, a.P, a.D, a.M, a.means3D, a.shs, a.opacities, a.scales, a.rotations, a.scale_modifier,
                                a.antialiasing, a.colors_precomp, a.cov3D_precomp)) return GSR_ERR_INVALID;
-        if (!a.geom_buffer || !a.binning_buffer || !a.image_buffer || !a.dL_dpix || !a.radii)
+        if (!a.geom_buffer || !a.radii || ((stages & 1) && (!a.binning_buffer || !a.image_buffer || !a.dL_dpix)))
             return fail(GSR_ERR_INVALID, "missing buffer");
         if (!a.dL_dmean2D || !a.dL_dconic || !a.dL_dcolor) return fail(GSR_ERR_INVALID, "missing per-view gradient output");
         if (a.dL_dinvdepth_pix && !a.dL_dinvdepth) return fail(GSR_ERR_INVALID, "dL_dinvdepth output required");
         if (check_aligned16(a.dL_dconic, "dL_dconic")) return GSR_ERR_INVALID;
         const int gx = (W + GSR_TILE - 1) / GSR_TILE, gy = (H + GSR_TILE - 1) / GSR_TILE;
         GeomView g = geom_view(a.geom_buffer, P);
-        ImageView im = image_view(a.image_buffer, W, H);
-        BinningView b = binning_view(a.binning_buffer, (size_t)a.R, W, H);
         BwdParams p;
         memset(&p, 0, sizeof(p));
         p.P = P; p.D = a.D; p.M = a.M; p.W = W; p.H = H; p.gx = gx; p.gy = gy;
@@ -527,9 +526,13 @@ extern "C" int gsr_backward_batch(int n_views, const gsr_backward_args* views, v
         p.dop_view = reinterpret_cast<float*>(g.gsort_keys[0]);
         p.dL_dpix = a.dL_dpix; p.dL_dinvdepth_pix = a.dL_dinvdepth_pix;
         p.dL_dmean2D = a.dL_dmean2D; p.dL_dconic = a.dL_dconic; p.dL_dcolor = a.dL_dcolor;
-        p.dL_dinvdepth = a.dL_dinvdepth_pix ? a.dL_dinvdepth : nullptr;
+        // stage 2 alone has no pixel gradients to look at: a non-null dL_dinvdepth output says the blend filled it
+        p.dL_dinvdepth = (a.dL_dinvdepth_pix || !(stages & 1)) ? a.dL_dinvdepth : nullptr;
         const size_t sp = (size_t)P;
         cudaStream_t sv = vstream(v);
+        if (stages & 1) {
+        ImageView im = image_view(a.image_buffer, W, H);
+        BinningView b = binning_view(a.binning_buffer, (size_t)a.R, W, H);
         if (sv != stream) CUDA_TRY(cudaStreamWaitEvent(sv, ev[0], 0));
         CUDA_TRY(cudaMemsetAsync(a.dL_dmean2D, 0, sp * 3 * 4, sv));
         CUDA_TRY(cudaMemsetAsync(a.dL_dconic, 0, sp * 4 * 4, sv));
@@ -544,6 +547,7 @@ extern "C" int gsr_backward_batch(int n_views, const gsr_backward_args* views, v
             CUDA_TRY(cudaEventRecord(ev[1 + v], sv));
             CUDA_TRY(cudaStreamWaitEvent(stream, ev[1 + v], 0));
         }
+        }
         BwdBatchView& w = bp.view[v];
         w.viewmatrix = a.viewmatrix; w.projmatrix = a.projmatrix; w.cam_pos = a.cam_pos;
         w.tan_fovx = a.tan_fovx; w.tan_fovy = a.tan_fovy;
@@ -552,9 +556,23 @@ extern "C" int gsr_backward_batch(int n_views, const gsr_backward_args* views, v
         w.dL_dconic = a.dL_dconic; w.dL_dmean2D = a.dL_dmean2D; w.dL_dcolor = a.dL_dcolor; w.dL_dinvdepth = p.dL_dinvdepth;
         w.dop_view = p.dop_view;
     }
-    launch_preprocess_bwd_batch(bp, stream);
-    STAGE_CHECK(a0.debug, stream, "preprocess backward (batch)");
+    if (stages & 2) {
+        launch_preprocess_bwd_batch(bp, stream);
+        STAGE_CHECK(a0.debug, stream, "preprocess backward (batch)");
+    }
     return GSR_OK;
+}
+
+extern "C" int gsr_backward_batch(int n_views, const gsr_backward_args* views, void* stream, void* const* view_streams) {
+    return backward_batch_impl(n_views, views, stream, view_streams, 3);
+}
+// The two halves of gsr_backward_batch for callers that learn about the views of a step one at a time (an autograd engine
+// calls one backward per view): the blend of a view now, the per-Gaussian launch over all of them once the last is in.
+extern "C" int gsr_backward_blend(const gsr_backward_args* view, void* stream) {
+    return backward_batch_impl(1, view, stream, nullptr, 1);
+}
+extern "C" int gsr_backward_params_batch(int n_views, const gsr_backward_args* views, void* stream) {
+    return backward_batch_impl(n_views, views, stream, nullptr, 2);
 }
 
 extern "C" int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,

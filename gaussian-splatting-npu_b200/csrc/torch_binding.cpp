@@ -13,6 +13,7 @@
 #include <torch/extension.h>
 #include <ATen/cuda/CUDAContext.h>
 #include <c10/cuda/CUDAGuard.h>
+#include <mutex>
 #include <stdexcept>
 #include <tuple>
 #include "gsr.h"
@@ -99,7 +100,37 @@ RasterizeGaussiansCUDA(const torch::Tensor& background, const torch::Tensor& mea
 // Optional gradient sink (extension over the reference API, see diff_gaussian_rasterization.grad_sink):
 // the five parameter gradients are written -- or, with accumulate, added -- straight into caller-owned
 // tensors (views of an all-reduce bucket) instead of fresh allocations.
-struct GradSink { torch::Tensor means3D, sh, opacity, scales, rotations; bool accumulate = false; bool active = false; };
+struct GradSink { torch::Tensor means3D, sh, opacity, scales, rotations; bool accumulate = false; bool active = false; bool defer = false; };
+
+// Deferred sink (grad_sink(..., defer=True)): autograd hands over the views of a step one backward at a time; each runs its
+// backward blend at once (gsr_backward_blend) and is parked here with the tensors the per-Gaussian stage still needs; ONE
+// gsr_backward_params_batch per (up to) GSR_MAX_BATCH_VIEWS views then sums their parameter gradients in registers and
+// writes the sink once (flush_grad_sink, called when the Python context closes).  Process-wide like the Python-side sink:
+// autograd runs backward nodes on its own threads.
+struct DeferredView {
+    gsr_backward_args a;                       // pointers into the tensors below
+    std::vector<torch::Tensor> keep;
+};
+struct DeferredState {
+    std::mutex mu;
+    std::vector<DeferredView> views;
+    bool accumulate = false;                   // of the next flush: the first one follows the sink's flag, later ones add
+    c10::Device device = c10::Device(c10::kCPU);
+};
+DeferredState& deferred() { static DeferredState d; return d; }
+
+void flush_locked(DeferredState& d) {
+    if (d.views.empty()) return;
+    const c10::cuda::CUDAGuard guard(d.device);
+    cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+    std::vector<gsr_backward_args> arr;
+    for (auto& v : d.views) arr.push_back(v.a);
+    arr[0].accumulate = d.accumulate ? 1 : 0;
+    const int st = gsr_backward_params_batch((int)arr.size(), arr.data(), stream);
+    d.views.clear();
+    d.accumulate = true;                       // whatever follows in the same context adds to what was just written
+    check(st);
+}
 
 typedef std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor> BwdTuple;
 
@@ -183,7 +214,30 @@ backward_impl(const GradSink& sink, const torch::Tensor& background, const torch
         a.dL_drot = has_scales ? dL_drotations.data_ptr<float>() : nullptr;
         a.antialiasing = antialiasing; a.debug = debug;
         a.accumulate = (sink.active && sink.accumulate) ? 1 : 0;            // the reference API always overwrites
-        check(gsr_backward(&a, stream));
+        const bool can_defer = sink.active && sink.defer && M == 16 && has_scales && colors.numel() == 0 && cov3D_precomp.numel() == 0;
+        if (can_defer) {
+            DeferredState& d = deferred();
+            std::lock_guard<std::mutex> lock(d.mu);
+            // a different set of Gaussians / sinks than the parked views' (or a full batch): write those out first
+            if (!d.views.empty()) {
+                const gsr_backward_args& f = d.views[0].a;
+                if (d.views.size() >= GSR_MAX_BATCH_VIEWS || f.P != a.P || f.means3D != a.means3D || f.shs != a.shs || f.dL_dsh != a.dL_dsh ||
+                    f.D != a.D || f.scale_modifier != a.scale_modifier || f.antialiasing != a.antialiasing) flush_locked(d);
+            } else {
+                d.accumulate = sink.accumulate;
+            }
+            check(gsr_backward_blend(&a, stream));
+            dL_dcov3D.zero_();                     // not produced on this path (it only exists per view); nobody reads it
+            d.device = means3D.device();
+            DeferredView dv;
+            dv.a = a;
+            dv.keep = keep;
+            for (const torch::Tensor& t : { radii_c, gb, dL_dmeans2D, dL_dconic, dL_dcolors, dL_dinvdepths, dL_dmeans3D, dL_dopacity,
+                                             dL_dsh, dL_dscales, dL_drotations }) dv.keep.push_back(t);
+            d.views.push_back(std::move(dv));
+        } else {
+            check(gsr_backward(&a, stream));
+        }
     }
     return std::make_tuple(dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations);
 }
@@ -213,13 +267,24 @@ RasterizeGaussiansBackwardInto(const torch::Tensor& background, const torch::Ten
                                const torch::Tensor& geomBuffer, const int R, const torch::Tensor& binningBuffer,
                                const torch::Tensor& imageBuffer, const bool antialiasing, const bool debug,
                                const torch::Tensor& sink_means3D, const torch::Tensor& sink_sh, const torch::Tensor& sink_opacity,
-                               const torch::Tensor& sink_scales, const torch::Tensor& sink_rotations, const bool accumulate) {
+                               const torch::Tensor& sink_scales, const torch::Tensor& sink_rotations, const bool accumulate,
+                               const bool defer) {
     GradSink sink;
     sink.means3D = sink_means3D; sink.sh = sink_sh; sink.opacity = sink_opacity; sink.scales = sink_scales;
-    sink.rotations = sink_rotations; sink.accumulate = accumulate; sink.active = true;
+    sink.rotations = sink_rotations; sink.accumulate = accumulate; sink.active = true; sink.defer = defer;
     return backward_impl(sink, background, means3D, radii, colors, opacities, scales, rotations, scale_modifier, cov3D_precomp,
                          viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, dL_dout_invdepth, sh, degree, campos,
                          geomBuffer, R, binningBuffer, imageBuffer, antialiasing, debug);
+}
+
+// Writes out whatever grad_sink(defer=True) has parked; returns how many views that were.
+int FlushGradSink() {
+    DeferredState& d = deferred();
+    std::lock_guard<std::mutex> lock(d.mu);
+    const int n = (int)d.views.size();
+    flush_locked(d);
+    d.accumulate = false;
+    return n;
 }
 
 torch::Tensor markVisible(torch::Tensor& means3D, torch::Tensor& viewmatrix, torch::Tensor& projmatrix) {
@@ -242,6 +307,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.def("rasterize_gaussians_backward", &RasterizeGaussiansBackwardCUDA);
     m.def("mark_visible", &markVisible);
     m.def("rasterize_gaussians_backward_into", &RasterizeGaussiansBackwardInto);
+    m.def("flush_grad_sink", &FlushGradSink);
     // the fork's spellings (DGR/ext.cpp:16, rasterize_points.h:18,41)
     m.def("rasterize_gaussians_npu", &RasterizeGaussiansCUDA);
     m.def("rasterize_gaussians_backward_npu", &RasterizeGaussiansBackwardCUDA);

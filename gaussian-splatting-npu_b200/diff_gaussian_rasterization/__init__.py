@@ -37,7 +37,7 @@ _tls = _SinkState
 
 
 @contextlib.contextmanager
-def grad_sink(means3D, shs, opacities, scales, rotations, accumulate=False):
+def grad_sink(means3D, shs, opacities, scales, rotations, accumulate=False, defer=False):
     """Extension over the reference API (opt-in; nothing changes unless it is used).
 
     Inside this context every `backward()` through the rasterizer writes the five PARAMETER gradients
@@ -47,14 +47,23 @@ def grad_sink(means3D, shs, opacities, scales, rotations, accumulate=False):
     ADD into the visible rows (second and later views of one training step); with False they overwrite
     every row (first view).  means2D / colors_precomp / cov3D_precomp gradients flow through autograd
     as usual (densification reads means2D.grad per view).
+
+    `defer=True` is for a context that spans ALL views of a step: every backward runs its blend stage at once and the
+    per-Gaussian stage is postponed; when the context closes, ONE launch per (up to) 8 views sums their parameter
+    gradients in registers and writes the sink once (gsr_backward_params_batch; `accumulate` then says whether that
+    first write adds or overwrites).  The sink tensors hold the step's gradients only after the context has closed.
+    Configurations the batched kernel does not cover (M != 16, colors_precomp, cov3D_precomp) run undeferred: the first
+    such backward follows `accumulate`, so give every view of such a step its own context as before.
     """
     prev = getattr(_tls, "sink", None)
     none = torch.empty(0)
-    _tls.sink = tuple(none if t is None else t for t in (means3D, shs, opacities, scales, rotations)) + (bool(accumulate),)
+    _tls.sink = tuple(none if t is None else t for t in (means3D, shs, opacities, scales, rotations)) + (bool(accumulate), bool(defer))
     try:
         yield
     finally:
         _tls.sink = prev
+        if defer:
+            _C.flush_grad_sink()
 
 
 class GaussianRasterizationSettings(NamedTuple):

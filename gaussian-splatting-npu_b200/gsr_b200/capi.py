@@ -66,7 +66,7 @@ class AdamSegment(ctypes.Structure):
                 ("rows", c_size_t), ("cols", c_int), ("split_col", c_int), ("lr_a", c_float), ("lr_b", c_float)]
 
 
-EXPORTS = ["gsr_forward", "gsr_backward", "gsr_forward_batch", "gsr_backward_batch", "gsr_mark_visible", "gsr_geometry_bytes", "gsr_image_bytes",
+EXPORTS = ["gsr_forward", "gsr_backward", "gsr_forward_batch", "gsr_backward_batch", "gsr_backward_blend", "gsr_backward_params_batch", "gsr_mark_visible", "gsr_geometry_bytes", "gsr_image_bytes",
            "gsr_binning_bytes", "gsr_sort_temp_bytes", "gsr_sort_pairs", "gsr_get_geometry_layout",
            "gsr_get_binning_layout", "gsr_get_image_layout", "gsr_materialize_keys", "gsr_set_profiling",
            "gsr_last_stage_ms",

@@ -161,6 +161,13 @@ int gsr_forward_batch(int n_views, const gsr_forward_args* views,
                       gsr_alloc_fn image_alloc, void* const* image_users,
                       void* stream, void* const* view_streams /* [n_views] or NULL */, int* num_rendered /* [n_views] */);
 int gsr_backward_batch(int n_views, const gsr_backward_args* views, void* stream, void* const* view_streams /* or NULL */);
+/* gsr_backward_batch in two calls, for callers that are handed the views of a step one at a time (an autograd engine runs
+ * one backward per view): gsr_backward_blend does the backward blend of ONE view now (its dL_dmean2D / dL_dconic /
+ * dL_dcolor / dL_dinvdepth outputs and the view's geometry buffer must stay alive), gsr_backward_params_batch the one
+ * per-Gaussian launch over all of them later (same argument structs; pixel gradients, binning and image buffers are not
+ * read any more; a non-NULL dL_dinvdepth means the blend produced it). */
+int gsr_backward_blend(const gsr_backward_args* view, void* stream);
+int gsr_backward_params_batch(int n_views, const gsr_backward_args* views, void* stream);
 
 /* Rasterizer::markVisible (rasterizer.h:28-33, rasterizer_impl.cu:141-153). present is bool[P] (1 byte each). */
 int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,

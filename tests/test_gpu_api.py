@@ -252,3 +252,68 @@ def test_workspace_reuse_gives_the_same_render(cuda):
         for k in ("dL_dmeans3D", "dL_dsh", "dL_dopacity"):
             assert (ga[k] - gb[k]).abs().max().item() <= 1e-4 * (ga[k].abs().max().item() + 1e-30), (name, k)
     assert ws.binning.t.numel() > 0
+
+
+@pytest.mark.parametrize("n_views", [3, 10])
+def test_grad_sink_immediate_and_deferred_equal_autograd_sum(cuda, n_views):
+    """diff_gaussian_rasterization.grad_sink: the parameter gradients of the views of a step written into caller-owned
+    tensors -- view by view (accumulate) or, with defer=True, by ONE batched per-Gaussian launch per 8 views when the
+    context closes -- equal what plain autograd accumulates in .grad; means2D gradients keep flowing through autograd."""
+    import torch
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer, grad_sink
+    from gsr_b200 import synth
+    P, W, H = 20_000, 167, 101
+    scene = synth.trained_like_scene(P, 31, s0=0.03)
+    cams = synth.orbit_cameras(max(8, n_views), W, H, 31)[:n_views]
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(cuda)
+    names = ("means3D", "shs", "opacities", "scales", "rotations")
+    rng = np.random.default_rng(7)
+    weights = [t(rng.standard_normal((3, H, W)).astype(np.float32)) for _ in cams]
+    bg = torch.tensor([0.2, 0.1, 0.3], device=cuda)
+
+    def render_all(leaves, ctx_for):
+        m2d = []
+        for v, c in enumerate(cams):
+            rs = GaussianRasterizationSettings(
+                image_height=H, image_width=W, tanfovx=c.tanfovx, tanfovy=c.tanfovy, bg=bg, scale_modifier=1.0,
+                viewmatrix=t(c.world_view_transform), projmatrix=t(c.full_proj_transform), sh_degree=3, campos=t(c.camera_center),
+                prefiltered=False, debug=False, antialiasing=False)
+            means2D = torch.zeros(P, 3, device=cuda, requires_grad=True)
+            color, radii, invd = GaussianRasterizer(rs)(means3D=leaves["means3D"], means2D=means2D, opacities=leaves["opacities"],
+                                                        shs=leaves["shs"], scales=leaves["scales"], rotations=leaves["rotations"])
+            loss = (color * weights[v]).sum() + 0.3 * invd.sum()
+            with ctx_for(v):
+                loss.backward()
+            m2d.append(means2D)
+        return m2d
+
+    import contextlib
+    # plain autograd: .grad accumulates over the views
+    ref = {k: t(scene[k]).requires_grad_(True) for k in names}
+    m2d_ref = render_all(ref, lambda v: contextlib.nullcontext())
+    want = {k: ref[k].grad.double() for k in names}
+    tol = dict(scales=1e-3, rotations=1e-3)
+
+    def check(sinks, m2d):
+        for k in names:
+            err = (sinks[k].double() - want[k]).abs().max().item() / (want[k].abs().max().item() + 1e-30)
+            assert err <= tol.get(k, 1e-5), (k, err)
+        for a, b in zip(m2d, m2d_ref):
+            assert (a.grad - b.grad).abs().max().item() <= 1e-5 * (b.grad.abs().max().item() + 1e-30)
+
+    # immediate sink, one context per view
+    leaves = {k: t(scene[k]).requires_grad_(True) for k in names}
+    sinks = {k: torch.full_like(leaves[k], 9.0) for k in names}
+    m2d = render_all(leaves, lambda v: grad_sink(*(sinks[k] for k in names), accumulate=(v > 0)))
+    assert all(leaves[k].grad is None for k in names)
+    check(sinks, m2d)
+
+    # deferred sink, one context around the whole step (n_views = 10: two batched launches, the second one adds)
+    leaves = {k: t(scene[k]).requires_grad_(True) for k in names}
+    sinks = {k: torch.full_like(leaves[k], 9.0) for k in names}
+    with grad_sink(*(sinks[k] for k in names), accumulate=False, defer=True):
+        m2d = render_all(leaves, lambda v: contextlib.nullcontext())
+    assert all(leaves[k].grad is None for k in names)
+    check(sinks, m2d)
+    from diff_gaussian_rasterization import _C
+    assert _C.flush_grad_sink() == 0                      # nothing left parked
