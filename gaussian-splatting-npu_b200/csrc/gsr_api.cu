@@ -429,10 +429,22 @@ extern "C" int gsr_forward_batch(int n_views, const gsr_forward_args* views, gsr
     cudaEvent_t* ev = batch_events(dev_id);
     if (!ev) return fail(GSR_ERR_CUDA, "batch: cannot create events");
     CUDA_TRY(cudaEventRecord(ev[0], stream));
+    // on every exit path -- errors included -- the caller's stream is ordered after whatever the view streams were given:
+    // the scratch they touch is the caller's and may be released once this call returns
+    struct JoinViews {
+        cudaStream_t main; cudaStream_t sv[GSR_MAX_VIEWS]; cudaEvent_t* ev; int n = 0; bool armed = true;
+        ~JoinViews() {
+            if (!armed) return;
+            for (int v = 0; v < n; v++)
+                if (sv[v] != main) { cudaEventRecord(ev[1 + v], sv[v]); cudaStreamWaitEvent(main, ev[1 + v], 0); }
+        }
+    } join_views;
+    join_views.main = stream; join_views.ev = ev;
     const int gsort_bits = 32, gsort_passes = (gsort_bits + 7) / 8;
     const int g0 = (gsort_passes & 1) ? 1 : 0;
     for (int v = 0; v < n_views; v++) {
         cudaStream_t sv = vstream(v);
+        join_views.sv[v] = sv; join_views.n = v + 1;
         if (sv != stream) CUDA_TRY(cudaStreamWaitEvent(sv, ev[0], 0));
         launch_scan_compact(P, g[v], g[v].gsort_keys[g0], g[v].gsort_vals[g0], sv);
         CUDA_TRY(cudaMemcpyAsync(pinned + 4 * v, g[v].scan_state + 1, 12, cudaMemcpyDeviceToHost, sv));
@@ -477,6 +489,7 @@ extern "C" int gsr_forward_batch(int n_views, const gsr_forward_args* views, gsr
             CUDA_TRY(cudaStreamWaitEvent(stream, ev[1 + v], 0));
         }
     }
+    join_views.armed = false;           // joined view by view above
     return GSR_OK;
 }
 

@@ -114,3 +114,14 @@ def test_fused_ssim_package_has_no_cpu_fallback():
         l1_ssim_loss(a[0], a[0])
     with pytest.raises(AssertionError):
         fused_ssim(a, a, padding="reflect")
+
+
+def test_headers_are_plain_c():
+    """The boundary is a C ABI: every header under include/ compiles as C99 on its own (no C++, no torch, no CUDA types)."""
+    import glob
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for h in sorted(glob.glob(os.path.join(root, "include", "*.h"))):
+        r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-x", "c", "-fsyntax-only", "-"],
+                           input='#include "%s"\n' % h, capture_output=True, text=True)
+        assert r.returncode == 0, (h, r.stderr[:500])
