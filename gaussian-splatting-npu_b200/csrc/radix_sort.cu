@@ -331,3 +331,71 @@ void launch_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out,
         cudaMemcpyAsync(vals_out, vals_in, n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s);
     }
 }
+
+// ---- gsr_sort_pairs_static: the same sort for callers that cannot allocate ---------------------------
+//
+// gsr_sort_pairs needs a `temp` block from its caller.  Some callers have no way to provide one: a
+// plugin loaded into a host application that owns the whole device heap and hands the plugin only its
+// input and output buffers, a real-time loop that forbids allocator calls once it is running, or an FFI
+// binding (cgo/JNI/ctypes without torch) that has no device allocator at hand at all.  For them the
+// histogram / ticket / look-back status block lives in the library's own image, in the file-scope
+// array below.  Its size is fixed at build time for GSR_SORT_STATIC_MAX_PAIRS pairs (2^20 -> about
+// 2.1 MB); every device that loads libgsr_b200.so holds that much until the process exits.
+#include "../../include/gsr.h"
+#include <mutex>
+
+#define SORT_STATIC_HEAD (((size_t)SORT_MAX_PASSES * RADIX * 4 + 64 + 255) / 256 * 256)
+#define SORT_STATIC_TILES (((size_t)GSR_SORT_STATIC_MAX_PAIRS + SORT_TILE - 1) / SORT_TILE)
+#define SORT_STATIC_BYTES (SORT_STATIC_HEAD + (size_t)SORT_MAX_PASSES * SORT_STATIC_TILES * RADIX * 4 + 256)
+
+static __device__ __align__(256) unsigned char g_sort_static_scratch[SORT_STATIC_BYTES];
+
+// On the host, `g_sort_static_scratch` is only a handle for the runtime's symbol table -- it is not
+// where the array lives on the GPU, and a kernel or memset given that value would touch the wrong
+// memory.  The device address is asked for once per device (while that device is current) and kept.
+#define SORT_STATIC_MAX_DEVICES 64
+static std::mutex g_sort_static_mutex;
+static char* g_sort_static_ptr[SORT_STATIC_MAX_DEVICES];   // zero-initialised: "not looked up yet"
+
+static int sort_static_scratch(char** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return gsr_set_error(GSR_ERR_CUDA, cudaGetErrorString(e));
+    if (dev < 0 || dev >= SORT_STATIC_MAX_DEVICES) return gsr_set_error(GSR_ERR_INVALID, "gsr_sort_pairs_static: device ordinal out of range");
+    std::lock_guard<std::mutex> lock(g_sort_static_mutex);
+    if (!g_sort_static_ptr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_sort_static_scratch);
+        if (e != cudaSuccess || !p) {
+            cudaGetLastError();
+            return gsr_set_error(GSR_ERR_CUDA, e != cudaSuccess ? cudaGetErrorString(e) : "gsr_sort_pairs_static: cudaGetSymbolAddress returned null");
+        }
+        g_sort_static_ptr[dev] = static_cast<char*>(p);
+    }
+    *out = g_sort_static_ptr[dev];
+    return GSR_OK;
+}
+
+extern "C" size_t gsr_sort_static_max_pairs(void) { return (size_t)GSR_SORT_STATIC_MAX_PAIRS; }
+
+extern "C" int gsr_sort_pairs_static(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                                     size_t n, int end_bit, void* stream_) {
+    if (end_bit < 0 || end_bit > 64) return gsr_set_error(GSR_ERR_INVALID, "end_bit out of range");
+    if (n > (size_t)GSR_SORT_STATIC_MAX_PAIRS)
+        return gsr_set_error(GSR_ERR_INVALID, "gsr_sort_pairs_static: n exceeds GSR_SORT_STATIC_MAX_PAIRS (2^20); "
+                                              "use gsr_sort_pairs with caller-provided temp for larger inputs");
+    if (n && (!keys_in || !vals_in || !keys_out || !vals_out)) return gsr_set_error(GSR_ERR_INVALID, "null argument");
+    if (n == 0) return GSR_OK;
+    static_assert(SORT_STATIC_BYTES < ((size_t)4 << 20), "the built-in scratch is meant to stay small");
+    if (sort_temp_bytes(n) > SORT_STATIC_BYTES) return gsr_set_error(GSR_ERR_INVALID, "gsr_sort_pairs_static: built-in scratch too small for n");
+    char* scratch = nullptr;
+    int rc = sort_static_scratch(&scratch);
+    if (rc != GSR_OK) return rc;
+    cudaStream_t s = (cudaStream_t)stream_;
+    // launch_sort_pairs zeroes the histogram, ticket and status words it is about to use (whatever the
+    // previous call left there) with a memset on `s`, then runs the same kernels as gsr_sort_pairs.
+    launch_sort_pairs(keys_in, vals_in, keys_out, vals_out, n, end_bit, scratch, s);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return gsr_set_error(GSR_ERR_CUDA, cudaGetErrorString(e));
+    return GSR_OK;
+}

@@ -67,7 +67,8 @@ class AdamSegment(ctypes.Structure):
 
 
 EXPORTS = ["gsr_forward", "gsr_backward", "gsr_forward_batch", "gsr_backward_batch", "gsr_backward_blend", "gsr_backward_params_batch", "gsr_mark_visible", "gsr_geometry_bytes", "gsr_image_bytes",
-           "gsr_binning_bytes", "gsr_sort_temp_bytes", "gsr_sort_pairs", "gsr_get_geometry_layout",
+           "gsr_binning_bytes", "gsr_sort_temp_bytes", "gsr_sort_pairs", "gsr_sort_static_max_pairs", "gsr_sort_pairs_static",
+           "gsr_get_geometry_layout",
            "gsr_get_binning_layout", "gsr_get_image_layout", "gsr_materialize_keys", "gsr_set_profiling",
            "gsr_last_stage_ms",
            "gsr_last_error", "gsr_version",
@@ -112,6 +113,10 @@ def lib():
         L.gsr_sort_temp_bytes.argtypes = [c_size_t]
         L.gsr_sort_pairs.restype = c_int
         L.gsr_sort_pairs.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_void_p, c_void_p]
+        L.gsr_sort_static_max_pairs.restype = c_size_t
+        L.gsr_sort_static_max_pairs.argtypes = []
+        L.gsr_sort_pairs_static.restype = c_int
+        L.gsr_sort_pairs_static.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_void_p]
         L.gsr_get_geometry_layout.argtypes = [c_int, POINTER(GeometryLayout)]
         L.gsr_get_binning_layout.argtypes = [c_size_t, c_int, c_int, POINTER(BinningLayout)]
         L.gsr_get_image_layout.argtypes = [c_int, c_int, POINTER(ImageLayout)]
@@ -443,6 +448,20 @@ def sort_pairs(keys, values, end_bit):
     with torch.cuda.device(keys.device):
         _check(L.gsr_sort_pairs(_ptr(keys) if n else None, _ptr(values) if n else None, c_void_p(ko.data_ptr()) if n else None,
                                 c_void_p(vo.data_ptr()) if n else None, n, end_bit, c_void_p(temp.data_ptr()), _stream()))
+    return ko, vo
+
+
+def sort_pairs_static(keys, values, ko, vo, end_bit):
+    """gsr_sort_pairs_static: the 64-bit sort on the library's built-in scratch array, for callers that
+    cannot allocate device memory.  All four tensors come from the caller (this wrapper allocates
+    nothing, so that it can stand in for such a caller); keys/values are clobbered, the result lands in
+    ko/vo.  At most gsr_sort_static_max_pairs() pairs; calls that overlap on the GPU race on the array."""
+    L = lib()
+    n = keys.numel()
+    with torch.cuda.device(keys.device):
+        _check(L.gsr_sort_pairs_static(_ptr(keys) if n else None, _ptr(values) if n else None,
+                                       c_void_p(ko.data_ptr()) if n else None, c_void_p(vo.data_ptr()) if n else None,
+                                       n, end_bit, _stream()))
     return ko, vo
 
 

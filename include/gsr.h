@@ -18,7 +18,8 @@
  *   - every function returns GSR_OK (0) or a negative error code and never throws;
  *     gsr_last_error() returns the calling thread's last message;
  *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream, which is what the
- *     reference launches on).  Entry points are re-entrant and keep no global mutable state.
+ *     reference launches on).  Entry points are re-entrant and keep no global mutable state
+ *     (the one exception is gsr_sort_pairs_static, which says so).
  */
 #ifndef GSR_H_INCLUDED
 #define GSR_H_INCLUDED
@@ -188,6 +189,35 @@ size_t gsr_binning_bytes(size_t num_rendered, int width, int height);
 size_t gsr_sort_temp_bytes(size_t n);
 int gsr_sort_pairs(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
                    size_t n, int end_bit, char* temp, void* stream);
+
+/*
+ * gsr_sort_pairs for callers that cannot allocate device memory.  (No counterpart in the reference:
+ * its sort always draws temp storage from the torch allocator through the binning-buffer callback.)
+ *
+ * Who needs it: code that is handed its input and output buffers by someone else and has no device
+ * allocator of its own -- a plugin inside a host application that owns the device heap, a frame loop
+ * that bans allocator calls after start-up, an FFI binding without torch.  Same sort, same kernels,
+ * same result as gsr_sort_pairs (stable, key bits [0, end_bit), inputs clobbered, result in
+ * keys_out/vals_out), but the histogram / ticket / look-back status block is a fixed array built into
+ * libgsr_b200.so instead of a `temp` argument.  The call itself performs no cudaMalloc/cudaFree and
+ * uses no allocating library routine.
+ *
+ * Limits and rules
+ *   - n <= GSR_SORT_STATIC_MAX_PAIRS (also returned by gsr_sort_static_max_pairs()); a larger n is
+ *     refused with GSR_ERR_INVALID and a message naming the limit -- use gsr_sort_pairs then.
+ *   - The array is about 2.1 MB and is held by every device that loads the library, until exit.
+ *   - The first call on each device looks up the array's device address (the device must be current,
+ *     as for every entry point) and keeps it; make that first call before starting any stream
+ *     capture.  Later calls on that device only enqueue a memset and the sort kernels on `stream`.
+ *   - There is ONE array per device and every call uses it.  Each call clears the words it needs
+ *     first, so nothing has to be reset between calls, but two calls whose GPU work can overlap
+ *     (different streams without an ordering between them, or two host threads) race on it and
+ *     produce garbage.  Order them on one stream or with events.
+ */
+#define GSR_SORT_STATIC_MAX_PAIRS (1u << 20)
+size_t gsr_sort_static_max_pairs(void);
+int gsr_sort_pairs_static(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                          size_t n, int end_bit, void* stream);
 
 /*
  * Introspection of the opaque scratch buffers for the parity tests (the reference's tests would
