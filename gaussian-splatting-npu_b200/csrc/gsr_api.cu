@@ -359,6 +359,7 @@ static int batch_shared_check(int n, int P0, int D0, int M0, const float* m0, co
 
 // Per-(thread, device) events of the batch entry points: [0] = the batched kernel has run on the caller's stream,
 // [1 + v] = view v's work on its own stream (counts copied / chain finished).
+static_assert(GSR_MAX_VIEWS == GSR_MAX_BATCH_VIEWS, "the public batch limit (gsr.h) and the kernels' view arrays (gsr_common.cuh) must agree");
 static cudaEvent_t* batch_events(int dev_id) {
     static thread_local cudaEvent_t ev[64][1 + GSR_MAX_VIEWS] = {};
     if (!ev[dev_id][0])
@@ -497,12 +498,7 @@ extern "C" int gsr_forward_batch(int n_views, const gsr_forward_args* views, gsr
 static int backward_batch_impl(int n_views, const gsr_backward_args* views, void* stream_, void* const* view_streams, int stages) {
     cudaStream_t stream = (cudaStream_t)stream_;
     auto vstream = [&](int v) { return (view_streams && view_streams[v]) ? (cudaStream_t)view_streams[v] : stream; };
-    int dev_id = 0;
-    CUDA_TRY(cudaGetDevice(&dev_id));
-    if (dev_id < 0 || dev_id >= 64) return fail(GSR_ERR_INVALID, "device ordinal %d out of range", dev_id);
-    cudaEvent_t* ev = batch_events(dev_id);
-    if (!ev) return fail(GSR_ERR_CUDA, "batch: cannot create events");
-    CUDA_TRY(cudaEventRecord(ev[0], stream));
+    // every argument is checked before anything is enqueued: a rejected call leaves the streams untouched
     if (!views) return fail(GSR_ERR_INVALID, "null argument");
     if (n_views < 1 || n_views > GSR_MAX_VIEWS) return fail(GSR_ERR_INVALID, "batch: n_views = %d outside 1..%d", n_views, GSR_MAX_VIEWS);
     const gsr_backward_args& a0 = views[0];
@@ -513,6 +509,28 @@ static int backward_batch_impl(int n_views, const gsr_backward_args* views, void
         return fail(GSR_ERR_INVALID, "batch: views[0] must carry the five parameter-gradient outputs");
     if (check_aligned16(a0.rotations, "rotations") || check_aligned16(a0.dL_drot, "dL_drot") || check_aligned16(a0.shs, "shs") ||
         check_aligned16(a0.dL_dsh, "dL_dsh")) return GSR_ERR_INVALID;
+    for (int v = 0; v < n_views; v++) {
+        const gsr_backward_args& a = views[v];
+        if (a.width <= 0 || a.height <= 0 || a.R < 0) return fail(GSR_ERR_INVALID, "bad sizes");
+        if (a.D < 0 || a.D > 3 || (a.D + 1) * (a.D + 1) > a.M) return fail(GSR_ERR_INVALID, "SH degree %d does not fit M=%d", a.D, a.M);
+        if (batch_shared_check(n_views, a0.P, a0.D, a0.M, a0.means3D, a0.shs, a0.opacities, a0.scales, a0.rotations, a0.scale_modifier,
+                               a0.antialiasing, a.P, a.D, a.M, a.means3D, a.shs, a.opacities, a.scales, a.rotations, a.scale_modifier,
+                               a.antialiasing, a.colors_precomp, a.cov3D_precomp)) return GSR_ERR_INVALID;
+        if (!a.means3D || !a.opacities) return fail(GSR_ERR_INVALID, "missing required input pointer");
+        if ((stages & 2) && (!a.viewmatrix || !a.projmatrix || !a.cam_pos)) return fail(GSR_ERR_INVALID, "missing camera pointer");
+        if ((stages & 1) && !a.background) return fail(GSR_ERR_INVALID, "background is null");
+        if (!a.geom_buffer || !a.radii || ((stages & 1) && (!a.binning_buffer || !a.image_buffer || !a.dL_dpix)))
+            return fail(GSR_ERR_INVALID, "missing buffer");
+        if (!a.dL_dmean2D || !a.dL_dconic || !a.dL_dcolor) return fail(GSR_ERR_INVALID, "missing per-view gradient output");
+        if (a.dL_dinvdepth_pix && !a.dL_dinvdepth) return fail(GSR_ERR_INVALID, "dL_dinvdepth output required");
+        if (check_aligned16(a.dL_dconic, "dL_dconic")) return GSR_ERR_INVALID;
+    }
+    int dev_id = 0;
+    CUDA_TRY(cudaGetDevice(&dev_id));
+    if (dev_id < 0 || dev_id >= 64) return fail(GSR_ERR_INVALID, "device ordinal %d out of range", dev_id);
+    cudaEvent_t* ev = batch_events(dev_id);
+    if (!ev) return fail(GSR_ERR_CUDA, "batch: cannot create events");
+    CUDA_TRY(cudaEventRecord(ev[0], stream));
     BwdBatchParams bp;
     bp.P = P; bp.D = a0.D; bp.V = n_views; bp.antialiasing = a0.antialiasing; bp.accumulate = a0.accumulate != 0;
     bp.scale_modifier = a0.scale_modifier;
@@ -521,15 +539,6 @@ static int backward_batch_impl(int n_views, const gsr_backward_args* views, void
     for (int v = 0; v < n_views; v++) {
         const gsr_backward_args& a = views[v];
         const int W = a.width, H = a.height;
-        if (W <= 0 || H <= 0 || a.R < 0) return fail(GSR_ERR_INVALID, "bad sizes");
-        if (batch_shared_check(n_views, a0.P, a0.D, a0.M, a0.means3D, a0.shs, a0.opacities, a0.scales, a0.rotations, a0.scale_modifier,
-                               a0.antialiasing, a.P, a.D, a.M, a.means3D, a.shs, a.opacities, a.scales, a.rotations, a.scale_modifier,
-                               a.antialiasing, a.colors_precomp, a.cov3D_precomp)) return GSR_ERR_INVALID;
-        if (!a.geom_buffer || !a.radii || ((stages & 1) && (!a.binning_buffer || !a.image_buffer || !a.dL_dpix)))
-            return fail(GSR_ERR_INVALID, "missing buffer");
-        if (!a.dL_dmean2D || !a.dL_dconic || !a.dL_dcolor) return fail(GSR_ERR_INVALID, "missing per-view gradient output");
-        if (a.dL_dinvdepth_pix && !a.dL_dinvdepth) return fail(GSR_ERR_INVALID, "dL_dinvdepth output required");
-        if (check_aligned16(a.dL_dconic, "dL_dconic")) return GSR_ERR_INVALID;
         const int gx = (W + GSR_TILE - 1) / GSR_TILE, gy = (H + GSR_TILE - 1) / GSR_TILE;
         GeomView g = geom_view(a.geom_buffer, P);
         BwdParams p;

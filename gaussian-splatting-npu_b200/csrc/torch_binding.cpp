@@ -12,6 +12,8 @@
 // *current* device), and outputs the kernels fully write are torch::empty instead of zero-filled.
 #include <torch/extension.h>
 #include <ATen/cuda/CUDAContext.h>
+#include <ATen/cuda/CUDAEvent.h>
+#include <c10/cuda/CUDACachingAllocator.h>
 #include <c10/cuda/CUDAGuard.h>
 #include <mutex>
 #include <stdexcept>
@@ -110,6 +112,7 @@ struct GradSink { torch::Tensor means3D, sh, opacity, scales, rotations; bool ac
 struct DeferredView {
     gsr_backward_args a;                       // pointers into the tensors below
     std::vector<torch::Tensor> keep;
+    at::cuda::CUDAEvent done;                  // recorded behind this view's blend, on the stream the blend ran on
 };
 struct DeferredState {
     std::mutex mu;
@@ -119,12 +122,32 @@ struct DeferredState {
 };
 DeferredState& deferred() { static DeferredState d; return d; }
 
+// Two views may share one gsr_backward_params_batch launch only if they read the same Gaussians (all five parameter
+// arrays, not just means3D / shs: a caller that recomputes sigmoid / exp per render hands over fresh tensors every time)
+// and write the same sink.  This is exactly what batch_shared_check (gsr_api.cu) insists on, so a view that passes it
+// can never make the flush fail and take the parked views' gradients with it.
+static bool same_batch(const gsr_backward_args& f, const gsr_backward_args& a) {
+    return f.P == a.P && f.D == a.D && f.M == a.M && f.means3D == a.means3D && f.shs == a.shs && f.opacities == a.opacities &&
+           f.scales == a.scales && f.rotations == a.rotations && f.scale_modifier == a.scale_modifier &&
+           f.antialiasing == a.antialiasing && f.dL_dmean3D == a.dL_dmean3D && f.dL_dsh == a.dL_dsh &&
+           f.dL_dopacity == a.dL_dopacity && f.dL_dscale == a.dL_dscale && f.dL_drot == a.dL_drot;
+}
+
 void flush_locked(DeferredState& d) {
     if (d.views.empty()) return;
     const c10::cuda::CUDAGuard guard(d.device);
-    cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+    // The flush runs on the flushing thread's current stream, which need not be the one the blends ran on (backward()
+    // under another stream context, or the context closed elsewhere): wait for every view's blend, and tell the caching
+    // allocator that the parked tensors are read on this stream too before they are released below.
+    const at::cuda::CUDAStream flush_stream = at::cuda::getCurrentCUDAStream();
+    cudaStream_t stream = flush_stream;
     std::vector<gsr_backward_args> arr;
-    for (auto& v : d.views) arr.push_back(v.a);
+    for (auto& v : d.views) {
+        arr.push_back(v.a);
+        v.done.block(flush_stream);
+        for (const torch::Tensor& t : v.keep)
+            if (t.defined() && t.is_cuda() && t.numel()) c10::cuda::CUDACachingAllocator::recordStream(t.storage().data_ptr(), flush_stream);
+    }
     arr[0].accumulate = d.accumulate ? 1 : 0;
     const int st = gsr_backward_params_batch((int)arr.size(), arr.data(), stream);
     d.views.clear();
@@ -220,9 +243,7 @@ backward_impl(const GradSink& sink, const torch::Tensor& background, const torch
             std::lock_guard<std::mutex> lock(d.mu);
             // a different set of Gaussians / sinks than the parked views' (or a full batch): write those out first
             if (!d.views.empty()) {
-                const gsr_backward_args& f = d.views[0].a;
-                if (d.views.size() >= GSR_MAX_BATCH_VIEWS || f.P != a.P || f.means3D != a.means3D || f.shs != a.shs || f.dL_dsh != a.dL_dsh ||
-                    f.D != a.D || f.scale_modifier != a.scale_modifier || f.antialiasing != a.antialiasing) flush_locked(d);
+                if (d.views.size() >= GSR_MAX_BATCH_VIEWS || !same_batch(d.views[0].a, a)) flush_locked(d);
             } else {
                 d.accumulate = sink.accumulate;
             }
@@ -232,6 +253,7 @@ backward_impl(const GradSink& sink, const torch::Tensor& background, const torch
             DeferredView dv;
             dv.a = a;
             dv.keep = keep;
+            dv.done.record(at::cuda::getCurrentCUDAStream());
             for (const torch::Tensor& t : { radii_c, gb, dL_dmeans2D, dL_dconic, dL_dcolors, dL_dinvdepths, dL_dmeans3D, dL_dopacity,
                                              dL_dsh, dL_dscales, dL_drotations }) dv.keep.push_back(t);
             d.views.push_back(std::move(dv));

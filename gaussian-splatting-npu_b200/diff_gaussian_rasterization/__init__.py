@@ -54,6 +54,12 @@ def grad_sink(means3D, shs, opacities, scales, rotations, accumulate=False, defe
     first write adds or overwrites).  The sink tensors hold the step's gradients only after the context has closed.
     Configurations the batched kernel does not cover (M != 16, colors_precomp, cov3D_precomp) run undeferred: the first
     such backward follows `accumulate`, so give every view of such a step its own context as before.
+    Views share a launch only when they pass the SAME five parameter tensors (same storage) to the rasterizer: a caller
+    that builds them afresh per render -- the reference's `pc.get_features` is a new `torch.cat` every time, `get_opacity`
+    a new sigmoid (scene/gaussian_model.py) -- gets a correct result, but each view is then written out on its own when
+    the next one arrives, i.e. nothing is batched.  Compute the activated tensors once per step to get the batching.
+    The write-out happens on the stream that is current where the context closes (or where a later view forces it); it
+    waits for the blends of the parked views, whatever stream those ran on.
     """
     prev = getattr(_tls, "sink", None)
     none = torch.empty(0)

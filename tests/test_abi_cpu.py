@@ -68,6 +68,39 @@ def test_argument_validation_without_gpu():
     assert L.gsr_mark_visible(0, None, None, None, None, None) == 0
     assert L.gsr_sort_pairs(None, None, None, None, 0, 80, None, None) == -1
     assert L.gsr_last_stage_ms(0) == -1.0
+    # the allocation-free sort refuses what its built-in array cannot hold, before touching the device
+    assert L.gsr_sort_static_max_pairs() == 1 << 20
+    assert L.gsr_sort_pairs_static(1, 1, 1, 1, (1 << 20) + 1, 45, None) == -1
+    assert b"GSR_SORT_STATIC_MAX_PAIRS" in L.gsr_last_error()
+    assert L.gsr_sort_pairs_static(None, None, None, None, 0, 45, None) == 0
+
+
+def test_backward_batch_validates_before_any_cuda_call():
+    """gsr_backward_batch / _blend / _params_batch reject bad arguments with GSR_ERR_INVALID before they touch the device
+    (on this GPU-less box a CUDA call would come back as GSR_ERR_CUDA = -2 instead): SH degree outside 0..3, missing
+    camera pointers, views that do not share their Gaussians."""
+    L = capi.lib()
+    assert L.gsr_backward_batch(1, None, None, None) == -1
+    arr = (capi.BackwardArgs * 2)()
+    for a in arr:
+        a.P, a.D, a.M, a.R, a.width, a.height = 10, 3, 16, 5, 32, 32
+        a.scale_modifier = 1.0
+        for name in ("background", "means3D", "shs", "opacities", "scales", "rotations", "viewmatrix", "projmatrix", "cam_pos",
+                     "radii", "geom_buffer", "binning_buffer", "image_buffer", "dL_dpix", "dL_dmean2D", "dL_dconic",
+                     "dL_dopacity", "dL_dcolor", "dL_dmean3D", "dL_dsh", "dL_dscale", "dL_drot"):
+            setattr(a, name, 256)                         # aligned non-null sentinel, never dereferenced on the host
+    assert L.gsr_backward_batch(9, arr, None, None) == -1 and b"n_views" in L.gsr_last_error()
+    arr[1].D = 5
+    assert L.gsr_backward_batch(2, arr, None, None) == -1 and b"SH degree" in L.gsr_last_error()
+    arr[1].D = 3
+    arr[1].cam_pos = None
+    assert L.gsr_backward_params_batch(2, arr, None) == -1 and b"camera" in L.gsr_last_error()
+    arr[1].cam_pos = 256
+    arr[1].opacities = 512
+    assert L.gsr_backward_batch(2, arr, None, None) == -1 and b"share" in L.gsr_last_error()
+    arr[1].opacities = 256
+    arr[0].dL_dconic = 260
+    assert L.gsr_backward_blend(arr, None) == -1 and b"aligned" in L.gsr_last_error()
 
 
 def test_python_api_has_no_cpu_fallback():

@@ -317,3 +317,69 @@ def test_grad_sink_immediate_and_deferred_equal_autograd_sum(cuda, n_views):
     check(sinks, m2d)
     from diff_gaussian_rasterization import _C
     assert _C.flush_grad_sink() == 0                      # nothing left parked
+
+
+def test_deferred_grad_sink_with_fresh_parameter_tensors_and_a_side_stream(cuda):
+    """grad_sink(defer=True) when the views do NOT share their parameter tensors (a caller that recomputes the activations
+    per render, as the reference's GaussianModel properties do) and when backward() runs under another stream than the one
+    the context closes on: views that cannot share a batched launch are written out one by one instead of failing at the
+    flush, the write-out waits for the blends, and the sink still holds the autograd sum."""
+    import contextlib
+    import torch
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer, grad_sink, _C
+    from gsr_b200 import synth
+    P, W, H, n_views = 20_000, 167, 101, 4
+    scene = synth.trained_like_scene(P, 33, s0=0.03)
+    cams = synth.orbit_cameras(8, W, H, 33)[:n_views]
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(cuda)
+    names = ("means3D", "shs", "opacities", "scales", "rotations")
+    rng = np.random.default_rng(9)
+    weights = [t(rng.standard_normal((3, H, W)).astype(np.float32)) for _ in cams]
+    bg = torch.tensor([0.2, 0.1, 0.3], device=cuda)
+    alive = []                                            # keeps the per-view copies alive so their addresses differ
+
+    def render_all(leaves, fresh):
+        for v, c in enumerate(cams):
+            rs = GaussianRasterizationSettings(
+                image_height=H, image_width=W, tanfovx=c.tanfovx, tanfovy=c.tanfovy, bg=bg, scale_modifier=1.0,
+                viewmatrix=t(c.world_view_transform), projmatrix=t(c.full_proj_transform), sh_degree=3, campos=t(c.camera_center),
+                prefiltered=False, debug=False, antialiasing=False)
+            args = dict(leaves)
+            for k in fresh(v):
+                args[k] = leaves[k].detach().clone().requires_grad_(True)
+                alive.append(args[k])
+            means2D = torch.zeros(P, 3, device=cuda, requires_grad=True)
+            color, radii, invd = GaussianRasterizer(rs)(means3D=args["means3D"], means2D=means2D, opacities=args["opacities"],
+                                                        shs=args["shs"], scales=args["scales"], rotations=args["rotations"])
+            ((color * weights[v]).sum() + 0.3 * invd.sum()).backward()
+
+    ref = {k: t(scene[k]).requires_grad_(True) for k in names}
+    render_all(ref, lambda v: ())
+    want = {k: ref[k].grad.double() for k in names}
+    tol = dict(scales=1e-3, rotations=1e-3)
+
+    def check(sinks):
+        torch.cuda.synchronize()
+        for k in names:
+            err = (sinks[k].double() - want[k]).abs().max().item() / (want[k].abs().max().item() + 1e-30)
+            assert err <= tol.get(k, 1e-5), (k, err)
+
+    # (1) opacities / scales / rotations are new tensors in views 1 and 3, shs in view 2: four write-outs, no error
+    leaves = {k: t(scene[k]).requires_grad_(True) for k in names}
+    sinks = {k: torch.full_like(leaves[k], 9.0) for k in names}
+    pick = {0: (), 1: ("opacities", "scales", "rotations"), 2: ("shs",), 3: ("opacities",)}
+    with grad_sink(*(sinks[k] for k in names), accumulate=False, defer=True):
+        render_all(leaves, lambda v: pick[v])
+    assert _C.flush_grad_sink() == 0
+    check(sinks)
+
+    # (2) shared tensors, forward + backward on a side stream, the context closes (and flushes) on the default stream
+    leaves = {k: t(scene[k]).requires_grad_(True) for k in names}
+    sinks = {k: torch.full_like(leaves[k], 9.0) for k in names}
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with grad_sink(*(sinks[k] for k in names), accumulate=False, defer=True):
+        with torch.cuda.stream(side):
+            render_all(leaves, lambda v: ())
+    check(sinks)
+    del alive[:]
