@@ -88,8 +88,12 @@ class SymmetricGaussians(FlatGaussians):
             import torch.distributed._symmetric_memory as symm_mem
             try:
                 symm_mem.enable_symm_mem_for_group(self.group.group_name)
-            except Exception:
-                pass
+            except Exception as e:                                   # noqa: BLE001 -- re-raised unless it is the benign case
+                # a second SymmetricGaussians on the same group (FusedExchange.remap after a densification) finds the
+                # group enabled already; anything else is a real set-up failure and must not be swallowed
+                if "already" not in str(e).lower():
+                    raise RuntimeError("symmetric memory cannot be enabled for process group %r: %s"
+                                       % (self.group.group_name, e)) from e
             self._storage = symm_mem.empty(self._n_total, dtype=torch.float32, device=device)
             self._storage.zero_()
             self._hdl = symm_mem.rendezvous(self._storage, self.group.group_name)
@@ -209,3 +213,64 @@ class FusedExchange:
 
     def allreduce(self, stats=False):
         self._launch(False, stats)
+
+    def remap(self, keep_mask=None, new_rows=None):
+        """Carries the sharded optimizer across a densification event; returns a NEW FusedExchange on a NEW
+        SymmetricGaussians of P' = keep_mask.sum() + n_new rows (this object and its `flat` are dead afterwards).
+
+        The reference edits the optimizer state row by row when the set of Gaussians changes
+        (/root/reference/train.py:163-174): `_prune_optimizer` keeps the masked rows of every parameter and of its
+        exp_avg / exp_avg_sq (/root/reference/scene/gaussian_model.py:316-331), `cat_tensors_to_optimizer` appends the new
+        rows with ZERO moments (:344-363), and `densification_postfix` / `prune_points` start the three statistic
+        accumulators over at the new size (:381-392).  Here the moments are sharded by flat-buffer offset and the offsets
+        depend on P, so the shards are first brought back to row space (every rank contributes its shard to a zeroed
+        full-length buffer, summed over the group -- x + 0 is exact), pruned / extended exactly as above, laid out for P',
+        and re-sharded.  The step count (Adam's bias correction), learning rates and the chosen data path carry over.
+
+        keep_mask  bool[P] (True = the Gaussian stays), None = keep all.
+        new_rows   {"xyz": [n,3], "shs": [n,16,3], "opacity": [n,1], "scales": [n,3], "rotations": [n,4]} appended after
+                   the kept rows, None = nothing appended.
+        COLLECTIVE: every rank of the group calls it with the same mask and rows (the replicas are identical)."""
+        f = self.flat
+        dev = f.device
+        keep = torch.ones(f.P, dtype=torch.bool, device=dev) if keep_mask is None else keep_mask.to(device=dev, dtype=torch.bool)
+        assert keep.numel() == f.P
+        names = [name for name, _ in SEGMENTS]
+        n_new = 0
+        if new_rows:
+            assert sorted(new_rows) == sorted(names), "new_rows needs exactly the segments %s" % (names,)
+            n_new = int(new_rows["xyz"].shape[0])
+            assert all(int(new_rows[k].shape[0]) == n_new for k in names)
+        kept = int(keep.sum().item())
+        P2 = kept + n_new
+        torch.cuda.synchronize(dev)
+        if f.world > 1:
+            dist.barrier(f.group)                          # nobody is still inside the previous exchange kernel
+        b, e = self.shard
+        full = torch.zeros(2, f.n_grad, dtype=torch.float32, device=dev)
+        full[0, b:e] = self.exp_avg[:e - b]
+        full[1, b:e] = self.exp_avg_sq[:e - b]
+        if f.world > 1:
+            dist.all_reduce(full, op=dist.ReduceOp.SUM, group=f.group)
+        flat2 = SymmetricGaussians(P2, dev, f.group)       # zeroed: gradients, statistic segments, parameters
+        full2 = torch.zeros(2, flat2.n_grad, dtype=torch.float32, device=dev)
+        cols = dict(SEGMENTS)
+        for name in names:
+            old = f._view(f.params, name)[keep]
+            if n_new:
+                old = torch.cat([old, new_rows[name].to(device=dev, dtype=torch.float32).reshape((n_new,) + tuple(old.shape[1:]))])
+            flat2._view(flat2.params, name).copy_(old)
+            c, o, o2 = cols[name], f.offsets[name], flat2.offsets[name]
+            for k in range(2):                             # new rows keep the zeros (cat_tensors_to_optimizer)
+                full2[k, o2:o2 + kept * c].view(kept, c).copy_(full[k, o:o + f.P * c].view(f.P, c)[keep])
+        opt = FusedExchange(flat2, lrs=self.lrs, spatial_lr_scale=1.0, betas=self.betas, eps=self.eps,
+                            use_multicast=self.use_multicast)
+        opt.calibration_ms = self.calibration_ms
+        opt.step_count = self.step_count
+        b2, e2 = opt.shard
+        opt.exp_avg[:e2 - b2] = full2[0, b2:e2]
+        opt.exp_avg_sq[:e2 - b2] = full2[1, b2:e2]
+        torch.cuda.synchronize(dev)
+        if f.world > 1:
+            dist.barrier(f.group)
+        return opt
