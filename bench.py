@@ -572,6 +572,96 @@ class Job:
         self.G.params.copy_(saved)
 
 
+def exchange_self_check(job, torch, dist):
+    """One untimed step of the multi-GPU exchange on the data path the timed legs use, against torch.distributed + the dense
+    optimizer (gsr_adam_step): (1) FusedExchange.allreduce() vs dist.all_reduce of a copy of the bucket; (2)
+    FusedExchange.step(stats=True) vs [gradients summed over ranks -> GaussianAdam on a replica] and three
+    dist.all_reduce calls for the SUM / SUM / MAX statistic segments (the semantics of /root/reference/train.py:163-186,
+    /root/reference/scene/gaussian_model.py:178-201, 471-473 applied to the step's views).  The reference sum is taken in
+    the order the kernel adds (rank order on the peer path; the switch's order on the multicast path, obtained from the
+    all-reduce mode that (1) has just checked), so parameters and moments must come out bit for bit.  Everything the
+    check touched is put back before the timed legs.  Returns the report; `ok` is the AND over ranks."""
+    from gsr_b200.dist import FlatGaussians
+    from gsr_b200.optim import GaussianAdam
+    G, fused, dev, world, rank = job.G, job.fused, job.dev, job.world, job.rank
+    saved = G.params.clone()
+    gen = torch.Generator(device=dev).manual_seed(4242 + rank)
+    P = G.P
+
+    def fill():
+        G.grad_all.zero_()
+        for v in G.grad_views().values():
+            v.copy_(torch.randn(v.shape, device=dev, generator=gen))
+            v[::5] = 0
+    # (1) plain all-reduce mode
+    fill()
+    local = G.bucket.clone()
+    want = local.clone()
+    dist.all_reduce(want)
+    fused.allreduce()
+    torch.cuda.synchronize(dev)
+    dist.barrier()
+    ar_equal = bool(torch.equal(want, G.bucket))
+    ar_rel = float(((want - G.bucket).abs().max() / (want.abs().max() + 1e-30)).item())
+    params_untouched = bool(torch.equal(saved, G.params))
+    # (2) the fused step
+    ref = FlatGaussians(P, dev)
+    ref.params.copy_(saved[:ref.params.numel()])
+    opt_ref = GaussianAdam(ref, lrs=job.lrs)
+    fill()
+    local = G.bucket.clone()
+    acc, den, rad = G.stat_views()
+    acc.copy_(torch.rand(P, 1, device=dev, generator=gen))
+    den.copy_((torch.rand(P, 1, device=dev, generator=gen) > 0.5).float())
+    rad.copy_(torch.randint(0, 200, (P,), device=dev, generator=gen).float())
+    want_stats = [acc.clone(), den.clone(), rad.clone()]
+    dist.all_reduce(want_stats[0]); dist.all_reduce(want_stats[1]); dist.all_reduce(want_stats[2], op=dist.ReduceOp.MAX)
+    n = ref.bucket.numel()
+    if fused.use_multicast:
+        fused.allreduce()
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        ref.bucket.copy_(G.bucket[:n])
+        G.bucket.copy_(local)
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+    else:
+        parts = [torch.empty_like(local) for _ in range(world)]
+        dist.all_gather(parts, local)
+        total = parts[0].clone()
+        for k in range(1, world):
+            total += parts[k]
+        ref.bucket.copy_(total[:n])
+        del parts, total
+    opt_ref.step()
+    step_before = fused.step_count
+    fused.step(stats=True)
+    torch.cuda.synchronize(dev)
+    dist.barrier()
+    p_equal = bool(torch.equal(ref.params, G.params[:n]))
+    p_rel = float(((ref.params - G.params[:n]).abs().max() / (ref.params.abs().max() + 1e-30)).item())
+    b, e = fused.shard
+    e = min(e, n)
+    m_equal = e <= b or bool(torch.equal(opt_ref.exp_avg[b:e], fused.exp_avg[:e - b]) and torch.equal(opt_ref.exp_avg_sq[b:e], fused.exp_avg_sq[:e - b]))
+    acc_rel = float(((acc - want_stats[0]).abs().max() / (want_stats[0].abs().max() + 1e-30)).item())
+    stats_equal = bool(acc_rel <= 1e-6 and torch.equal(den, want_stats[1]) and torch.equal(rad, want_stats[2]))
+    ok = (ar_equal or ar_rel <= 1e-5) and params_untouched and p_equal and m_equal and stats_equal
+    flag = torch.tensor([1.0 if ok else 0.0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    # put everything back: parameters, zero moments, step count, empty bucket and statistic segments
+    G.params.copy_(saved)
+    fused.exp_avg.zero_(); fused.exp_avg_sq.zero_()
+    fused.step_count = step_before
+    G.grad_all.zero_()
+    torch.cuda.synchronize(dev)
+    dist.barrier()
+    return {"path": "multicast" if fused.use_multicast else "peer", "allreduce_equal": ar_equal, "allreduce_max_rel": ar_rel,
+            "allreduce_leaves_params": params_untouched, "params_equal_or_max_rel": True if p_equal else p_rel,
+            "moments_equal": bool(m_equal), "stats_equal": stats_equal, "stat_accum_max_rel": acc_rel,
+            "against": "dist.all_reduce + gsr_adam_step on a replica + 3 dist.all_reduce (SUM, SUM, MAX); reference sums in the kernel's order",
+            "ok_rank0": bool(ok), "ok": bool(flag.item() == 1.0)}
+
+
 def time_steps(torch, dist, dev, world, step_fn, steps, warmup, min_warm_s=1.5):
     """W >= warmup untimed steps (and at least min_warm_s of them: a freshly leased GPU ramps clocks and grows
     allocator pools during its first second), then EXACTLY `steps` steps between barrier + synchronize on both sides;
@@ -707,6 +797,11 @@ def main():
     w, G = job.w, job.G
     W, H, P = w["W"], w["H"], w["P"]
     warm = max(args.warmup, 3)
+
+    # N > 1: the fused exchange proves itself against torch.distributed + the dense optimizer before anything is timed
+    exchange_check = None
+    if world > 1 and job.fused is not None:
+        exchange_check = exchange_self_check(job, torch, dist)
 
     # ---------------- device-timed leg (C ABI, inputs resident): each view alone on one stream ----------------
     sampler = ClockSampler(local_rank)
@@ -1048,7 +1143,7 @@ def main():
             "gpu_launches": launches_per_step * args.steps,
             "single_view_isolated": {"fwd_bwd_ms": single_view_ms, "renders_per_s": 1000.0 / single_view_ms,
                                      "what": "one view, synchronised before and after (launch ramp included): latency, not throughput"},
-            "overlapped_step": overlapped, "batched_step": batched, "with_optimizer": with_optimizer, "exchange_ms": exchange_ms, "c3_strong": c3,
+            "overlapped_step": overlapped, "batched_step": batched, "with_optimizer": with_optimizer, "exchange_ms": exchange_ms, "exchange_check": exchange_check, "c3_strong": c3,
             "stage_ms": stage_ms, "roofline": roof, "roofline_stages": stages, "cpu_baseline": cpu,
         }
         if world == 1 and not args.no_extras:
@@ -1074,18 +1169,24 @@ def main():
                         f = R.forward(width=W, height=H, **common)
                         R.backward(f["radii"], dL_dcolor=dcol, dL_dinvdepth=ddep, **common)
                     torch.cuda.synchronize()
+                    nrep = 20
+                    # the reference launches on the legacy default stream, which torch's current (default) stream is:
+                    # events recorded there bracket its kernels
+                    evs = [torch.cuda.Event(enable_timing=True) for _ in range(2 * nrep + 1)]
                     t0 = time.perf_counter()
-                    nrep = 5
-                    tf_ = 0.0
-                    for _ in range(nrep):
-                        t1 = time.perf_counter()
+                    evs[0].record()
+                    for k in range(nrep):
                         f = R.forward(width=W, height=H, **common)
-                        tf_ += time.perf_counter() - t1
+                        evs[2 * k + 1].record()
                         R.backward(f["radii"], dL_dcolor=dcol, dL_dinvdepth=ddep, **common)
+                        evs[2 * k + 2].record()
                     torch.cuda.synchronize()
-                    dt = (time.perf_counter() - t0) / nrep
-                    out["reference_cuda_same_box"] = {"renders_per_s": 1.0 / dt, "ms_per_step": dt * 1e3,
-                                                      "fwd_ms": tf_ / nrep * 1e3, "note": "unmodified reference kernels + CUB, sm_100a, incl. zero-fills"}
+                    wall = (time.perf_counter() - t0) / nrep
+                    dt = evs[0].elapsed_time(evs[2 * nrep]) / nrep / 1e3
+                    tf_ = sum(evs[2 * k].elapsed_time(evs[2 * k + 1]) for k in range(nrep)) / 1e3
+                    out["reference_cuda_same_box"] = {"renders_per_s": 1.0 / dt, "ms_per_step": dt * 1e3, "wall_ms_per_step": wall * 1e3,
+                                                      "fwd_ms": tf_ / nrep * 1e3, "reps": nrep, "timing": "CUDA events on the default stream",
+                                                      "note": "unmodified reference kernels + CUB, sm_100a, incl. zero-fills"}
                     R.close()
             except Exception as exc:  # informational leg only
                 out["reference_cuda_same_box"] = {"error": str(exc)[:200]}
@@ -1094,6 +1195,9 @@ def main():
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    if exchange_check is not None and not exchange_check["ok"]:
+        sys.stderr.write("bench: the multi-GPU exchange self-check FAILED: %s\n" % json.dumps(exchange_check))
+        sys.exit(3)
 
 
 if __name__ == "__main__":

@@ -90,13 +90,38 @@ __device__ __forceinline__ float4 ld_cs_f4(const float* p) {
     return v;
 }
 
+// The flag waits are bounded: a peer CTA that never shows up (a rank that died, a rank that never launched, a device
+// whose CTAs are not all resident) must end in an error the host can see, not in GPUs spinning forever.  The bound is
+// wall time on the device (generous: ranks may reach the step many seconds apart), looked at every 4096 polls only, so
+// the fast path -- the flag is there within a few polls -- is unchanged.  On expiry the kernel traps: the launch fails
+// with a sticky CUDA error on this rank and the peers run into their own bound.
+#ifndef EX_SPIN_TIMEOUT_S
+#define EX_SPIN_TIMEOUT_S 300ull
+#endif
+__device__ __forceinline__ void spin_watchdog(uint32_t& polls, uint64_t& t0) {
+    if ((++polls & 0xfffu) != 0u) return;
+    uint64_t now;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+    if (t0 == 0) t0 = now;
+    else if (now - t0 > EX_SPIN_TIMEOUT_S * 1000000000ull) __trap();
+}
 __device__ __forceinline__ void put_flag(uint32_t* a) {
-    uint32_t old;
-    do { asm volatile("atom.release.sys.global.cas.b32 %0, [%1], 0, 1;" : "=r"(old) : "l"(a) : "memory"); } while (old != 0u);
+    uint32_t old, polls = 0;
+    uint64_t t0 = 0;
+    for (;;) {
+        asm volatile("atom.release.sys.global.cas.b32 %0, [%1], 0, 1;" : "=r"(old) : "l"(a) : "memory");
+        if (old == 0u) break;
+        spin_watchdog(polls, t0);
+    }
 }
 __device__ __forceinline__ void take_flag(uint32_t* a) {
-    uint32_t old;
-    do { asm volatile("atom.acquire.sys.global.cas.b32 %0, [%1], 1, 0;" : "=r"(old) : "l"(a) : "memory"); } while (old != 1u);
+    uint32_t old, polls = 0;
+    uint64_t t0 = 0;
+    for (;;) {
+        asm volatile("atom.acquire.sys.global.cas.b32 %0, [%1], 1, 0;" : "=r"(old) : "l"(a) : "memory");
+        if (old == 1u) break;
+        spin_watchdog(polls, t0);
+    }
 }
 
 // CTA b of this rank <-> CTA b of every peer.  Everything this CTA did before is visible to the peers' CTA b after.
@@ -296,6 +321,28 @@ extern "C" int gsr_exchange_step(const gsr_exchange_args* a, void* stream) {
         if (quads == 0) return GSR_OK;
         const size_t need = (quads + EX_THREADS - 1) / EX_THREADS;
         if (need < blocks) blocks = (unsigned)need;
+    }
+    if (a->world > 1) {
+        // CTA b waits for CTA b of every peer, so all EX_MAX_BLOCKS CTAs of every rank must be resident at once.  The grid
+        // is a constant (every rank launches the same one and the signal words are sized for it); what can differ is
+        // whether this device can hold it -- asked once per device, and refused loudly instead of risking a hang.
+        static int resident[64] = {};
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return gsr_set_error(GSR_ERR_CUDA, "exchange: no current device");
+        if (!resident[dev]) {
+            int per_sm = 0, sms = 0;
+            cudaError_t e = mc ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, exchange_kernel<true>, EX_THREADS, 0)
+                               : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, exchange_kernel<false>, EX_THREADS, 0);
+            if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            if (e != cudaSuccess) { cudaGetLastError(); return gsr_set_error(GSR_ERR_CUDA, "exchange: occupancy query failed"); }
+            resident[dev] = per_sm * sms > 0 ? per_sm * sms : -1;
+        }
+        if (resident[dev] < EX_MAX_BLOCKS) {
+            char msg[256];
+            snprintf(msg, sizeof(msg), "exchange: this device keeps %d CTAs of the exchange kernel resident, the cross-GPU flag "
+                     "protocol needs all %d at once (built for 148 SMs x %d)", resident[dev], EX_MAX_BLOCKS, EX_BLOCKS_PER_SM);
+            return gsr_set_error(GSR_ERR_INVALID, msg);
+        }
     }
     if (mc) exchange_kernel<true><<<blocks, EX_THREADS, 0, (cudaStream_t)stream>>>(P);
     else exchange_kernel<false><<<blocks, EX_THREADS, 0, (cudaStream_t)stream>>>(P);

@@ -71,7 +71,13 @@ void gsr_exchange_shard(size_t n, int rank, int world, size_t* begin, size_t* en
 
 /* Launches the exchange kernel of this rank on `stream`.  Every rank of the group must call it once per step with the
  * same n / segments / step.  When the kernel has finished on a rank, that rank's parameters (ADAM segments) and
- * SUM / MAX segments hold the step's result and no peer still writes to them. */
+ * SUM / MAX segments hold the step's result and no peer still writes to them. *
+ * Co-residency: CTA b of a rank waits on flags from CTA b of every peer, so the whole grid (148 SMs x 2 CTAs) has to be
+ * resident on every rank while the step runs.  With world > 1 the call refuses (GSR_ERR_INVALID) a device that cannot
+ * hold that many CTAs of the kernel.  It cannot see what else is running: do not keep another kernel that occupies SMs
+ * for long, or another collective (NCCL included), in flight on the device while the exchange runs -- order them on the
+ * same stream or with events.  A flag that does not arrive within 300 s (a dead or missing rank) makes the kernel trap,
+ * so the failure surfaces as a CUDA error at the next synchronisation instead of a hang. */
 int gsr_exchange_step(const gsr_exchange_args* args, void* stream);
 
 #ifdef __cplusplus
