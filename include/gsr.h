@@ -155,7 +155,7 @@ int gsr_backward(const gsr_backward_args* args, void* stream);
  * (several views may share a stream); the one-launch stages run on `stream`, which is ordered before the chains and
  * continues after all of them.  NULL (or a NULL entry): everything on `stream`.
  */
-#define GSR_MAX_BATCH_VIEWS 8
+#define GSR_MAX_BATCH_VIEWS 8   /* the kernels' own name for this limit is GSR_MAX_VIEWS (csrc/gsr_common.cuh); a static_assert keeps them equal */
 int gsr_forward_batch(int n_views, const gsr_forward_args* views,
                       gsr_alloc_fn geom_alloc, void* const* geom_users,
                       gsr_alloc_fn binning_alloc, void* const* binning_users,
@@ -226,7 +226,7 @@ int gsr_sort_pairs_static(uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_o
  */
 typedef struct gsr_geometry_layout {
     size_t depths;        /* f32[P] */
-    size_t records;       /* f32[P,12]: x,y,conic.a,conic.b | conic.c,opacity,r,g | b,1/depth,0,0 */
+    size_t records;       /* f32[P,12]: x,y,conic.a,conic.c | conic.b,opacity,r,g | b,1/depth,0,0  (conic = [a b; b c]) */
     size_t cov3D;         /* f32[P,6] */
     size_t clamped;       /* u8[P]: bit c set <=> colour channel c was clamped */
     size_t tiles_touched; /* u32[P] */

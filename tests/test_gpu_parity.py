@@ -11,7 +11,7 @@ import numpy as np
 import pytest
 
 import cases
-from test_oracle_golden import GRAD_TOL, GOLD
+from test_oracle_golden import GRAD_TOL, ORACLE_GRAD_TOL, GOLD
 
 pytestmark = pytest.mark.gpu
 
@@ -23,7 +23,8 @@ def _record(kind, name, rep):
     WORST.setdefault(kind, {})[name] = {k: rep[k] for k in rep if k.endswith("_relmax") or k.endswith("_viol") or k.endswith("_absmax")}
 
 
-def _assert_parity(rep, against_ref, name):
+def _assert_parity(rep, against_ref, name, tol=None):
+    tol = GRAD_TOL if tol is None else tol
     assert rep["num_rendered"][0] == rep["num_rendered"][1]
     for k in cases.INT_KEYS:
         assert rep[k] == 0, (name, k, rep[k])
@@ -37,7 +38,7 @@ def _assert_parity(rep, against_ref, name):
         assert rep["out_color_maxabs"] <= 1e-6 and rep["final_T_maxabs"] == 0.0 and rep["invdepth_maxabs"] <= 1e-6
     for k in cases.BWD_KEYS:
         if k + "_relmax" in rep:
-            assert rep[k + "_relmax"] <= GRAD_TOL[k], (name, k, rep[k + "_relmax"])
+            assert rep[k + "_relmax"] <= tol[k], (name, k, rep[k + "_relmax"])
         # elementwise bar: |dx| <= tol |y| + 0.1 tol max|y| for every entry, not just the worst relative to the max
         if k + "_viol" in rep and k + "_relmax" in rep:
             assert rep[k + "_viol"] <= VIOL_FRAC * rep[k + "_size"], (name, k, rep[k + "_viol"], rep[k + "_size"])
@@ -56,9 +57,9 @@ def test_cuda_vs_oracle(cuda, name):
     grads = cases.grads_for(cam)
     o = cases.run_oracle(scene, cam, opts, grads)
     c = cases.run_cuda(scene, cam, opts, grads)
-    rep = cases.compare(c, o, o["borderline"], GRAD_TOL)
+    rep = cases.compare(c, o, o["borderline"], GRAD_TOL)     # the elementwise bar keeps its table; the max-norm bar is 1e-4
     _record("cuda_vs_oracle", name, rep)
-    _assert_parity(rep, False, name)
+    _assert_parity(rep, False, name, ORACLE_GRAD_TOL)
     assert rep.get("n_contrib_borderline_mismatch", 0) <= max(3, int(o["borderline"].sum()))
     # deep_list: every pixel ends on the T < 1e-4 termination test after ~2100 layers, a few land on the threshold
     assert o["borderline"].mean() < (5e-3 if name == "deep_list" else 1e-3)
